@@ -1,0 +1,165 @@
+// gs_common.cuh -- shared declarations of the sm_100a kernels behind libgsplat_b200.so.
+//
+// Numerical contract ("canonical op order"): every decision-critical FP32 expression (depth bits of the
+// sort key, radius, tile rectangle, blend skip / termination tests) is written with explicit
+// __fmaf_rn/__fmul_rn/__fadd_rn intrinsics (which the compiler never re-associates or re-contracts) in
+// the order nvcc emits for the reference kernels (cuda_rasterizer/forward.cu, auxiliary.h), so the
+// integer artefacts are bit-identical to the reference build and to the CPU oracle.  exp() in the blend is
+// gs_exp(): a fixed FMA polynomial, bit-reproducible on CPU and GPU.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/gsplat_b200.h"
+
+#define GS_TILE 16          // BLOCK_X = BLOCK_Y = 16 (cuda_rasterizer/config.h:16-17); defines keys/ranges/n_contrib
+#define GS_ALIGN 256
+
+// ---- workspace layouts (private; reached from outside only through gs_debug_read) ----
+struct GsHeader {            // first 256 bytes of the geom workspace
+  unsigned long long num_rendered;  // N, written by the emit kernel
+  unsigned int overflow;            // N > pair_capacity
+  unsigned int error;               // look-back spin limit hit etc.
+  unsigned int pad[60];
+};
+
+// One packed record per Gaussian, what both blend kernels gather per list entry (3 x LDG.128).
+struct __align__(16) GsRec {
+  float x, y, tau, depth;   // pixel-space mean, ln(255*opacity), view depth
+  float ca, cb, cc, o;      // conic (inverse 2D covariance) + opacity
+  float r, g, b, pad;       // colour used by the blend (colors_precomp or SH result)
+};
+
+struct GsGeom {
+  GsHeader* hdr;
+  GsRec* rec;               // [P]
+  uint32_t* rect;           // [P*2]  (xmin | ymin<<16), (xmax | ymax<<16)
+  uint32_t* tiles_touched;  // [P]
+  float* cov3D;             // [P*6]  (only written when computed from scales/rotations)
+  uint8_t* clamped;         // [P*3]  (SH path)
+};
+
+struct GsImage {
+  uint2* ranges;            // [tiles]
+  uint32_t* n_contrib;      // [H*W]
+  float* final_T;           // [H*W]
+};
+
+struct GsScratch {
+  uint32_t* dkey[2];        // [P] depth bits ping-pong
+  uint32_t* dval[2];        // [P] Gaussian index ping-pong
+  uint32_t* tkey[2];        // [cap] tile id per pair ping-pong
+  uint32_t* tval[2];        // [cap] Gaussian index per pair ping-pong (the last pass writes into the list)
+  // ---- one contiguous region zeroed by a single memset at the start of every forward ----
+  uint32_t* zero_begin;
+  uint32_t* hist;           // [8][256] digit histograms (passes 0-3 depth, 4-7 tile id)
+  uint32_t* counters;       // [64] tickets: [pass] for the sorts, [8] for the emit kernel
+  uint32_t* status_d;       // [4][blocks_d][256] onesweep look-back status, depth passes
+  uint32_t* status_t;       // [4][blocks_t][256] onesweep look-back status, tile passes
+  unsigned long long* scan_status;  // [blocks_e] emit-kernel look-back
+  uint32_t* zero_end;
+  size_t blocks_d, blocks_t, blocks_e;
+};
+
+static inline __host__ __device__ size_t gs_align_up(size_t v) { return (v + GS_ALIGN - 1) / GS_ALIGN * GS_ALIGN; }
+
+template <typename T>
+static inline __host__ void gs_carve(char*& p, T*& out, size_t count) {
+  out = reinterpret_cast<T*>(p);
+  p += gs_align_up(count * sizeof(T));
+}
+
+static inline __host__ size_t gs_carve_geom(char* base, int P, GsGeom* g) {
+  char* p = base;
+  GsGeom t;
+  gs_carve(p, t.hdr, 1);
+  gs_carve(p, t.rec, (size_t)P);
+  gs_carve(p, t.rect, (size_t)P * 2);
+  gs_carve(p, t.tiles_touched, (size_t)P);
+  gs_carve(p, t.cov3D, (size_t)P * 6);
+  gs_carve(p, t.clamped, (size_t)P * 3);
+  if (g) *g = t;
+  return (size_t)(p - base);
+}
+
+static inline __host__ size_t gs_carve_image(char* base, int W, int H, GsImage* im) {
+  char* p = base;
+  GsImage t;
+  size_t tiles = (size_t)((W + GS_TILE - 1) / GS_TILE) * ((H + GS_TILE - 1) / GS_TILE);
+  gs_carve(p, t.ranges, tiles);
+  gs_carve(p, t.n_contrib, (size_t)W * H);
+  gs_carve(p, t.final_T, (size_t)W * H);
+  if (im) *im = t;
+  return (size_t)(p - base);
+}
+
+#define GS_SORT_ITEMS 16
+#define GS_SORT_THREADS 256
+#define GS_SORT_TILE (GS_SORT_ITEMS * GS_SORT_THREADS)   // 4096 keys per CTA
+#define GS_EMIT_THREADS 256
+
+static inline __host__ size_t gs_carve_scratch(char* base, int P, int W, int H, int64_t cap, GsScratch* s) {
+  (void)W; (void)H;
+  char* p = base;
+  GsScratch t;
+  t.blocks_d = ((size_t)P + GS_SORT_TILE - 1) / GS_SORT_TILE + 1;
+  t.blocks_t = ((size_t)cap + GS_SORT_TILE - 1) / GS_SORT_TILE + 1;
+  t.blocks_e = ((size_t)P + GS_EMIT_THREADS - 1) / GS_EMIT_THREADS + 1;
+  for (int i = 0; i < 2; i++) gs_carve(p, t.dkey[i], (size_t)P);
+  for (int i = 0; i < 2; i++) gs_carve(p, t.dval[i], (size_t)P);
+  for (int i = 0; i < 2; i++) gs_carve(p, t.tkey[i], (size_t)cap);
+  for (int i = 0; i < 2; i++) gs_carve(p, t.tval[i], (size_t)cap);
+  t.zero_begin = reinterpret_cast<uint32_t*>(p);
+  gs_carve(p, t.hist, 8 * 256);
+  gs_carve(p, t.counters, 64);
+  gs_carve(p, t.status_d, 4 * t.blocks_d * 256);
+  gs_carve(p, t.status_t, 4 * t.blocks_t * 256);
+  gs_carve(p, t.scan_status, t.blocks_e);
+  t.zero_end = reinterpret_cast<uint32_t*>(p);
+  if (s) *s = t;
+  return (size_t)(p - base);
+}
+
+// ---- device math helpers ----
+#ifdef __CUDACC__
+// a*b + c*d + e*f + g as nvcc contracts it for the reference:  g + fma(e,f, fma(a,b, c*d))
+__device__ __forceinline__ float gs_dot3p(float a, float b, float c, float d, float e, float f, float g) {
+  return __fadd_rn(g, __fmaf_rn(e, f, __fmaf_rn(a, b, __fmul_rn(c, d))));
+}
+__device__ __forceinline__ float gs_dot3(float a, float b, float c, float d, float e, float f) {
+  return __fmaf_rn(e, f, __fmaf_rn(a, b, __fmul_rn(c, d)));
+}
+
+// Deterministic exp for x <= 0 (same specification as oracle/gs_oracle.c:gso_exp, written independently).
+__device__ __forceinline__ float gs_exp(float x) {
+  const float L2E_HI = 0x1.715476p+0f, L2E_LO = 0x1.4ae0cp-26f;
+  float xc = fmaxf(x, -87.0f);
+  float t = __fmul_rn(xc, L2E_HI);
+  float r = __fadd_rn(t, 12582912.0f);
+  float n = __fadd_rn(r, -12582912.0f);
+  float f = __fmaf_rn(xc, L2E_HI, -n);
+  f = __fmaf_rn(xc, L2E_LO, f);
+  float p = 0x1.41fbe4p-13f;
+  p = __fmaf_rn(p, f, 0x1.5f3e5ap-10f);
+  p = __fmaf_rn(p, f, 0x1.3b2d4cp-7f);
+  p = __fmaf_rn(p, f, 0x1.c6aee8p-5f);
+  p = __fmaf_rn(p, f, 0x1.ebfbdcp-3f);
+  p = __fmaf_rn(p, f, 0x1.62e43p-1f);
+  p = __fmaf_rn(p, f, 1.0f);
+  // r's low mantissa bits hold n + 0x400000 (two's complement for negative n): shift into the exponent
+  float res = __uint_as_float(__float_as_uint(p) + (__float_as_uint(r) << 23));
+  return (x >= -87.0f) ? res : 0.0f;
+}
+#endif
+
+// ---- launchers (one per translation unit) ----
+int gs_launch_preprocess(const GsForwardArgs& a, const GsGeom& g, const GsScratch& s, cudaStream_t st);
+int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsScratch& s, uint32_t* list,
+                      int64_t cap, cudaStream_t st);
+int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const uint32_t* list,
+                        cudaStream_t st);
+int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage& im, const uint32_t* list,
+                        cudaStream_t st);
+int gs_launch_preprocess_bwd(const GsBackwardArgs& a, const GsGeom& g, cudaStream_t st);
+int gs_launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
+int gs_check(cudaError_t e);

@@ -1,0 +1,284 @@
+// gs_sort.cu -- binning: replaces InclusiveSum + duplicateWithKeys + cub::DeviceRadixSort::SortPairs +
+// identifyTileRanges (cuda_rasterizer/rasterizer_impl.cu:70-138, 277-318).
+//
+// The reference sorts N (Gaussian, tile) pairs by the 64-bit key tile<<32 | depth_bits with a stable LSD radix sort
+// (6 x 8-bit passes over 12-byte pairs).  The same final order -- ascending (tile, depth bits, Gaussian index) --
+// is produced here with far less traffic and without the host round trip for N:
+//   1. the P Gaussians are sorted by their 32-bit depth key (4 onesweep passes over P, not N, items);
+//   2. one kernel walks the depth-sorted Gaussians, does the tiles_touched prefix sum as a decoupled-look-back
+//      chained scan and emits (tile id, Gaussian index) pairs in that order -- N is produced on the device;
+//   3. the pairs are stably sorted by tile id only (ceil(bits/8) = 2 onesweep passes for up to 65536 tiles);
+//   4. tile ranges are read off the sorted tile ids.
+// Stability of step 3 preserves the depth order of step 1 inside each tile; ties in depth keep ascending Gaussian
+// index because step 1 is stable too, which is exactly the tie order of the reference's stable sort.
+//
+// onesweep pass: one kernel per 8-bit digit; warp-level multi-split with __match_any_sync, per-warp digit counters
+// in shared memory, CTA-wide digit offsets, decoupled look-back across CTAs on a (flag|count) status word per
+// (CTA, digit); digit histograms come for free from the producing kernels (preprocess / emit).
+#include "gs_common.cuh"
+
+namespace {
+
+#define FLAG_LOCAL 0x40000000u
+#define FLAG_INCL 0x80000000u
+#define VALUE_MASK 0x3FFFFFFFu
+#define SPIN_LIMIT (1u << 26)
+
+__device__ __forceinline__ uint32_t ld_volatile(const uint32_t* p) { return *reinterpret_cast<const volatile uint32_t*>(p); }
+__device__ __forceinline__ void st_volatile(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
+
+// One stable 8-bit radix pass.  n is read from n_ptr when non-null (clipped to n_cap), else n = n_cap.
+__global__ void __launch_bounds__(GS_SORT_THREADS)
+onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
+                     const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
+                     const unsigned long long* __restrict__ n_ptr, unsigned long long n_cap, int shift,
+                     const uint32_t* __restrict__ hist, uint32_t* __restrict__ status, uint32_t* __restrict__ ticket,
+                     unsigned int* __restrict__ error_flag) {
+  constexpr int WARPS = GS_SORT_THREADS / 32;
+  __shared__ uint32_t s_warp_hist[WARPS][256];
+  __shared__ uint32_t s_digit_base[256];
+  __shared__ uint32_t s_scan[WARPS];
+  __shared__ uint32_t s_ticket;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  unsigned long long n = n_cap;
+  if (n_ptr) { unsigned long long nn = *n_ptr; n = nn < n_cap ? nn : n_cap; }
+  if (tid == 0) s_ticket = atomicAdd(ticket, 1u);
+#pragma unroll
+  for (int i = 0; i < WARPS; i++) s_warp_hist[i][tid] = 0;
+  __syncthreads();
+  const uint32_t tile = s_ticket;
+  const unsigned long long base = (unsigned long long)tile * GS_SORT_TILE;
+  if (base >= n) return;
+
+  // ---- load keys (warp-striped inside a warp-contiguous chunk) and rank them ----
+  uint32_t key[GS_SORT_ITEMS], rank[GS_SORT_ITEMS];
+  const unsigned long long wbase = base + (unsigned long long)w * (32 * GS_SORT_ITEMS);
+#pragma unroll
+  for (int i = 0; i < GS_SORT_ITEMS; i++) {
+    unsigned long long idx = wbase + i * 32 + lane;
+    key[i] = idx < n ? keys_in[idx] : 0xFFFFFFFFu;
+  }
+  const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+  for (int i = 0; i < GS_SORT_ITEMS; i++) {
+    unsigned long long idx = wbase + i * 32 + lane;
+    bool valid = idx < n;
+    uint32_t digit = (key[i] >> shift) & 255u;
+    uint32_t m = __match_any_sync(0xFFFFFFFFu, valid ? digit : 256u);
+    int leader = __ffs(m) - 1;
+    uint32_t prev = 0;
+    if (valid && lane == leader) {
+      prev = s_warp_hist[w][digit];
+      s_warp_hist[w][digit] = prev + __popc(m);
+    }
+    prev = __shfl_sync(0xFFFFFFFFu, prev, leader);
+    rank[i] = prev + __popc(m & lt_mask);
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // ---- per digit (thread d = digit d): warp-exclusive offsets, CTA count, look-back ----
+  const int d = tid;
+  uint32_t run = 0;
+#pragma unroll
+  for (int i = 0; i < WARPS; i++) {
+    uint32_t c = s_warp_hist[i][d];
+    s_warp_hist[i][d] = run;
+    run += c;
+  }
+  uint32_t* my_status = status + (size_t)tile * 256 + d;
+  st_volatile(my_status, (tile == 0 ? FLAG_INCL : FLAG_LOCAL) | run);
+  uint32_t excl = 0;
+  if (tile > 0) {
+    long long t = (long long)tile - 1;
+    uint32_t spins = 0;
+    while (t >= 0) {
+      uint32_t sv = ld_volatile(status + (size_t)t * 256 + d);
+      if (sv == 0) {
+        if (++spins > SPIN_LIMIT) { atomicExch(error_flag, 1u); break; }
+        continue;
+      }
+      excl += sv & VALUE_MASK;
+      if (sv & FLAG_INCL) break;
+      t--;
+    }
+    st_volatile(my_status, FLAG_INCL | (excl + run));
+  }
+  // exclusive scan of the global digit histogram over the 256 digits
+  uint32_t h = hist[d];
+  uint32_t incl = h;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t2 = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if (lane >= o) incl += t2;
+  }
+  if (lane == 31) s_scan[w] = incl;
+  __syncthreads();
+  uint32_t wpre = 0;
+#pragma unroll
+  for (int i = 0; i < WARPS; i++) wpre += (i < w) ? s_scan[i] : 0u;
+  s_digit_base[d] = wpre + incl - h + excl;
+  __syncthreads();
+
+  // ---- scatter ----
+#pragma unroll
+  for (int i = 0; i < GS_SORT_ITEMS; i++) {
+    unsigned long long idx = wbase + i * 32 + lane;
+    if (idx < n) {
+      uint32_t digit = (key[i] >> shift) & 255u;
+      uint32_t pos = s_digit_base[digit] + s_warp_hist[w][digit] + rank[i];
+      if (keys_out) keys_out[pos] = key[i];
+      vals_out[pos] = vals_in[idx];
+    }
+  }
+}
+
+// Chained scan of tiles_touched over the depth-sorted Gaussians + pair emission (duplicateWithKeys,
+// rasterizer_impl.cu:70-111, without the 64-bit key: the depth order is already in the traversal order).
+__global__ void __launch_bounds__(GS_EMIT_THREADS)
+emit_kernel(int P, const uint32_t* __restrict__ sorted_gid, const uint32_t* __restrict__ tiles_touched,
+            const uint32_t* __restrict__ rect, int grid_x, unsigned long long cap, uint32_t* __restrict__ tkey,
+            uint32_t* __restrict__ tval, uint32_t* __restrict__ hist /* [4][256] tile-id digits */, int tile_passes,
+            unsigned long long* __restrict__ scan_status, uint32_t* __restrict__ ticket, GsHeader* __restrict__ hdr) {
+  constexpr int WARPS = GS_EMIT_THREADS / 32;
+  __shared__ uint32_t s_hist[4 * 256];
+  __shared__ unsigned long long s_wsum[WARPS];
+  __shared__ unsigned long long s_base;
+  __shared__ uint32_t s_ticket;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  if (tid == 0) s_ticket = atomicAdd(ticket, 1u);
+  for (int i = tid; i < tile_passes * 256; i += GS_EMIT_THREADS) s_hist[i] = 0;
+  __syncthreads();
+  const uint32_t blk = s_ticket;
+  const int nblocks = (P + GS_EMIT_THREADS - 1) / GS_EMIT_THREADS;
+  const int i = blk * GS_EMIT_THREADS + tid;
+  uint32_t gid = 0, cnt = 0;
+  if (i < P) { gid = sorted_gid[i]; cnt = tiles_touched[gid]; }
+  // block-exclusive scan of cnt
+  uint32_t incl = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t2 = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if (lane >= o) incl += t2;
+  }
+  if (lane == 31) s_wsum[w] = incl;
+  __syncthreads();
+  unsigned long long wpre = 0, total = 0;
+#pragma unroll
+  for (int k = 0; k < WARPS; k++) { unsigned long long v = s_wsum[k]; if (k < w) wpre += v; total += v; }
+  if (tid == 0) {
+    const unsigned long long F_LOCAL = 1ull << 62, F_INCL = 2ull << 62, VMASK = (1ull << 62) - 1;
+    volatile unsigned long long* st = scan_status;
+    st[blk] = (blk == 0 ? F_INCL : F_LOCAL) | total;
+    unsigned long long excl = 0;
+    if (blk > 0) {
+      long long t = (long long)blk - 1;
+      uint32_t spins = 0;
+      while (t >= 0) {
+        unsigned long long sv = st[t];
+        if (sv == 0) {
+          if (++spins > SPIN_LIMIT) { atomicExch(&hdr->error, 2u); break; }
+          continue;
+        }
+        excl += sv & VMASK;
+        if (sv & F_INCL) break;
+        t--;
+      }
+      st[blk] = F_INCL | (excl + total);
+    }
+    s_base = excl;
+    if ((int)blk == nblocks - 1) {
+      hdr->num_rendered = excl + total;
+      hdr->overflow = (excl + total) > cap ? 1u : 0u;
+    }
+  }
+  __syncthreads();
+  if (cnt) {
+    unsigned long long off = s_base + wpre + (incl - cnt);
+    uint32_t r0 = rect[2 * (size_t)gid], r1 = rect[2 * (size_t)gid + 1];
+    int x0 = r0 & 0xFFFF, y0 = r0 >> 16, x1 = r1 & 0xFFFF, y1 = r1 >> 16;
+    for (int y = y0; y < y1; y++)
+      for (int x = x0; x < x1; x++) {
+        uint32_t t = (uint32_t)(y * grid_x + x);
+        if (off < cap) {
+          tkey[off] = t;
+          tval[off] = gid;
+          for (int p = 0; p < tile_passes; p++) atomicAdd(&s_hist[p * 256 + ((t >> (8 * p)) & 255u)], 1u);
+        }
+        off++;
+      }
+  }
+  __syncthreads();
+  for (int k = tid; k < tile_passes * 256; k += GS_EMIT_THREADS) {
+    uint32_t c = s_hist[k];
+    if (c) atomicAdd(&hist[k], c);
+  }
+}
+
+// identifyTileRanges, rasterizer_impl.cu:116-138 (ranges zeroed beforehand, :310)
+__global__ void tile_ranges_kernel(const uint32_t* __restrict__ tkey_sorted, const unsigned long long* __restrict__ n_ptr,
+                                   unsigned long long cap, uint2* __restrict__ ranges) {
+  unsigned long long n = *n_ptr;
+  if (n > cap) n = cap;
+  for (unsigned long long idx = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; idx < n;
+       idx += (unsigned long long)gridDim.x * blockDim.x) {
+    uint32_t cur = tkey_sorted[idx];
+    if (idx == 0) ranges[cur].x = 0;
+    else {
+      uint32_t prev = tkey_sorted[idx - 1];
+      if (cur != prev) { ranges[prev].y = (uint32_t)idx; ranges[cur].x = (uint32_t)idx; }
+    }
+    if (idx == n - 1) ranges[cur].y = (uint32_t)n;
+  }
+}
+
+uint32_t higher_msb(uint32_t n) {  // rasterizer_impl.cu:35-50
+  uint32_t msb = sizeof(n) * 4, step = msb;
+  while (step > 1) {
+    step /= 2;
+    if (n >> msb) msb += step; else msb -= step;
+  }
+  if (n >> msb) msb++;
+  return msb;
+}
+
+}  // namespace
+
+int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsScratch& s, uint32_t* list,
+                      int64_t cap, cudaStream_t st) {
+  const int P = a.P;
+  const int gx = (a.width + GS_TILE - 1) / GS_TILE, gy = (a.height + GS_TILE - 1) / GS_TILE;
+  const int tiles = gx * gy;
+  // 1. depth sort of the P Gaussians: 4 passes, dkey/dval ping-pong, ends in buffer 0
+  const int blocks_d = (P + GS_SORT_TILE - 1) / GS_SORT_TILE;
+  for (int p = 0; p < 4; p++) {
+    onesweep_pass_kernel<<<blocks_d, GS_SORT_THREADS, 0, st>>>(
+        s.dkey[p & 1], s.dkey[(p + 1) & 1], s.dval[p & 1], s.dval[(p + 1) & 1], nullptr, (unsigned long long)P, 8 * p,
+        s.hist + p * 256, s.status_d + (size_t)p * s.blocks_d * 256, s.counters + p, &g.hdr->error);
+  }
+  // 2. chained scan + pair emission in depth order
+  int bits = (int)higher_msb((uint32_t)tiles);
+  int tile_passes = (bits + 7) / 8;
+  if (tile_passes < 1) tile_passes = 1;
+  if (tile_passes > 4) tile_passes = 4;
+  // the LAST tile pass must write into `list`: choose the start buffer by parity
+  uint32_t* vbuf[2] = {s.tval[0], s.tval[1]};
+  const int blocks_e = (P + GS_EMIT_THREADS - 1) / GS_EMIT_THREADS;
+  emit_kernel<<<blocks_e, GS_EMIT_THREADS, 0, st>>>(P, s.dval[0], g.tiles_touched, g.rect, gx, (unsigned long long)cap,
+                                                    s.tkey[0], vbuf[0], s.hist + 4 * 256, tile_passes, s.scan_status,
+                                                    s.counters + 8, g.hdr);
+  // 3. stable sort of the pairs by tile id
+  const int blocks_t = (int)((cap + GS_SORT_TILE - 1) / GS_SORT_TILE);
+  for (int p = 0; p < tile_passes; p++) {
+    uint32_t* vout = (p == tile_passes - 1) ? list : vbuf[(p + 1) & 1];
+    onesweep_pass_kernel<<<blocks_t, GS_SORT_THREADS, 0, st>>>(
+        s.tkey[p & 1], s.tkey[(p + 1) & 1], vbuf[p & 1], vout, &g.hdr->num_rendered, (unsigned long long)cap, 8 * p,
+        s.hist + (4 + p) * 256, s.status_t + (size_t)p * s.blocks_t * 256, s.counters + 4 + p, &g.hdr->error);
+  }
+  // 4. tile ranges
+  int rb = blocks_t * (GS_SORT_TILE / 256);
+  if (rb > 148 * 16) rb = 148 * 16;
+  if (rb < 1) rb = 1;
+  tile_ranges_kernel<<<rb, 256, 0, st>>>(s.tkey[tile_passes & 1], &g.hdr->num_rendered, (unsigned long long)cap, im.ranges);
+  return gs_check(cudaGetLastError());
+}

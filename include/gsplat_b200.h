@@ -1,0 +1,185 @@
+/*
+ * gsplat_b200.h -- C ABI of the B200-native 3DGS-Avatar hot path (libgsplat_b200.so).
+ *
+ * Plain pointers and sizes only: no torch types, no C++ types.  All pointers are DEVICE pointers unless a
+ * name ends in _host.  The caller owns every buffer (outputs and workspaces); the library never
+ * allocates device memory and keeps no global state, so it is safe for one stream per process-per-GPU.
+ * Every entry point takes the CUDA stream to launch on (a cudaStream_t passed as void*).
+ *
+ * Which reference interface each entry point replaces (paths under
+ * /root/reference/submodules/diff-gaussian-rasterization/):
+ *   gs_forward        <- CudaRasterizer::Rasterizer::forward   cuda_rasterizer/rasterizer.h:31-58,
+ *                        cuda_rasterizer/rasterizer_impl.cu:198-336 (called by RasterizeGaussiansCUDA,
+ *                        rasterize_points.cu:35-115)
+ *   gs_backward       <- CudaRasterizer::Rasterizer::backward  cuda_rasterizer/rasterizer.h:60-84,
+ *                        rasterizer_impl.cu:340-434 (RasterizeGaussiansBackwardCUDA, rasterize_points.cu:117-196)
+ *   gs_mark_visible   <- CudaRasterizer::Rasterizer::markVisible rasterizer.h:24-29, rasterizer_impl.cu:141-153
+ *   gs_*_bytes        <- required<GeometryState/ImageState/BinningState>() rasterizer_impl.h:66-72 and the three
+ *                        std::function<char*(size_t)> resize callbacks of forward()
+ *   gs_debug_*        <- no counterpart; exposes the private workspace (keys, point_list, ranges, n_contrib,
+ *                        final_T) that the bit-exact parity tests compare
+ *   pose_forward / pose_backward <- the PyTorch posing chain models/deformer/rigid.py:49-71 / 215-236,
+ *                        scene/gaussian_model.py:28-32,154-157, models/texture/texture.py:21-38 (no native
+ *                        counterpart in the reference)
+ *
+ * Null pointers select code paths exactly as the reference's nullptr tests do: colors_precomp == NULL -> SH
+ * colours are evaluated (forward.cu:241); cov3D_precomp == NULL -> covariance from scales/rotations
+ * (forward.cu:205).
+ */
+#ifndef GSPLAT_B200_H
+#define GSPLAT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* status codes (0 = ok; negative = error) */
+#define GS_OK 0
+#define GS_ERR_BAD_ARG (-1)        /* null/shape problem; mirrors AT_ERROR in rasterize_points.cu:57-59 */
+#define GS_ERR_WORKSPACE_SMALL (-2) /* a caller buffer is smaller than gs_*_bytes() says */
+#define GS_ERR_CUDA (-3)           /* a CUDA call failed; gs_last_cuda_error() has the code */
+#define GS_ERR_NON_RGB (-4)        /* rasterizer_impl.cu:242-245 */
+
+typedef struct GsForwardArgs {
+  int32_t P;             /* number of Gaussians */
+  int32_t D;             /* active SH degree */
+  int32_t M;             /* SH coefficients per channel held in `shs` ((max_degree+1)^2), 0 if none */
+  int32_t width, height; /* image size */
+  float tan_fovx, tan_fovy;
+  float scale_modifier;
+  int32_t prefiltered;
+  int32_t debug;           /* !=0: synchronise + check after every stage (CHECK_CUDA, auxiliary.h:166-173) */
+  const float* background; /* [3] */
+  const float* means3D;    /* [P,3] */
+  const float* shs;        /* [P,M,3] or NULL */
+  const float* colors_precomp; /* [P,3] or NULL */
+  const float* opacities;  /* [P] */
+  const float* scales;     /* [P,3] or NULL */
+  const float* rotations;  /* [P,4] (w,x,y,z) or NULL */
+  const float* cov3D_precomp; /* [P,6] or NULL */
+  const float* viewmatrix; /* [16] */
+  const float* projmatrix; /* [16] */
+  const float* campos;     /* [3] */
+  float* out_color;        /* [3,H,W] */
+  int32_t* radii;          /* [P] */
+} GsForwardArgs;
+
+typedef struct GsBackwardArgs {
+  int32_t P, D, M;
+  int32_t width, height;
+  float tan_fovx, tan_fovy;
+  float scale_modifier;
+  int32_t debug;
+  const float* background;
+  const float* means3D;
+  const float* shs;
+  const float* colors_precomp;
+  const float* scales;
+  const float* rotations;
+  const float* cov3D_precomp;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+  const int32_t* radii;
+  const float* dL_dpix;  /* [3,H,W] */
+  /* outputs; every one must be zero-filled by the caller (rasterize_points.cu:151-159) */
+  float* dL_dmean2D;     /* [P,3]  (.z stays 0) */
+  float* dL_dconic;      /* [P,4]  (2x2; .z never written) */
+  float* dL_dopacity;    /* [P] */
+  float* dL_dcolor;      /* [P,3] */
+  float* dL_dmean3D;     /* [P,3] */
+  float* dL_dcov3D;      /* [P,6] */
+  float* dL_dsh;         /* [P,M,3] or NULL when M == 0 */
+  float* dL_dscale;      /* [P,3] */
+  float* dL_drot;        /* [P,4] */
+} GsBackwardArgs;
+
+/* Workspace sizes.  geom and image are kept for backward (like geomBuffer / imgBuffer); `list` holds the
+ * sorted Gaussian index per (Gaussian, tile) pair (like binningBuffer) and is kept too; `scratch` is only
+ * used inside gs_forward and may be reused by the next call. */
+size_t gs_geom_bytes(int32_t P);
+size_t gs_image_bytes(int32_t width, int32_t height);
+size_t gs_list_bytes(int64_t pair_capacity);
+size_t gs_scratch_bytes(int32_t P, int32_t width, int32_t height, int64_t pair_capacity);
+
+/* Forward.  Launches everything on `stream` without synchronising (unless args->debug).  The number of
+ * (Gaussian, tile) pairs N is produced on the device; when it exceeds pair_capacity the image is NOT valid
+ * (the kernels stop at capacity): the caller reads N back with gs_read_num_rendered() (or from
+ * num_rendered_pinned_host, filled by an async copy on `stream`) and, if N > pair_capacity, calls gs_forward
+ * again with larger `list` / `scratch` buffers.  Returns GS_OK or a negative status. */
+int gs_forward(const GsForwardArgs* args, void* geom, size_t geom_bytes, void* image, size_t image_bytes,
+               void* list, size_t list_bytes, void* scratch, size_t scratch_bytes, int64_t pair_capacity,
+               int64_t* num_rendered_pinned_host, void* stream);
+
+/* Blocking read of N from a geom workspace filled by gs_forward on `stream`. */
+int gs_read_num_rendered(const void* geom, int64_t* num_rendered_host, void* stream);
+
+int gs_backward(const GsBackwardArgs* args, const void* geom, size_t geom_bytes, const void* image,
+                size_t image_bytes, const void* list, size_t list_bytes, void* stream);
+
+/* present[P] (bytes 0/1) = p_view.z > 0.2 */
+int gs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                    uint8_t* present, void* stream);
+
+/* Debug accessors (device -> device copies into caller buffers; used by the parity tests).
+ * which: 0 ranges uint32[tiles*2] | 1 n_contrib uint32[H*W] | 2 final_T float[H*W] | 3 point_list uint32[N]
+ *        4 sorted keys uint64[N] (tile<<32 | depth bits) | 5 means2D float[P*2] | 6 depths float[P]
+ *        7 conic_opacity float[P*4] | 8 tiles_touched uint32[P] | 9 rgb float[P*3] | 10 cov3D float[P*6]
+ *        11 clamped uint8[P*3] */
+int gs_debug_read(int32_t which, const GsForwardArgs* args, const void* geom, const void* image, const void* list,
+                  int64_t num_rendered, void* dst, size_t dst_bytes, void* stream);
+
+/* ---- posing (fused rigid LBS + covariance + SH colour) ---- */
+typedef struct PoseArgs {
+  int32_t P;
+  int32_t sh_degree;      /* active degree 0..3 */
+  int32_t M;              /* coefficients per channel stored (16 for max degree 3) */
+  int32_t cano_view_dir;  /* texture.py:24 */
+  float scaling_modifier;
+  const float* xyz;       /* [P,3] canonical means */
+  const float* rotation;  /* [P,4] raw quaternions (normalised inside, general_utils.py:88-90) */
+  const float* scaling;   /* [P,3] log-scales */
+  const float* opacity;   /* [P] logits */
+  const float* features_dc;   /* [P,1,3] */
+  const float* features_rest; /* [P,M-1,3] (may be NULL when M == 1) */
+  const float* weights;   /* [P,24] skinning weights */
+  const float* bone_transforms; /* [24,4,4] row-major */
+  const float* camera_center;   /* [3] */
+  /* outputs */
+  float* means3D;   /* [P,3] */
+  float* cov3D;     /* [P,6] */
+  float* colors;    /* [P,3] */
+  float* opacity_out; /* [P] sigmoid */
+  float* T_fwd;     /* [P,16] or NULL */
+  float* rotation_bar; /* [P,9] or NULL */
+} PoseArgs;
+
+typedef struct PoseBackwardArgs {
+  PoseArgs fwd;             /* same inputs as the forward call (outputs ignored) */
+  const float* dL_dmeans3D; /* [P,3] */
+  const float* dL_dcov3D;   /* [P,6] */
+  const float* dL_dcolors;  /* [P,3] */
+  const float* dL_dopacity; /* [P] */
+  /* outputs (assigned, not accumulated) */
+  float* dL_dxyz;      /* [P,3] */
+  float* dL_drotation; /* [P,4] */
+  float* dL_dscaling;  /* [P,3] */
+  float* dL_dopacity_logit; /* [P] */
+  float* dL_dfeatures_dc;   /* [P,1,3] */
+  float* dL_dfeatures_rest; /* [P,M-1,3] */
+  float* dL_dweights;  /* [P,24] or NULL */
+} PoseBackwardArgs;
+
+int pose_forward(const PoseArgs* args, void* stream);
+int pose_backward(const PoseBackwardArgs* args, void* stream);
+
+int gs_last_cuda_error(void);
+const char* gs_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
