@@ -19,6 +19,22 @@ int gs_check(cudaError_t e) {
     if (_s != GS_OK) return _s; \
   } while (0)
 
+// ---- optional per-stage timing (bench.py's roofline leg): CUDA events on the launching stream ----
+enum { ST_PRE = 0, ST_BIN, ST_BLEND_F, ST_BLEND_B, ST_PRE_B, ST_COUNT };
+static int g_prof_on = 0;
+static cudaEvent_t g_ev[ST_COUNT][2];
+static int g_ev_valid[ST_COUNT];
+static int g_ev_init = 0;
+static void prof_mark(int stage, int end, cudaStream_t st) {
+  if (!g_prof_on) return;
+  if (!g_ev_init) {
+    for (int i = 0; i < ST_COUNT; i++) { cudaEventCreate(&g_ev[i][0]); cudaEventCreate(&g_ev[i][1]); g_ev_valid[i] = 0; }
+    g_ev_init = 1;
+  }
+  cudaEventRecord(g_ev[stage][end], st);
+  if (end) g_ev_valid[stage] = 1;
+}
+
 static int debug_sync(int debug, cudaStream_t st) {
   if (!debug) return GS_OK;
   return gs_check(cudaStreamSynchronize(st));
@@ -62,14 +78,20 @@ int gs_forward(const GsForwardArgs* args, void* geom, size_t geom_bytes, void* i
   GS_TRY(gs_check(cudaMemsetAsync(s.zero_begin, 0, (size_t)((char*)s.zero_end - (char*)s.zero_begin), st)));
   GS_TRY(gs_check(cudaMemsetAsync(im.ranges, 0, tiles * sizeof(uint2), st)));  // rasterizer_impl.cu:310
 
+  prof_mark(ST_PRE, 0, st);
   GS_TRY(gs_launch_preprocess(a, g, s, st));
+  prof_mark(ST_PRE, 1, st);
   GS_TRY(debug_sync(a.debug, st));
+  prof_mark(ST_BIN, 0, st);
   GS_TRY(gs_launch_binning(a, g, im, s, (uint32_t*)list, pair_capacity, st));
+  prof_mark(ST_BIN, 1, st);
   GS_TRY(debug_sync(a.debug, st));
   if (num_rendered_pinned_host)
     GS_TRY(gs_check(cudaMemcpyAsync(num_rendered_pinned_host, &g.hdr->num_rendered, 2 * sizeof(int64_t),
                                     cudaMemcpyDeviceToHost, st)));
+  prof_mark(ST_BLEND_F, 0, st);
   GS_TRY(gs_launch_blend_fwd(a, g, im, (const uint32_t*)list, st));
+  prof_mark(ST_BLEND_F, 1, st);
   GS_TRY(debug_sync(a.debug, st));
   return GS_OK;
 }
@@ -100,9 +122,13 @@ int gs_backward(const GsBackwardArgs* args, const void* geom, size_t geom_bytes,
   GsImage im;
   if (gs_carve_geom((char*)geom, a.P, &g) > geom_bytes) return GS_ERR_WORKSPACE_SMALL;
   if (gs_carve_image((char*)image, a.width, a.height, &im) > image_bytes) return GS_ERR_WORKSPACE_SMALL;
+  prof_mark(ST_BLEND_B, 0, st);
   GS_TRY(gs_launch_blend_bwd(a, g, im, (const uint32_t*)list, st));
+  prof_mark(ST_BLEND_B, 1, st);
   GS_TRY(debug_sync(a.debug, st));
+  prof_mark(ST_PRE_B, 0, st);
   GS_TRY(gs_launch_preprocess_bwd(a, g, st));
+  prof_mark(ST_PRE_B, 1, st);
   GS_TRY(debug_sync(a.debug, st));
   return GS_OK;
 }
@@ -115,7 +141,40 @@ int gs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, co
   return gs_launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
 }
 
+void gs_profile_enable(int on) { g_prof_on = on; }
+
+/* ms[5] = preprocess, binning (sorts+emit+ranges), blend fwd, blend bwd, preprocess bwd of the LAST call
+ * (-1 where no stage was recorded).  Synchronises on the recorded events. */
+int gs_profile_read(float* ms_host) {
+  for (int i = 0; i < ST_COUNT; i++) {
+    ms_host[i] = -1.f;
+    if (g_ev_init && g_ev_valid[i]) {
+      if (cudaEventSynchronize(g_ev[i][1]) != cudaSuccess) return GS_ERR_CUDA;
+      if (cudaEventElapsedTime(&ms_host[i], g_ev[i][0], g_ev[i][1]) != cudaSuccess) return GS_ERR_CUDA;
+    }
+  }
+  return GS_OK;
+}
+
 }  // extern "C"
+
+// FP32 FMA throughput probe (bench.py measures the FP32 roofline denominator with it: it is not in MEASURED_PEAKS.json)
+namespace {
+__global__ void fma_probe_kernel(int iters, float* out) {
+  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f, a7 = a0 + 7.f;
+  const float m = 0.999f, c = 1e-3f;
+  for (int i = 0; i < iters; i++) {
+    a0 = fmaf(a0, m, c); a1 = fmaf(a1, m, c); a2 = fmaf(a2, m, c); a3 = fmaf(a3, m, c);
+    a4 = fmaf(a4, m, c); a5 = fmaf(a5, m, c); a6 = fmaf(a6, m, c); a7 = fmaf(a7, m, c);
+  }
+  float r = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+  if (r == 123.456f) out[0] = r;
+}
+}  // namespace
+extern "C" int gs_fma_probe(int blocks, int threads, int iters, float* out_dev, void* stream) {
+  fma_probe_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, out_dev);
+  return gs_check(cudaGetLastError());
+}
 
 // ---- debug accessors ----
 namespace {

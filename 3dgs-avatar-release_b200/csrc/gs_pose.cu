@@ -1,0 +1,322 @@
+// gs_pose.cu -- fused posing of canonical Gaussians: one kernel forward, one kernel backward, replacing the ~60-kernel
+// PyTorch chain of the reference per frame:
+//   rigid LBS of mean and rotation          models/deformer/rigid.py:49-71 (SMPLNN) / :215-236 (SkinningField, after
+//                                           get_forward_transform produced the weights)
+//   build_rotation (normalise + matrix)     utils/general_utils.py:87-108
+//   covariance R S S^T R^T packed to 6      scene/gaussian_model.py:28-32,154-157; utils/general_utils.py:194-207,73-85
+//   activations sigmoid / exp               scene/gaussian_model.py:132-152
+//   SH2RGB: canonical view dir + eval_sh    models/texture/texture.py:21-38; utils/sh_utils.py:58-113
+// and the two GaussianModel.clone() copies (scene/gaussian_model.py:68-87) disappear.
+// HBM-bound: 384 B/Gaussian forward, 716 B/Gaussian backward; one thread per Gaussian, the
+// 24 bone matrices staged in shared memory.
+#include "gs_common.cuh"
+
+namespace {
+
+#define C0f 0.28209479177387814f
+#define C1f 0.4886025119029199f
+__constant__ float pC2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f, -1.0925484305920792f,
+                             0.5462742152960396f};
+__constant__ float pC3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f, 0.3731763325901154f,
+                             -0.4570457994644658f, 1.445305721320277f, -0.5900435899266435f};
+
+__device__ __forceinline__ void sh_basis(int deg, float x, float y, float z, float* b) {
+  b[0] = C0f;
+  if (deg > 0) {
+    b[1] = -C1f * y; b[2] = C1f * z; b[3] = -C1f * x;
+    if (deg > 1) {
+      float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+      b[4] = pC2[0] * xy; b[5] = pC2[1] * yz; b[6] = pC2[2] * (2.0f * zz - xx - yy); b[7] = pC2[3] * xz;
+      b[8] = pC2[4] * (xx - yy);
+      if (deg > 2) {
+        b[9] = pC3[0] * y * (3 * xx - yy); b[10] = pC3[1] * xy * z; b[11] = pC3[2] * y * (4 * zz - xx - yy);
+        b[12] = pC3[3] * z * (2 * zz - 3 * xx - 3 * yy); b[13] = pC3[4] * x * (4 * zz - xx - yy);
+        b[14] = pC3[5] * z * (xx - yy); b[15] = pC3[6] * x * (xx - 3 * yy);
+      }
+    }
+  }
+}
+
+// d(basis_k)/d(x,y,z)
+__device__ __forceinline__ void sh_basis_grad(int deg, float x, float y, float z, float* gx, float* gy, float* gz) {
+#pragma unroll
+  for (int k = 0; k < 16; k++) { gx[k] = 0.f; gy[k] = 0.f; gz[k] = 0.f; }
+  if (deg > 0) {
+    gy[1] = -C1f; gz[2] = C1f; gx[3] = -C1f;
+    if (deg > 1) {
+      float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+      gx[4] = pC2[0] * y; gy[4] = pC2[0] * x;
+      gy[5] = pC2[1] * z; gz[5] = pC2[1] * y;
+      gx[6] = -2.f * pC2[2] * x; gy[6] = -2.f * pC2[2] * y; gz[6] = 4.f * pC2[2] * z;
+      gx[7] = pC2[3] * z; gz[7] = pC2[3] * x;
+      gx[8] = 2.f * pC2[4] * x; gy[8] = -2.f * pC2[4] * y;
+      if (deg > 2) {
+        gx[9] = pC3[0] * 6.f * xy; gy[9] = pC3[0] * 3.f * (xx - yy);
+        gx[10] = pC3[1] * yz; gy[10] = pC3[1] * xz; gz[10] = pC3[1] * xy;
+        gx[11] = pC3[2] * -2.f * xy; gy[11] = pC3[2] * (4.f * zz - xx - 3.f * yy); gz[11] = pC3[2] * 8.f * yz;
+        gx[12] = pC3[3] * -6.f * xz; gy[12] = pC3[3] * -6.f * yz; gz[12] = pC3[3] * (6.f * zz - 3.f * xx - 3.f * yy);
+        gx[13] = pC3[4] * (4.f * zz - 3.f * xx - yy); gy[13] = pC3[4] * -2.f * xy; gz[13] = pC3[4] * 8.f * xz;
+        gx[14] = pC3[5] * 2.f * xz; gy[14] = pC3[5] * -2.f * yz; gz[14] = pC3[5] * (xx - yy);
+        gx[15] = pC3[6] * 3.f * (xx - yy); gy[15] = pC3[6] * -6.f * xy;
+      }
+    }
+  }
+}
+
+struct PoseCore {
+  float A[3][3], t[3];     // blended transform (rows 0..2 of T_fwd)
+  float qn[4], inv_norm;   // normalised quaternion
+  float R[3][3];           // rotation of qn
+  float Rb[3][3];          // A * R
+  float s[3];              // mod * exp(scaling)
+  float xb[3];             // posed mean
+};
+
+__device__ __forceinline__ void pose_core(const PoseArgs& a, int i, const float* __restrict__ s_bones, PoseCore& c) {
+  float T[12];
+#pragma unroll
+  for (int k = 0; k < 12; k++) T[k] = 0.f;
+  const float* w = a.weights + (size_t)i * 24;
+#pragma unroll 4
+  for (int j = 0; j < 24; j++) {
+    const float wj = w[j];
+#pragma unroll
+    for (int k = 0; k < 12; k++) T[k] = fmaf(wj, s_bones[j * 16 + k], T[k]);
+  }
+#pragma unroll
+  for (int r = 0; r < 3; r++) {
+    c.A[r][0] = T[4 * r]; c.A[r][1] = T[4 * r + 1]; c.A[r][2] = T[4 * r + 2]; c.t[r] = T[4 * r + 3];
+  }
+  const float x = a.xyz[3 * (size_t)i], y = a.xyz[3 * (size_t)i + 1], z = a.xyz[3 * (size_t)i + 2];
+#pragma unroll
+  for (int r = 0; r < 3; r++) c.xb[r] = c.A[r][0] * x + c.A[r][1] * y + c.A[r][2] * z + c.t[r];
+  const float4 q = *reinterpret_cast<const float4*>(a.rotation + 4 * (size_t)i);
+  const float norm = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+  c.inv_norm = 1.0f / norm;
+  const float qr = q.x * c.inv_norm, qx = q.y * c.inv_norm, qy = q.z * c.inv_norm, qz = q.w * c.inv_norm;
+  c.qn[0] = qr; c.qn[1] = qx; c.qn[2] = qy; c.qn[3] = qz;
+  c.R[0][0] = 1 - 2 * (qy * qy + qz * qz); c.R[0][1] = 2 * (qx * qy - qr * qz); c.R[0][2] = 2 * (qx * qz + qr * qy);
+  c.R[1][0] = 2 * (qx * qy + qr * qz); c.R[1][1] = 1 - 2 * (qx * qx + qz * qz); c.R[1][2] = 2 * (qy * qz - qr * qx);
+  c.R[2][0] = 2 * (qx * qz - qr * qy); c.R[2][1] = 2 * (qy * qz + qr * qx); c.R[2][2] = 1 - 2 * (qx * qx + qy * qy);
+#pragma unroll
+  for (int r = 0; r < 3; r++)
+#pragma unroll
+    for (int k = 0; k < 3; k++) c.Rb[r][k] = c.A[r][0] * c.R[0][k] + c.A[r][1] * c.R[1][k] + c.A[r][2] * c.R[2][k];
+#pragma unroll
+  for (int k = 0; k < 3; k++) c.s[k] = a.scaling_modifier * expf(a.scaling[3 * (size_t)i + k]);
+}
+
+// view direction fed to eval_sh (texture.py:23-35): returns d (un-normalised), n = |d|
+__device__ __forceinline__ void view_dir(const PoseArgs& a, const PoseCore& c, const float* cam, float* d, float& n) {
+  const float v0 = c.xb[0] - cam[0], v1 = c.xb[1] - cam[1], v2 = c.xb[2] - cam[2];
+  if (a.cano_view_dir) {  // R_bwd = T_fwd[:3,:3]^T (transpose, not inverse)
+    d[0] = c.A[0][0] * v0 + c.A[1][0] * v1 + c.A[2][0] * v2;
+    d[1] = c.A[0][1] * v0 + c.A[1][1] * v1 + c.A[2][1] * v2;
+    d[2] = c.A[0][2] * v0 + c.A[1][2] * v1 + c.A[2][2] * v2;
+  } else { d[0] = v0; d[1] = v1; d[2] = v2; }
+  n = sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+}
+
+__device__ __forceinline__ float sh_coef(const PoseArgs& a, int i, int k, int ch) {
+  return k == 0 ? a.features_dc[3 * (size_t)i + ch] : a.features_rest[((size_t)i * (a.M - 1) + (k - 1)) * 3 + ch];
+}
+
+__global__ void __launch_bounds__(128) pose_fwd_kernel(PoseArgs a) {
+  __shared__ float s_bones[24 * 16];
+  __shared__ float s_cam[3];
+  for (int k = threadIdx.x; k < 24 * 16; k += blockDim.x) s_bones[k] = a.bone_transforms[k];
+  if (threadIdx.x < 3) s_cam[threadIdx.x] = a.camera_center[threadIdx.x];
+  __syncthreads();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.P; i += gridDim.x * blockDim.x) {
+    PoseCore c;
+    pose_core(a, i, s_bones, c);
+    a.means3D[3 * (size_t)i] = c.xb[0]; a.means3D[3 * (size_t)i + 1] = c.xb[1]; a.means3D[3 * (size_t)i + 2] = c.xb[2];
+    float L[3][3];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+      for (int k = 0; k < 3; k++) L[r][k] = c.Rb[r][k] * c.s[k];
+    float* cov = a.cov3D + 6 * (size_t)i;
+    cov[0] = L[0][0] * L[0][0] + L[0][1] * L[0][1] + L[0][2] * L[0][2];
+    cov[1] = L[0][0] * L[1][0] + L[0][1] * L[1][1] + L[0][2] * L[1][2];
+    cov[2] = L[0][0] * L[2][0] + L[0][1] * L[2][1] + L[0][2] * L[2][2];
+    cov[3] = L[1][0] * L[1][0] + L[1][1] * L[1][1] + L[1][2] * L[1][2];
+    cov[4] = L[1][0] * L[2][0] + L[1][1] * L[2][1] + L[1][2] * L[2][2];
+    cov[5] = L[2][0] * L[2][0] + L[2][1] * L[2][1] + L[2][2] * L[2][2];
+    a.opacity_out[i] = 1.0f / (1.0f + expf(-a.opacity[i]));
+    float d[3], n;
+    view_dir(a, c, s_cam, d, n);
+    const float inv = 1.0f / (n + 1e-12f);
+    float b[16];
+    sh_basis(a.sh_degree, d[0] * inv, d[1] * inv, d[2] * inv, b);
+    const int nb = (a.sh_degree + 1) * (a.sh_degree + 1);
+#pragma unroll
+    for (int ch = 0; ch < 3; ch++) {
+      float acc = 0.f;
+      for (int k = 0; k < nb; k++) acc += b[k] * sh_coef(a, i, k, ch);
+      a.colors[3 * (size_t)i + ch] = fmaxf(acc + 0.5f, 0.0f);
+    }
+    if (a.T_fwd) {
+      float* T = a.T_fwd + 16 * (size_t)i;
+#pragma unroll
+      for (int r = 0; r < 3; r++) { T[4 * r] = c.A[r][0]; T[4 * r + 1] = c.A[r][1]; T[4 * r + 2] = c.A[r][2]; T[4 * r + 3] = c.t[r]; }
+      float t3[4] = {0.f, 0.f, 0.f, 0.f};
+      const float* w = a.weights + (size_t)i * 24;
+      for (int j = 0; j < 24; j++)
+#pragma unroll
+        for (int k = 0; k < 4; k++) t3[k] = fmaf(w[j], s_bones[j * 16 + 12 + k], t3[k]);
+#pragma unroll
+      for (int k = 0; k < 4; k++) T[12 + k] = t3[k];
+    }
+    if (a.rotation_bar) {
+#pragma unroll
+      for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) a.rotation_bar[9 * (size_t)i + 3 * r + k] = c.Rb[r][k];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
+  const PoseArgs& a = ba.fwd;
+  __shared__ float s_bones[24 * 16];
+  __shared__ float s_cam[3];
+  for (int k = threadIdx.x; k < 24 * 16; k += blockDim.x) s_bones[k] = a.bone_transforms[k];
+  if (threadIdx.x < 3) s_cam[threadIdx.x] = a.camera_center[threadIdx.x];
+  __syncthreads();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.P; i += gridDim.x * blockDim.x) {
+    PoseCore c;
+    pose_core(a, i, s_bones, c);
+    float gxb[3] = {ba.dL_dmeans3D[3 * (size_t)i], ba.dL_dmeans3D[3 * (size_t)i + 1], ba.dL_dmeans3D[3 * (size_t)i + 2]};
+    // ---- colour -> SH coefficients and view direction ----
+    {
+      float d[3], n;
+      view_dir(a, c, s_cam, d, n);
+      const float inv = 1.0f / (n + 1e-12f);
+      const float ux = d[0] * inv, uy = d[1] * inv, uz = d[2] * inv;
+      float b[16], bx[16], by[16], bz[16];
+      sh_basis(a.sh_degree, ux, uy, uz, b);
+      sh_basis_grad(a.sh_degree, ux, uy, uz, bx, by, bz);
+      const int nb = (a.sh_degree + 1) * (a.sh_degree + 1);
+      float gu[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+      for (int ch = 0; ch < 3; ch++) {
+        float acc = 0.f;
+        for (int k = 0; k < nb; k++) acc += b[k] * sh_coef(a, i, k, ch);
+        const float gc = (acc + 0.5f < 0.0f) ? 0.f : ba.dL_dcolors[3 * (size_t)i + ch];
+        ba.dL_dfeatures_dc[3 * (size_t)i + ch] = b[0] * gc;
+        for (int k = 1; k < a.M; k++) {
+          const float coef = k < nb ? sh_coef(a, i, k, ch) : 0.f;
+          ba.dL_dfeatures_rest[((size_t)i * (a.M - 1) + (k - 1)) * 3 + ch] = k < nb ? b[k] * gc : 0.f;
+          if (k < nb) { gu[0] += bx[k] * coef * gc; gu[1] += by[k] * coef * gc; gu[2] += bz[k] * coef * gc; }
+        }
+      }
+      // u = d / (n + eps):  dL/dd = g/(n+eps) - d (d.g) / (n (n+eps)^2)
+      const float dg = d[0] * gu[0] + d[1] * gu[1] + d[2] * gu[2];
+      const float k2 = n > 0.f ? dg * inv * inv / n : 0.f;
+      const float gd[3] = {gu[0] * inv - d[0] * k2, gu[1] * inv - d[1] * k2, gu[2] * inv - d[2] * k2};
+      if (a.cano_view_dir) {  // d = A^T v with A detached -> dL/dv = A gd
+#pragma unroll
+        for (int r = 0; r < 3; r++) gxb[r] += c.A[r][0] * gd[0] + c.A[r][1] * gd[1] + c.A[r][2] * gd[2];
+      } else {
+#pragma unroll
+        for (int r = 0; r < 3; r++) gxb[r] += gd[r];
+      }
+    }
+    // ---- covariance -> R_bar, scaling ----
+    const float* g6 = ba.dL_dcov3D + 6 * (size_t)i;
+    const float G[3][3] = {{g6[0], 0.5f * g6[1], 0.5f * g6[2]}, {0.5f * g6[1], g6[3], 0.5f * g6[4]}, {0.5f * g6[2], 0.5f * g6[4], g6[5]}};
+    float L[3][3], dLm[3][3], gRb[3][3];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+      for (int k = 0; k < 3; k++) L[r][k] = c.Rb[r][k] * c.s[k];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+      for (int k = 0; k < 3; k++) dLm[r][k] = 2.f * (G[r][0] * L[0][k] + G[r][1] * L[1][k] + G[r][2] * L[2][k]);
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      const float gs = dLm[0][k] * c.Rb[0][k] + dLm[1][k] * c.Rb[1][k] + dLm[2][k] * c.Rb[2][k];
+      ba.dL_dscaling[3 * (size_t)i + k] = gs * c.s[k];  // s = mod * exp(sigma)
+#pragma unroll
+      for (int r = 0; r < 3; r++) gRb[r][k] = dLm[r][k] * c.s[k];
+    }
+    // R_bar = A R:  dL/dR = A^T gRb ; dL/dA = gRb R^T (+ gxb x^T below)
+    float gR[3][3], gA[3][3];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        gR[r][k] = c.A[0][r] * gRb[0][k] + c.A[1][r] * gRb[1][k] + c.A[2][r] * gRb[2][k];
+        gA[r][k] = gRb[r][0] * c.R[k][0] + gRb[r][1] * c.R[k][1] + gRb[r][2] * c.R[k][2];
+      }
+    // rotation matrix -> normalised quaternion (w,x,y,z)
+    {
+      const float qr = c.qn[0], qx = c.qn[1], qy = c.qn[2], qz = c.qn[3];
+      float gq[4];
+      gq[0] = 2.f * (-qz * gR[0][1] + qy * gR[0][2] + qz * gR[1][0] - qx * gR[1][2] - qy * gR[2][0] + qx * gR[2][1]);
+      gq[1] = 2.f * (qy * gR[0][1] + qz * gR[0][2] + qy * gR[1][0] - 2.f * qx * gR[1][1] - qr * gR[1][2] + qz * gR[2][0] + qr * gR[2][1] - 2.f * qx * gR[2][2]);
+      gq[2] = 2.f * (-2.f * qy * gR[0][0] + qx * gR[0][1] + qr * gR[0][2] + qx * gR[1][0] + qz * gR[1][2] - qr * gR[2][0] + qz * gR[2][1] - 2.f * qy * gR[2][2]);
+      gq[3] = 2.f * (-2.f * qz * gR[0][0] - qr * gR[0][1] + qx * gR[0][2] + qr * gR[1][0] - 2.f * qz * gR[1][1] + qy * gR[1][2] + qx * gR[2][0] + qy * gR[2][1]);
+      const float dotq = gq[0] * qr + gq[1] * qx + gq[2] * qy + gq[3] * qz;
+      float4 out;
+      out.x = (gq[0] - qr * dotq) * c.inv_norm; out.y = (gq[1] - qx * dotq) * c.inv_norm;
+      out.z = (gq[2] - qy * dotq) * c.inv_norm; out.w = (gq[3] - qz * dotq) * c.inv_norm;
+      *reinterpret_cast<float4*>(ba.dL_drotation + 4 * (size_t)i) = out;
+    }
+    // mean: x_bar = A x + t
+    const float x = a.xyz[3 * (size_t)i], y = a.xyz[3 * (size_t)i + 1], z = a.xyz[3 * (size_t)i + 2];
+#pragma unroll
+    for (int k = 0; k < 3; k++) ba.dL_dxyz[3 * (size_t)i + k] = c.A[0][k] * gxb[0] + c.A[1][k] * gxb[1] + c.A[2][k] * gxb[2];
+    const float so = 1.0f / (1.0f + expf(-a.opacity[i]));
+    ba.dL_dopacity_logit[i] = ba.dL_dopacity[i] * so * (1.0f - so);
+    if (ba.dL_dweights) {
+      float gT[12];
+#pragma unroll
+      for (int r = 0; r < 3; r++) {
+        gT[4 * r] = gA[r][0] + gxb[r] * x; gT[4 * r + 1] = gA[r][1] + gxb[r] * y; gT[4 * r + 2] = gA[r][2] + gxb[r] * z;
+        gT[4 * r + 3] = gxb[r];
+      }
+      float* gw = ba.dL_dweights + (size_t)i * 24;
+      for (int j = 0; j < 24; j++) {
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < 12; k++) acc = fmaf(gT[k], s_bones[j * 16 + k], acc);
+        gw[j] = acc;
+      }
+    }
+  }
+}
+
+}  // namespace
+
+static int pose_args_ok(const PoseArgs& a) {
+  if (a.P < 0 || a.sh_degree < 0 || a.sh_degree > 3) return 0;
+  if (a.M < (a.sh_degree + 1) * (a.sh_degree + 1) || a.M > 16) return 0;
+  if (!a.xyz || !a.rotation || !a.scaling || !a.opacity || !a.features_dc || !a.weights || !a.bone_transforms || !a.camera_center) return 0;
+  if (a.M > 1 && !a.features_rest) return 0;
+  return 1;
+}
+
+extern "C" int pose_forward(const PoseArgs* args, void* stream) {
+  if (!args || !pose_args_ok(*args)) return GS_ERR_BAD_ARG;
+  if (!args->means3D || !args->cov3D || !args->colors || !args->opacity_out) return GS_ERR_BAD_ARG;
+  if (args->P == 0) return GS_OK;
+  int blocks = (args->P + 127) / 128;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  pose_fwd_kernel<<<blocks, 128, 0, (cudaStream_t)stream>>>(*args);
+  return gs_check(cudaGetLastError());
+}
+
+extern "C" int pose_backward(const PoseBackwardArgs* args, void* stream) {
+  if (!args || !pose_args_ok(args->fwd)) return GS_ERR_BAD_ARG;
+  if (!args->dL_dmeans3D || !args->dL_dcov3D || !args->dL_dcolors || !args->dL_dopacity) return GS_ERR_BAD_ARG;
+  if (!args->dL_dxyz || !args->dL_drotation || !args->dL_dscaling || !args->dL_dopacity_logit || !args->dL_dfeatures_dc) return GS_ERR_BAD_ARG;
+  if (args->fwd.M > 1 && !args->dL_dfeatures_rest) return GS_ERR_BAD_ARG;
+  if (args->fwd.P == 0) return GS_OK;
+  int blocks = (args->fwd.P + 127) / 128;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  pose_bwd_kernel<<<blocks, 128, 0, (cudaStream_t)stream>>>(*args);
+  return gs_check(cudaGetLastError());
+}
