@@ -31,6 +31,14 @@ class PoseBackwardArgs(ctypes.Structure):
 
 
 _configured = False
+_last_slab = [None]
+
+
+def last_grad_slab():
+    """The flat FP32 buffer the last pose backward wrote all per-Gaussian parameter gradients into
+    (xyz 3 | rotation 4 | scaling 3 | opacity 1 | features_dc 3 | features_rest 3*(M-1), attribute-major).  Data-parallel
+    training all-reduces THIS buffer with one NCCL call; the .grad tensors of the parameters are views into it."""
+    return _last_slab[0]
 
 
 def _lib():
@@ -129,6 +137,7 @@ class _FusedPose(torch.autograd.Function):
             ba.dL_dweights = gw.data_ptr() if gw is not None else None
             if P:
                 _gs._check(L.pose_backward(ctypes.byref(ba), torch.cuda.current_stream(dev).cuda_stream), "pose_backward")
+        _last_slab[0] = flat
         gop = gop.view(op.shape)
         return gxyz, grot, gsc, gop, gdc, grest, gw, None, None, None, None, None, None
 
