@@ -20,12 +20,12 @@ int gs_check(cudaError_t e) {
   } while (0)
 
 // ---- optional per-stage timing (bench.py's roofline leg): CUDA events on the launching stream ----
-enum { ST_PRE = 0, ST_BIN, ST_BLEND_F, ST_BLEND_B, ST_PRE_B, ST_COUNT };
+enum { ST_PRE = 0, ST_BIN, ST_BLEND_F, ST_BLEND_B, ST_PRE_B, ST_POSE_F, ST_POSE_B, ST_COUNT };
 static int g_prof_on = 0;
 static cudaEvent_t g_ev[ST_COUNT][2];
 static int g_ev_valid[ST_COUNT];
 static int g_ev_init = 0;
-static void prof_mark(int stage, int end, cudaStream_t st) {
+void gs_prof_mark(int stage, int end, cudaStream_t st) {
   if (!g_prof_on) return;
   if (!g_ev_init) {
     for (int i = 0; i < ST_COUNT; i++) { cudaEventCreate(&g_ev[i][0]); cudaEventCreate(&g_ev[i][1]); g_ev_valid[i] = 0; }
@@ -78,20 +78,20 @@ int gs_forward(const GsForwardArgs* args, void* geom, size_t geom_bytes, void* i
   GS_TRY(gs_check(cudaMemsetAsync(s.zero_begin, 0, (size_t)((char*)s.zero_end - (char*)s.zero_begin), st)));
   GS_TRY(gs_check(cudaMemsetAsync(im.ranges, 0, tiles * sizeof(uint2), st)));  // rasterizer_impl.cu:310
 
-  prof_mark(ST_PRE, 0, st);
+  gs_prof_mark(ST_PRE, 0, st);
   GS_TRY(gs_launch_preprocess(a, g, s, st));
-  prof_mark(ST_PRE, 1, st);
+  gs_prof_mark(ST_PRE, 1, st);
   GS_TRY(debug_sync(a.debug, st));
-  prof_mark(ST_BIN, 0, st);
+  gs_prof_mark(ST_BIN, 0, st);
   GS_TRY(gs_launch_binning(a, g, im, s, (uint32_t*)list, pair_capacity, st));
-  prof_mark(ST_BIN, 1, st);
+  gs_prof_mark(ST_BIN, 1, st);
   GS_TRY(debug_sync(a.debug, st));
   if (num_rendered_pinned_host)
     GS_TRY(gs_check(cudaMemcpyAsync(num_rendered_pinned_host, &g.hdr->num_rendered, 2 * sizeof(int64_t),
                                     cudaMemcpyDeviceToHost, st)));
-  prof_mark(ST_BLEND_F, 0, st);
+  gs_prof_mark(ST_BLEND_F, 0, st);
   GS_TRY(gs_launch_blend_fwd(a, g, im, (const uint32_t*)list, st));
-  prof_mark(ST_BLEND_F, 1, st);
+  gs_prof_mark(ST_BLEND_F, 1, st);
   GS_TRY(debug_sync(a.debug, st));
   return GS_OK;
 }
@@ -122,13 +122,13 @@ int gs_backward(const GsBackwardArgs* args, const void* geom, size_t geom_bytes,
   GsImage im;
   if (gs_carve_geom((char*)geom, a.P, &g) > geom_bytes) return GS_ERR_WORKSPACE_SMALL;
   if (gs_carve_image((char*)image, a.width, a.height, &im) > image_bytes) return GS_ERR_WORKSPACE_SMALL;
-  prof_mark(ST_BLEND_B, 0, st);
+  gs_prof_mark(ST_BLEND_B, 0, st);
   GS_TRY(gs_launch_blend_bwd(a, g, im, (const uint32_t*)list, st));
-  prof_mark(ST_BLEND_B, 1, st);
+  gs_prof_mark(ST_BLEND_B, 1, st);
   GS_TRY(debug_sync(a.debug, st));
-  prof_mark(ST_PRE_B, 0, st);
+  gs_prof_mark(ST_PRE_B, 0, st);
   GS_TRY(gs_launch_preprocess_bwd(a, g, st));
-  prof_mark(ST_PRE_B, 1, st);
+  gs_prof_mark(ST_PRE_B, 1, st);
   GS_TRY(debug_sync(a.debug, st));
   return GS_OK;
 }
@@ -143,7 +143,7 @@ int gs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, co
 
 void gs_profile_enable(int on) { g_prof_on = on; }
 
-/* ms[5] = preprocess, binning (sorts+emit+ranges), blend fwd, blend bwd, preprocess bwd of the LAST call
+/* ms[7] = preprocess, binning (sorts+emit+ranges), blend fwd, blend bwd, preprocess bwd, pose fwd, pose bwd of the LAST call
  * (-1 where no stage was recorded).  Synchronises on the recorded events. */
 int gs_profile_read(float* ms_host) {
   for (int i = 0; i < ST_COUNT; i++) {

@@ -92,9 +92,8 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       mask &= mask - 1;
       // reference test sequence, forward.cu:325-361, in the reference's FP32 operation order
       const float dx = __fsub_rn(sl.x[j], pfx), dy = __fsub_rn(sl.y[j], pfy);
-      const float power = __fsub_rn(
-          __fmul_rn(__fmaf_rn(dx, __fmul_rn(dx, sl.ca[j]), __fmul_rn(dy, __fmul_rn(dy, sl.cc[j]))), -0.5f),
-          __fmul_rn(dy, __fmul_rn(dx, sl.cb[j])));
+      const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, sl.ca[j]), __fmul_rn(dy, __fmul_rn(dy, sl.cc[j]))), -0.5f,
+                                    -__fmul_rn(dy, __fmul_rn(dx, sl.cb[j])));  // SASS: FFMA q*-0.5 - cross
       const float alpha = fminf(0.99f, __fmul_rn(sl.o[j], gs_exp(power)));
       bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
       const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
@@ -200,8 +199,8 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       const int epos = b * 32 + j;
       const float cx = sl.ca[j], cy = sl.cb[j], cz = sl.cc[j], o = sl.o[j];
       const float dx = __fsub_rn(sl.x[j], pfx), dy = __fsub_rn(sl.y[j], pfy);
-      const float power = __fsub_rn(__fmul_rn(__fmaf_rn(dx, __fmul_rn(dx, cx), __fmul_rn(dy, __fmul_rn(dy, cz))), -0.5f),
-                                    __fmul_rn(dy, __fmul_rn(dx, cy)));
+      const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, cx), __fmul_rn(dy, __fmul_rn(dy, cz))), -0.5f,
+                                    -__fmul_rn(dy, __fmul_rn(dx, cy)));
       const float G = gs_exp(power);
       const float alpha = fminf(0.99f, __fmul_rn(o, G));
       const bool ok = (epos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);

@@ -163,3 +163,4 @@ int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage&
 int gs_launch_preprocess_bwd(const GsBackwardArgs& a, const GsGeom& g, cudaStream_t st);
 int gs_launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 int gs_check(cudaError_t e);
+void gs_prof_mark(int stage, int end, cudaStream_t st);  // stages: see gs_api.cu (5 = pose fwd, 6 = pose bwd)

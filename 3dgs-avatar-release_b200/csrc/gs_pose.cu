@@ -305,7 +305,9 @@ extern "C" int pose_forward(const PoseArgs* args, void* stream) {
   if (args->P == 0) return GS_OK;
   int blocks = (args->P + 127) / 128;
   if (blocks > 148 * 16) blocks = 148 * 16;
+  gs_prof_mark(5, 0, (cudaStream_t)stream);
   pose_fwd_kernel<<<blocks, 128, 0, (cudaStream_t)stream>>>(*args);
+  gs_prof_mark(5, 1, (cudaStream_t)stream);
   return gs_check(cudaGetLastError());
 }
 
@@ -317,6 +319,8 @@ extern "C" int pose_backward(const PoseBackwardArgs* args, void* stream) {
   if (args->fwd.P == 0) return GS_OK;
   int blocks = (args->fwd.P + 127) / 128;
   if (blocks > 148 * 16) blocks = 148 * 16;
+  gs_prof_mark(6, 0, (cudaStream_t)stream);
   pose_bwd_kernel<<<blocks, 128, 0, (cudaStream_t)stream>>>(*args);
+  gs_prof_mark(6, 1, (cudaStream_t)stream);
   return gs_check(cudaGetLastError());
 }

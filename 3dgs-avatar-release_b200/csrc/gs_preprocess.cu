@@ -22,16 +22,16 @@ __device__ __forceinline__ void cov3d_from_scale_rot(const float* __restrict__ s
   // forward.cu:118-152; contraction pattern of the reference PTX (see oracle/gs_oracle.c)
   float sx = __fmul_rn(mod, s3[0]), sy = __fmul_rn(mod, s3[1]), sz = __fmul_rn(mod, s3[2]);
   float r = q4[0], x = q4[1], y = q4[2], z = q4[3];
-  float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z), xy = __fmul_rn(x, y), rz = __fmul_rn(r, z);
-  float xz = __fmul_rn(x, z), ry = __fmul_rn(r, y), yz = __fmul_rn(y, z), rx = __fmul_rn(r, x);
+  // fusion pattern of the reference SASS (sm_100): xy-rz = fma(x,y,-rz), ry+xz = fma(r,y,xz), xz-ry = fma(-r,y,xz) ...
+  float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z), xz = __fmul_rn(x, z), rx = __fmul_rn(r, x), rz = __fmul_rn(r, z);
   float a = __fsub_rn(1.f, __fmul_rn(2.f, __fadd_rn(yy, zz)));
-  float b = __fmul_rn(2.f, __fsub_rn(xy, rz));
-  float c = __fmul_rn(2.f, __fadd_rn(ry, xz));
-  float d = __fmul_rn(2.f, __fadd_rn(xy, rz));
+  float b = __fmul_rn(2.f, __fmaf_rn(x, y, -rz));
+  float c = __fmul_rn(2.f, __fmaf_rn(r, y, xz));
+  float d = __fmul_rn(2.f, __fmaf_rn(x, y, rz));
   float e = __fsub_rn(1.f, __fmul_rn(2.f, __fmaf_rn(x, x, zz)));
-  float f = __fmul_rn(2.f, __fsub_rn(yz, rx));
-  float g = __fmul_rn(2.f, __fsub_rn(xz, ry));
-  float h = __fmul_rn(2.f, __fadd_rn(rx, yz));
+  float f = __fmul_rn(2.f, __fmaf_rn(y, z, -rx));
+  float g = __fmul_rn(2.f, __fmaf_rn(-r, y, xz));
+  float h = __fmul_rn(2.f, __fmaf_rn(y, z, rx));
   float i = __fsub_rn(1.f, __fmul_rn(2.f, __fmaf_rn(x, x, yy)));
   float M00 = __fmul_rn(sx, a), M01 = __fmul_rn(sy, b), M02 = __fmul_rn(sz, c);
   float M10 = __fmul_rn(sx, d), M11 = __fmul_rn(sy, e), M12 = __fmul_rn(sz, f);
@@ -175,12 +175,12 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsForwardArgs a, GsGeom
       float cov_a = __fadd_rn(gs_dot3(T0[0], a0, T0[1], a1, T0[2], a2), 0.3f);
       float cov_b = gs_dot3(T0[0], b0, T0[1], b1, T0[2], b2);
       float cov_c = __fadd_rn(gs_dot3(T1[0], b0, T1[1], b1, T1[2], b2), 0.3f);
-      float det = __fsub_rn(__fmul_rn(cov_a, cov_c), __fmul_rn(cov_b, cov_b));
+      float det = __fmaf_rn(cov_a, cov_c, -__fmul_rn(cov_b, cov_b));  // SASS: FFMA a*c - (b*b)
       if (det != 0.0f) {
         float det_inv = __frcp_rn(det);
         float con_a = __fmul_rn(cov_c, det_inv), con_b = __fmul_rn(-cov_b, det_inv), con_c = __fmul_rn(cov_a, det_inv);
         float mid = __fmul_rn(__fadd_rn(cov_a, cov_c), 0.5f);
-        float sq = __fsqrt_rn(fmaxf(__fsub_rn(__fmul_rn(mid, mid), det), 0.1f));
+        float sq = __fsqrt_rn(fmaxf(__fmaf_rn(mid, mid, -det), 0.1f));
         float lam = fmaxf(__fadd_rn(mid, sq), __fsub_rn(mid, sq));
         float my_radius = ceilf(__fmul_rn(__fsqrt_rn(lam), 3.f));
         float px = ndc2pix(projx, W), py = ndc2pix(projy, H);

@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--height", type=int, default=H_DEFAULT)
     ap.add_argument("--cpu-steps", type=int, default=3, help="steps of the cpu_baseline sample inside the ours arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-only", action="store_true", help="run warmup+steps training steps and exit (for ncu)")
     return ap.parse_args()
 
 
@@ -203,38 +204,16 @@ def stage_times(hp, f, reps, dev):
     L.gs_profile_enable.argtypes = [ctypes.c_int]
     L.gs_profile_read.argtypes = [ctypes.c_void_p]
     L.gs_profile_enable(1)
-    acc = np.zeros(5)
-    buf = (ctypes.c_float * 5)()
-    pose_f = pose_b = 0.0
-    from avatar_pose import _FusedPose
+    acc = np.zeros(7)
+    buf = (ctypes.c_float * 7)()
     for _ in range(reps):
         hp.train_step(f)
         torch.cuda.synchronize(dev)
         L.gs_profile_read(ctypes.cast(buf, ctypes.c_void_p))
         acc += np.array(list(buf))
     L.gs_profile_enable(0)
-    # pose kernels: events around the autograd op (forward) and around its backward
-    p = hp.params
-    for _ in range(reps):
-        s0, s1, s2, s3 = (torch.cuda.Event(enable_timing=True) for _ in range(4))
-        s0.record()
-        out = hp.fused_pose(p["xyz"], p["rotation"], p["scaling"], p["opacity"], p["features_dc"], p["features_rest"],
-                            hp.weights, f["bones"], f["campos"], 3)
-        s1.record()
-        gr = [torch.ones_like(o) for o in out]
-        torch.cuda.synchronize(dev)
-        s2.record()
-        torch.autograd.backward(out, gr)
-        s3.record()
-        torch.cuda.synchronize(dev)
-        pose_f += s0.elapsed_time(s1)
-        pose_b += s2.elapsed_time(s3)
-        for v in p.values():
-            v.grad = None
-    names = ["preprocess_fwd", "binning", "blend_fwd", "blend_bwd", "preprocess_bwd"]
-    d = {n: acc[i] / reps for i, n in enumerate(names)}
-    d["pose_fwd"], d["pose_bwd"] = pose_f / reps, pose_b / reps
-    return d
+    names = ["preprocess_fwd", "binning", "blend_fwd", "blend_bwd", "preprocess_bwd", "pose_fwd", "pose_bwd"]
+    return {n: acc[i] / reps for i, n in enumerate(names)}
 
 
 # --------------------------------------------------------------------------------------------------------------
@@ -424,6 +403,12 @@ def ours_main(args):
             dist.all_reduce(tot, op=dist.ReduceOp.MAX)
         return float(tot.item()) / steps, ts
 
+    if args.profile_only:
+        for _ in range(args.warmup + args.steps):
+            train_resident()
+        torch.cuda.synchronize(dev)
+        print(json.dumps({"profile_only": True, "steps": args.warmup + args.steps}))
+        return
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()

@@ -179,7 +179,7 @@ int pose_backward(const PoseBackwardArgs* args, void* stream);
 /* Bench support (no reference counterpart): per-stage CUDA-event timing of the last forward/backward call, and an
  * FP32 FMA throughput probe (8 independent FMA chains per thread, `iters` rounds: 16*iters flop per thread). */
 void gs_profile_enable(int on);
-int gs_profile_read(float* ms_host /* [5]: preprocess, binning, blend fwd, blend bwd, preprocess bwd */);
+int gs_profile_read(float* ms_host /* [7]: preprocess, binning, blend fwd, blend bwd, preprocess bwd, pose fwd, pose bwd */);
 int gs_fma_probe(int blocks, int threads, int iters, float* out_dev, void* stream);
 
 int gs_last_cuda_error(void);

@@ -73,8 +73,8 @@ def lbs(xyz, rotation, pts_W, bone_transforms):
     :215-236 (SkinningField.forward after get_forward_transform).
     Returns T_fwd [P,4,4], x_bar [P,3], rotation_bar [P,3,3]."""
     n_pts = xyz.shape[0]
-    T_fwd = torch.matmul(pts_W, bone_transforms.view(-1, 16)).view(n_pts, 4, 4).float()
-    homo = torch.ones(n_pts, 1, dtype=torch.float32, device=xyz.device)
+    T_fwd = torch.matmul(pts_W, bone_transforms.view(-1, 16)).view(n_pts, 4, 4).to(xyz.dtype)  # .float() in the reference
+    homo = torch.ones(n_pts, 1, dtype=xyz.dtype, device=xyz.device)
     x_hat_homo = torch.cat([xyz, homo], dim=-1).view(n_pts, 4, 1)
     x_bar = torch.matmul(T_fwd, x_hat_homo)[:, :3, 0]
     rotation_hat = build_rotation(rotation)
