@@ -53,9 +53,20 @@ def build_rotation(r):
     return R
 
 
-def quaternion_multiply(r, s):
-    """utils/general_utils.py:184-192 (Hamilton product; pytorch3d's variant only adds a sign flip that
-    build_rotation is invariant to)."""
+def quaternion_multiply(a, b):
+    """Hamilton product a (x) b, real part first: what pytorch3d.transforms.quaternion_multiply computes
+    (models/deformer/non_rigid.py:114,281; pytorch3d 0.7.1 is not vendored -- its sign standardisation to a
+    non-negative real part is omitted because build_rotation is invariant to it).  R(a (x) b) = R(a) R(b)."""
+    aw, ax, ay, az = a.unbind(-1)
+    bw, bx, by, bz = b.unbind(-1)
+    return torch.stack([aw * bw - ax * bx - ay * by - az * bz, aw * bx + ax * bw + ay * bz - az * by,
+                        aw * by - ax * bz + ay * bw + az * bx, aw * bz + ax * by - ay * bx + az * bw], dim=-1)
+
+
+def quaternion_multiply_general_utils(r, s):
+    """utils/general_utils.py:184-192 restated as written: the cross-product part has the opposite sign of the Hamilton
+    product, i.e. it returns s (x) r.  Not on the hot path (non_rigid.py:281 uses pytorch3d's; the MLP variant :185
+    uses this one); kept for reference."""
     r0, r1, r2, r3 = r.unbind(-1)
     s0, s1, s2, s3 = s.unbind(-1)
     return torch.stack([r0 * s0 - r1 * s1 - r2 * s2 - r3 * s3, r0 * s1 + r1 * s0 - r2 * s3 + r3 * s2,
