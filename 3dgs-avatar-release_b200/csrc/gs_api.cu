@@ -47,7 +47,19 @@ const char* gs_version(void) { return "gsplat_b200 0.1 (sm_100a)"; }
 
 size_t gs_geom_bytes(int32_t P) { return gs_carve_geom(nullptr, P, nullptr); }
 size_t gs_image_bytes(int32_t width, int32_t height) { return gs_carve_image(nullptr, width, height, nullptr); }
-size_t gs_list_bytes(int64_t pair_capacity) { return gs_align_up((size_t)(pair_capacity > 0 ? pair_capacity : 1) * 4); }
+size_t gs_list_bytes(int64_t pair_capacity, int32_t width, int32_t height) {
+  return gs_carve_list(nullptr, pair_capacity > 0 ? pair_capacity : 1, width, height, nullptr);
+}
+/* Largest pair capacity (a multiple of 4096) whose list workspace fits list_bytes: inverse of gs_list_bytes on that
+ * lattice, where it is strictly increasing.  Lets a caller that only kept the buffer recover the capacity. */
+int64_t gs_list_capacity(size_t list_bytes, int32_t width, int32_t height) {
+  int64_t lo = 0, hi = (int64_t)(list_bytes / 4 / 4096) + 1;  // in units of 4096 pairs
+  while (lo < hi) {
+    int64_t mid = (lo + hi + 1) / 2;
+    if (gs_carve_list(nullptr, mid * 4096, width, height, nullptr) <= list_bytes) lo = mid; else hi = mid - 1;
+  }
+  return lo * 4096;
+}
 size_t gs_scratch_bytes(int32_t P, int32_t width, int32_t height, int64_t pair_capacity) {
   return gs_carve_scratch(nullptr, P, width, height, pair_capacity > 0 ? pair_capacity : 1, nullptr);
 }
@@ -71,7 +83,8 @@ int gs_forward(const GsForwardArgs* args, void* geom, size_t geom_bytes, void* i
   if (gs_carve_image((char*)image, a.width, a.height, &im) > image_bytes) return GS_ERR_WORKSPACE_SMALL;
   if (gs_carve_scratch((char*)scratch, a.P, a.width, a.height, pair_capacity, &s) > scratch_bytes)
     return GS_ERR_WORKSPACE_SMALL;
-  if (gs_list_bytes(pair_capacity) > list_bytes) return GS_ERR_WORKSPACE_SMALL;
+  GsList l;
+  if (gs_carve_list((char*)list, pair_capacity, a.width, a.height, &l) > list_bytes) return GS_ERR_WORKSPACE_SMALL;
 
   const size_t tiles = (size_t)((a.width + GS_TILE - 1) / GS_TILE) * ((a.height + GS_TILE - 1) / GS_TILE);
   GS_TRY(gs_check(cudaMemsetAsync(g.hdr, 0, sizeof(GsHeader), st)));
@@ -83,14 +96,14 @@ int gs_forward(const GsForwardArgs* args, void* geom, size_t geom_bytes, void* i
   gs_prof_mark(ST_PRE, 1, st);
   GS_TRY(debug_sync(a.debug, st));
   gs_prof_mark(ST_BIN, 0, st);
-  GS_TRY(gs_launch_binning(a, g, im, s, (uint32_t*)list, pair_capacity, st));
+  GS_TRY(gs_launch_binning(a, g, im, s, l, pair_capacity, st));
   gs_prof_mark(ST_BIN, 1, st);
   GS_TRY(debug_sync(a.debug, st));
   if (num_rendered_pinned_host)
     GS_TRY(gs_check(cudaMemcpyAsync(num_rendered_pinned_host, &g.hdr->num_rendered, 2 * sizeof(int64_t),
                                     cudaMemcpyDeviceToHost, st)));
   gs_prof_mark(ST_BLEND_F, 0, st);
-  GS_TRY(gs_launch_blend_fwd(a, g, im, (const uint32_t*)list, st));
+  GS_TRY(gs_launch_blend_fwd(a, g, im, l, st));
   gs_prof_mark(ST_BLEND_F, 1, st);
   GS_TRY(debug_sync(a.debug, st));
   return GS_OK;
@@ -108,9 +121,8 @@ int gs_read_num_rendered(const void* geom, int64_t* num_rendered_host, void* str
 }
 
 int gs_backward(const GsBackwardArgs* args, const void* geom, size_t geom_bytes, const void* image, size_t image_bytes,
-                const void* list, size_t list_bytes, void* stream) {
-  if (!args || !geom || !image || !list) return GS_ERR_BAD_ARG;
-  (void)list_bytes;
+                const void* list, size_t list_bytes, int64_t pair_capacity, void* stream) {
+  if (!args || !geom || !image || !list || pair_capacity <= 0) return GS_ERR_BAD_ARG;
   const GsBackwardArgs& a = *args;
   cudaStream_t st = (cudaStream_t)stream;
   if (a.P <= 0) return GS_ERR_BAD_ARG;
@@ -122,8 +134,10 @@ int gs_backward(const GsBackwardArgs* args, const void* geom, size_t geom_bytes,
   GsImage im;
   if (gs_carve_geom((char*)geom, a.P, &g) > geom_bytes) return GS_ERR_WORKSPACE_SMALL;
   if (gs_carve_image((char*)image, a.width, a.height, &im) > image_bytes) return GS_ERR_WORKSPACE_SMALL;
+  GsList l;
+  if (gs_carve_list((char*)list, pair_capacity, a.width, a.height, &l) > list_bytes) return GS_ERR_WORKSPACE_SMALL;
   gs_prof_mark(ST_BLEND_B, 0, st);
-  GS_TRY(gs_launch_blend_bwd(a, g, im, (const uint32_t*)list, st));
+  GS_TRY(gs_launch_blend_bwd(a, g, im, l, st));
   gs_prof_mark(ST_BLEND_B, 1, st);
   GS_TRY(debug_sync(a.debug, st));
   gs_prof_mark(ST_PRE_B, 0, st);

@@ -23,8 +23,10 @@ namespace {
 
 constexpr int kWarps = 8;
 
-struct Slab {  // per-warp staging of 32 list entries (SoA -> conflict-free lane-parallel stores, broadcast loads)
-  float x[32], y[32], ca[32], cb[32], cc[32], o[32], r[32], g[32], b[32];
+struct Slab {  // per-warp staging of 32 list entries: 2 x LDS.128 + 1 x LDS.32 broadcast reads per evaluated entry
+  float4 q0[32];  // x, y, conic a, conic b
+  float4 q1[32];  // conic c, opacity, r, g
+  float q2[32];   // b
   uint32_t id[32];
 };
 
@@ -54,15 +56,29 @@ __device__ __forceinline__ bool may_contribute(float x, float y, float ca, float
   return !(0.5f * m > tau + 0.01f);
 }
 
+// Gathers the 48-byte record of one list entry (3 x LDG.128).
+struct Rec3 { float4 a, b, c; };
+__device__ __forceinline__ Rec3 load_rec(const GsRec* __restrict__ rec, uint32_t id) {
+  const float4* rp = reinterpret_cast<const float4*>(rec + id);
+  Rec3 r;
+  r.a = __ldg(rp); r.b = __ldg(rp + 1); r.c = __ldg(rp + 2);
+  return r;
+}
+
+constexpr int kChunk = 4;  // survivors evaluated together: their exp() chains are independent (ILP), only the T update is serial
+
 __global__ void __launch_bounds__(kWarps * 32)
 blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H,
                  const GsRec* __restrict__ rec, const float* __restrict__ bg, float* __restrict__ final_T,
-                 uint32_t* __restrict__ n_contrib, float* __restrict__ out_color) {
+                 uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
+                 const uint32_t* __restrict__ seg_off, float4* __restrict__ ckpt) {
   __shared__ Slab s_slab[kWarps];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   Slab& sl = s_slab[w];
   const int tile = blockIdx.y * gridDim.x + blockIdx.x;
   const uint2 range = ranges[tile];
+  // checkpoint slots of this tile: one per segment start + one final (backward work items restart from them)
+  float4* const ck = ckpt + ((size_t)seg_off[tile] + tile) * 256 + threadIdx.x;
   const int bx = blockIdx.x * GS_TILE + (w & 1) * 8, by = blockIdx.y * GS_TILE + (w >> 1) * 4;
   const int px = bx + (lane & 7), py = by + (lane >> 3);
   const bool inside = px < W && py < H;
@@ -72,43 +88,72 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
   uint32_t last = 0;
 
+  // software pipeline: records of batch b and list indices of batch b+1 are in registers when batch b is processed
+  Rec3 cur;
+  cur.a = cur.b = cur.c = make_float4(0.f, 0.f, 0.f, 0.f);
+  uint32_t id_next = 0;
+  {
+    const uint32_t e = range.x + lane;
+    if (e < range.y) cur = load_rec(rec, list[e]);
+    if (e + 32 < range.y) id_next = list[e + 32];
+  }
   for (uint32_t base = range.x; base < range.y; base += 32) {
     if (__all_sync(0xFFFFFFFFu, done)) break;
     const uint32_t e = base + lane;
+    if (((base - range.x) & (GS_SEG - 1)) == 0) ck[(size_t)((base - range.x) / GS_SEG) * 256] = make_float4(T, C0, C1, C2);
     bool keep = false;
     if (e < range.y) {
-      const uint32_t id = list[e];
-      const float4* rp = reinterpret_cast<const float4*>(rec + id);
-      const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1), r2 = __ldg(rp + 2);
-      keep = may_contribute(r0.x, r0.y, r1.x, r1.y, r1.z, r0.z, X0, X1, Y0, Y1);
-      sl.x[lane] = r0.x; sl.y[lane] = r0.y;
-      sl.ca[lane] = r1.x; sl.cb[lane] = r1.y; sl.cc[lane] = r1.z; sl.o[lane] = r1.w;
-      sl.r[lane] = r2.x; sl.g[lane] = r2.y; sl.b[lane] = r2.z;
+      keep = may_contribute(cur.a.x, cur.a.y, cur.b.x, cur.b.y, cur.b.z, cur.a.z, X0, X1, Y0, Y1);
+      sl.q0[lane] = make_float4(cur.a.x, cur.a.y, cur.b.x, cur.b.y);
+      sl.q1[lane] = make_float4(cur.b.z, cur.b.w, cur.c.x, cur.c.y);
+      sl.q2[lane] = cur.c.z;
     }
+    // prefetch: records of the next batch, indices of the one after
+    Rec3 nxt = cur;
+    if (e + 32 < range.y) nxt = load_rec(rec, id_next);
+    uint32_t id_nn = 0;
+    if (e + 64 < range.y) id_nn = list[e + 64];
     __syncwarp();
     uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
     while (mask) {
-      const int j = __ffs(mask) - 1;
-      mask &= mask - 1;
-      // reference test sequence, forward.cu:325-361, in the reference's FP32 operation order
-      const float dx = __fsub_rn(sl.x[j], pfx), dy = __fsub_rn(sl.y[j], pfy);
-      const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, sl.ca[j]), __fmul_rn(dy, __fmul_rn(dy, sl.cc[j]))), -0.5f,
-                                    -__fmul_rn(dy, __fmul_rn(dx, sl.cb[j])));  // SASS: FFMA q*-0.5 - cross
-      const float alpha = fminf(0.99f, __fmul_rn(sl.o[j], gs_exp(power)));
-      bool ok = !done && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-      const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-      if (ok && test_T < 0.0001f) { done = true; ok = false; }
-      if (ok) {
-        C0 = __fmaf_rn(T, __fmul_rn(alpha, sl.r[j]), C0);
-        C1 = __fmaf_rn(T, __fmul_rn(alpha, sl.g[j]), C1);
-        C2 = __fmaf_rn(T, __fmul_rn(alpha, sl.b[j]), C2);
-        T = test_T;
-        last = base + j - range.x + 1;  // 1-based position in the tile list (contributor, forward.cu:328)
+      float al[kChunk], cr[kChunk], cg[kChunk], cb_[kChunk];
+      bool okk[kChunk];
+      int jj[kChunk];
+#pragma unroll
+      for (int k = 0; k < kChunk; k++) {
+        const bool valid = mask != 0;
+        const int j = valid ? (__ffs(mask) - 1) : 0;
+        mask &= mask - 1;  // 0 stays 0
+        jj[k] = j;
+        const float4 q0 = sl.q0[j], q1 = sl.q1[j];
+        // reference test sequence, forward.cu:325-361, in the reference's FP32 operation order
+        const float dx = __fsub_rn(q0.x, pfx), dy = __fsub_rn(q0.y, pfy);
+        const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x))), -0.5f,
+                                      -__fmul_rn(dy, __fmul_rn(dx, q0.w)));  // SASS: FFMA q*-0.5 - cross
+        const float alpha = fminf(0.99f, __fmul_rn(q1.y, gs_exp(power)));
+        al[k] = alpha; cr[k] = q1.z; cg[k] = q1.w; cb_[k] = sl.q2[j];
+        okk[k] = valid && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
       }
-      if (__all_sync(0xFFFFFFFFu, done)) { mask = 0; }
+#pragma unroll
+      for (int k = 0; k < kChunk; k++) {
+        bool ok = okk[k] && !done;
+        const float test_T = __fmul_rn(T, __fsub_rn(1.0f, al[k]));
+        if (ok && test_T < 0.0001f) { done = true; ok = false; }
+        if (ok) {
+          C0 = __fmaf_rn(T, __fmul_rn(al[k], cr[k]), C0);
+          C1 = __fmaf_rn(T, __fmul_rn(al[k], cg[k]), C1);
+          C2 = __fmaf_rn(T, __fmul_rn(al[k], cb_[k]), C2);
+          T = test_T;
+          last = base + jj[k] - range.x + 1;  // 1-based position in the tile list (contributor, forward.cu:328)
+        }
+      }
+      if (__all_sync(0xFFFFFFFFu, done)) mask = 0;
     }
     __syncwarp();
+    cur = nxt;
+    id_next = id_nn;
   }
+  ck[(size_t)((range.y - range.x + GS_SEG - 1) / GS_SEG) * 256] = make_float4(T, C0, C1, C2);
   if (inside) {
     const size_t pix = (size_t)py * W + px, hw = (size_t)H * W;
     final_T[pix] = T;
@@ -119,159 +164,203 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   }
 }
 
-// Sum v[0..7] over the 32 lanes with a transposing butterfly: afterwards lane 4*k (k = 0..7) holds the warp total of
-// v[k].  7 + 2 = 9 shuffles instead of 40.
-__device__ __forceinline__ float warp_reduce8(float (&v)[8], int lane) {
-  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
-  float a[4];
+// Transposing butterfly step: N values per lane -> N/2, exchanging with lane ^ XOR.  After the steps for XOR = 16, 8, 4, 2, 1
+// on 32 values, lane L holds the warp total of value L: 31 shuffles for 32 sums instead of 160.
+template <int N, int XOR>
+__device__ __forceinline__ void xpose_step(float* v, int lane) {
+  const bool up = lane & XOR;
 #pragma unroll
-  for (int k = 0; k < 4; k++) {
-    float send = b4 ? v[k] : v[4 + k];
-    float keepv = b4 ? v[4 + k] : v[k];
-    a[k] = keepv + __shfl_xor_sync(0xFFFFFFFFu, send, 16);
+  for (int k = 0; k < N / 2; k++) {
+    const float send = up ? v[k] : v[k + N / 2];
+    const float keepv = up ? v[k + N / 2] : v[k];
+    v[k] = keepv + __shfl_xor_sync(0xFFFFFFFFu, send, XOR);
   }
-  float c[2];
-#pragma unroll
-  for (int k = 0; k < 2; k++) {
-    float send = b3 ? a[k] : a[2 + k];
-    float keepv = b3 ? a[2 + k] : a[k];
-    c[k] = keepv + __shfl_xor_sync(0xFFFFFFFFu, send, 8);
-  }
-  float send = b2 ? c[0] : c[1];
-  float keepv = b2 ? c[1] : c[0];
-  float r = keepv + __shfl_xor_sync(0xFFFFFFFFu, send, 4);
-  r += __shfl_xor_sync(0xFFFFFFFFu, r, 2);
-  r += __shfl_xor_sync(0xFFFFFFFFu, r, 1);
-  return r;  // valid in lanes with (lane & 3) == 0: value index = (b4?4:0) + (b3?2:0) + (b2?1:0)
 }
 
+// One CTA per work item = (tile, segment of GS_SEG list entries), 8 warps = the tile's eight 8x4 pixel blocks.  A pixel
+// whose last contributor lies behind the segment restarts from the forward's checkpoint at the segment end:
+// T = T(seg end), accumulated colour behind it = (C_final - C(seg end)) / T(seg end); inside the segment the recurrences
+// are the reference's (backward.cu:497-534).  Deep tile lists thus spread over many SMs instead of one.
 __global__ void __launch_bounds__(kWarps * 32)
-blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H,
+blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H, int grid_x,
+                 const uint32_t* __restrict__ seg_off, int tiles, const uint2* __restrict__ items,
+                 const float4* __restrict__ ckpt,
                  const float* __restrict__ bg, const GsRec* __restrict__ rec, const float* __restrict__ final_Ts,
                  const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
                  float* __restrict__ dL_dmean2D /*[P,3]*/, float* __restrict__ dL_dconic /*[P,4]*/,
                  float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors) {
   __shared__ Slab s_slab[kWarps];
+  if (blockIdx.x >= seg_off[tiles]) return;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   Slab& sl = s_slab[w];
-  const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+  const uint2 item = items[blockIdx.x];
+  const int tile = (int)item.x;
   const uint2 range = ranges[tile];
-  if (range.y <= range.x) return;
-  const int bx = blockIdx.x * GS_TILE + (w & 1) * 8, by = blockIdx.y * GS_TILE + (w >> 1) * 4;
+  const int len = (int)(range.y - range.x);
+  const int seg_begin = (int)item.y * GS_SEG, seg_end = min(len, seg_begin + GS_SEG);
+  const int tx = tile % grid_x, ty = tile / grid_x;
+  const int bx = tx * GS_TILE + (w & 1) * 8, by = ty * GS_TILE + (w >> 1) * 4;
   const int px = bx + (lane & 7), py = by + (lane >> 3);
   const bool inside = px < W && py < H;
   const float pfx = (float)px, pfy = (float)py;
   const float X0 = (float)bx, X1 = (float)(bx + 7), Y0 = (float)by, Y1 = (float)(by + 3);
   const size_t pix = (size_t)py * W + px, hw = (size_t)H * W;
+  const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+  const int hi = min(last_contributor, seg_end);  // this pixel owns list positions [seg_begin, hi)
+  // entries at positions >= max(hi) over the warp are never touched
+  int wmax = hi;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xFFFFFFFFu, wmax, o));
+  if (wmax <= seg_begin) return;
   const float T_final = inside ? final_Ts[pix] : 0.f;
   float T = T_final;
-  const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+  float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_alpha = 0.f;
+  if (last_contributor > seg_end) {  // restart from the checkpoint at the segment end
+    const float4* ck = ckpt + ((size_t)seg_off[tile] + tile) * 256 + threadIdx.x;
+    const float4 c = ck[(size_t)(item.y + 1) * 256];
+    const float4 cf = ck[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256];
+    T = c.x;
+    const float rT = 1.f / T;
+    acc0 = (cf.y - c.y) * rT; acc1 = (cf.z - c.z) * rT; acc2 = (cf.w - c.w) * rT;
+  }
   float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
   if (inside) { dp0 = dL_dpixels[pix]; dp1 = dL_dpixels[hw + pix]; dp2 = dL_dpixels[2 * hw + pix]; }
   const float bg_dot_dpixel = bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2;
-  float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_alpha = 0.f;
+  const float nTfbg = -T_final * bg_dot_dpixel;
   const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:460-461
+  // which accumulator this lane feeds after the transposing reduction: entry (lane >> 3) of the chunk, component lane & 7
+  const int comp = lane & 7;
+  float* const comp_base = comp < 2 ? dL_dmean2D + comp : comp < 5 ? dL_dconic + (comp == 4 ? 3 : comp - 2)
+                                    : comp == 5 ? dL_dopacity : dL_dcolors + (comp - 6);
+  const int comp_stride = comp < 2 ? 3 : comp < 5 ? 4 : comp == 5 ? 1 : 3;
 
-  // entries at 0-based positions >= max(last_contributor) over the warp are never touched
-  int wmax = last_contributor;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xFFFFFFFFu, wmax, o));
-  if (wmax == 0) return;
-  // batches aligned to the start of the range so that positions map to lanes: pos = b*32 + lane
-  for (int b = (wmax - 1) >> 5; b >= 0; b--) {
+  // batches aligned to the start of the range so that positions map to lanes: pos = b*32 + lane; software pipeline as
+  // in the forward kernel (records of batch b and indices of batch b-1 in registers while batch b is processed)
+  const uint32_t* const seg_list = list + range.x + seg_begin;
+  wmax -= seg_begin;  // positions below are relative to the segment start (a multiple of 32)
+  const int hi_rel = hi - seg_begin;
+  int b = (wmax - 1) >> 5;
+  Rec3 cur;
+  cur.a = cur.b = cur.c = make_float4(0.f, 0.f, 0.f, 0.f);
+  uint32_t id_cur = 0, id_next = 0;
+  {
+    const int pos = b * 32 + lane;
+    if (pos < wmax) { id_cur = seg_list[pos]; cur = load_rec(rec, id_cur); }
+    if (b > 0) id_next = seg_list[pos - 32];
+  }
+  for (; b >= 0; b--) {
     const int pos = b * 32 + lane;
     bool keep = false;
     if (pos < wmax) {
-      const uint32_t id = list[range.x + pos];
-      const float4* rp = reinterpret_cast<const float4*>(rec + id);
-      const float4 r0 = __ldg(rp), r1 = __ldg(rp + 1), r2 = __ldg(rp + 2);
-      keep = may_contribute(r0.x, r0.y, r1.x, r1.y, r1.z, r0.z, X0, X1, Y0, Y1);
-      sl.x[lane] = r0.x; sl.y[lane] = r0.y;
-      sl.ca[lane] = r1.x; sl.cb[lane] = r1.y; sl.cc[lane] = r1.z; sl.o[lane] = r1.w;
-      sl.r[lane] = r2.x; sl.g[lane] = r2.y; sl.b[lane] = r2.z;
-      sl.id[lane] = id;
+      keep = may_contribute(cur.a.x, cur.a.y, cur.b.x, cur.b.y, cur.b.z, cur.a.z, X0, X1, Y0, Y1);
+      sl.q0[lane] = make_float4(cur.a.x, cur.a.y, cur.b.x, cur.b.y);
+      sl.q1[lane] = make_float4(cur.b.z, cur.b.w, cur.c.x, cur.c.y);
+      sl.q2[lane] = cur.c.z;
+      sl.id[lane] = id_cur;
     }
+    Rec3 nxt = cur;
+    if (b > 0) nxt = load_rec(rec, id_next);
+    uint32_t id_nn = 0;
+    if (b > 1) id_nn = seg_list[pos - 64];
     __syncwarp();
     uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
     while (mask) {
-      const int j = 31 - __clz(mask);  // back to front
-      mask &= ~(1u << j);
-      const int epos = b * 32 + j;
-      const float cx = sl.ca[j], cy = sl.cb[j], cz = sl.cc[j], o = sl.o[j];
-      const float dx = __fsub_rn(sl.x[j], pfx), dy = __fsub_rn(sl.y[j], pfy);
-      const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, cx), __fmul_rn(dy, __fmul_rn(dy, cz))), -0.5f,
-                                    -__fmul_rn(dy, __fmul_rn(dx, cy)));
-      const float G = gs_exp(power);
-      const float alpha = fminf(0.99f, __fmul_rn(o, G));
-      const bool ok = (epos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-      if (!__any_sync(0xFFFFFFFFu, ok)) continue;
-      float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, v8 = 0.f;
-      if (ok) {
-        T = T / (1.f - alpha);
-        const float dchannel_dcolor = alpha * T;
-        const float c0 = sl.r[j], c1 = sl.g[j], c2 = sl.b[j];
-        acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0; lc0 = c0;
-        acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1; lc1 = c1;
-        acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2; lc2 = c2;
-        float dL_dalpha = (c0 - acc0) * dp0 + (c1 - acc1) * dp1 + (c2 - acc2) * dp2;
-        dL_dalpha *= T;
-        last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+      float v[32], v8[kChunk];
+      uint32_t ids[kChunk];
+      bool any_ok = false;
+      float G_[kChunk], al[kChunk], rinv[kChunk], dx_[kChunk], dy_[kChunk];
+      float4 Q0[kChunk], Q1[kChunk];
+      float cb2[kChunk];
+      bool okk[kChunk];
+#pragma unroll
+      for (int k = 0; k < kChunk; k++) {  // independent per-entry math (ILP)
+        const bool valid = mask != 0;
+        const int j = valid ? (31 - __clz(mask)) : 0;  // back to front
+        mask &= ~(1u << j);
+        if (!valid) mask = 0;
+        const int epos = b * 32 + j;
+        ids[k] = sl.id[j];
+        const float4 q0 = sl.q0[j], q1 = sl.q1[j];
+        Q0[k] = q0; Q1[k] = q1; cb2[k] = sl.q2[j];
+        const float dx = __fsub_rn(q0.x, pfx), dy = __fsub_rn(q0.y, pfy);
+        const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x))), -0.5f,
+                                      -__fmul_rn(dy, __fmul_rn(dx, q0.w)));
+        const float G = gs_exp(power);
+        const float alpha = fminf(0.99f, __fmul_rn(q1.y, G));
+        okk[k] = valid && (epos < hi_rel) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+        any_ok |= okk[k];
+        G_[k] = G; al[k] = alpha; dx_[k] = dx; dy_[k] = dy;
+        rinv[k] = __frcp_rn(1.f - alpha);
+      }
+      if (!__any_sync(0xFFFFFFFFu, any_ok)) continue;
+#pragma unroll
+      for (int k = 0; k < kChunk; k++) {  // serial part: transmittance / colour recurrence of backward.cu:497-534
+        float* vk = v + 8 * k;
+        const bool ok = okk[k];
+        const float cx = Q0[k].z, cy = Q0[k].w, cz = Q1[k].x, o = Q1[k].y;
+        const float c0 = Q1[k].z, c1 = Q1[k].w, c2 = cb2[k];
+        const float Tn = T * rinv[k];
+        const float a0 = last_alpha * lc0 + (1.f - last_alpha) * acc0;
+        const float a1 = last_alpha * lc1 + (1.f - last_alpha) * acc1;
+        const float a2 = last_alpha * lc2 + (1.f - last_alpha) * acc2;
+        float dL_dalpha = ((c0 - a0) * dp0 + (c1 - a1) * dp1 + (c2 - a2) * dp2) * Tn + nTfbg * rinv[k];
+        const float dchannel_dcolor = al[k] * Tn;
         const float dL_dG = o * dL_dalpha;
-        const float gdx = G * dx, gdy = G * dy;
+        const float gdx = G_[k] * dx_[k], gdy = G_[k] * dy_[k];
         const float dG_ddelx = -gdx * cx - gdy * cy;
         const float dG_ddely = -gdy * cz - gdx * cy;
-        v[0] = dL_dG * dG_ddelx * ddelx_dx;
-        v[1] = dL_dG * dG_ddely * ddely_dy;
-        v[2] = -0.5f * gdx * dx * dL_dG;
-        v[3] = -0.5f * gdx * dy * dL_dG;
-        v[4] = -0.5f * gdy * dy * dL_dG;
-        v[5] = G * dL_dalpha;
-        v[6] = dchannel_dcolor * dp0;
-        v[7] = dchannel_dcolor * dp1;
-        v8 = dchannel_dcolor * dp2;
-      }
-      const float r = warp_reduce8(v, lane);
-#pragma unroll
-      for (int o2 = 16; o2 > 0; o2 >>= 1) v8 += __shfl_xor_sync(0xFFFFFFFFu, v8, o2);
-      const uint32_t id = sl.id[j];
-      if ((lane & 3) == 0) {
-        const int k = ((lane & 16) ? 4 : 0) + ((lane & 8) ? 2 : 0) + ((lane & 4) ? 1 : 0);
-        float* dst;
-        switch (k) {
-          case 0: dst = dL_dmean2D + 3 * (size_t)id; break;
-          case 1: dst = dL_dmean2D + 3 * (size_t)id + 1; break;
-          case 2: dst = dL_dconic + 4 * (size_t)id; break;
-          case 3: dst = dL_dconic + 4 * (size_t)id + 1; break;
-          case 4: dst = dL_dconic + 4 * (size_t)id + 3; break;
-          case 5: dst = dL_dopacity + id; break;
-          case 6: dst = dL_dcolors + 3 * (size_t)id; break;
-          default: dst = dL_dcolors + 3 * (size_t)id + 1; break;
+        vk[0] = ok ? dL_dG * dG_ddelx * ddelx_dx : 0.f;
+        vk[1] = ok ? dL_dG * dG_ddely * ddely_dy : 0.f;
+        vk[2] = ok ? -0.5f * gdx * dx_[k] * dL_dG : 0.f;
+        vk[3] = ok ? -0.5f * gdx * dy_[k] * dL_dG : 0.f;
+        vk[4] = ok ? -0.5f * gdy * dy_[k] * dL_dG : 0.f;
+        vk[5] = ok ? G_[k] * dL_dalpha : 0.f;
+        vk[6] = ok ? dchannel_dcolor * dp0 : 0.f;
+        vk[7] = ok ? dchannel_dcolor * dp1 : 0.f;
+        v8[k] = ok ? dchannel_dcolor * dp2 : 0.f;
+        if (ok) {
+          T = Tn; acc0 = a0; acc1 = a1; acc2 = a2; lc0 = c0; lc1 = c1; lc2 = c2; last_alpha = al[k];
         }
-        atomicAdd(dst, r);
-      } else if (lane == 1) {
-        atomicAdd(dL_dcolors + 3 * (size_t)id + 2, v8);
       }
+      // warp reduction BEFORE the atomics: lane L ends with the total of v[L] (entry L>>3, component L&7)
+      xpose_step<32, 16>(v, lane);
+      xpose_step<16, 8>(v, lane);
+      xpose_step<8, 4>(v, lane);
+      xpose_step<4, 2>(v, lane);
+      xpose_step<2, 1>(v, lane);
+      xpose_step<4, 16>(v8, lane);
+      xpose_step<2, 8>(v8, lane);
+      float r8 = v8[0];
+      r8 += __shfl_xor_sync(0xFFFFFFFFu, r8, 4);
+      r8 += __shfl_xor_sync(0xFFFFFFFFu, r8, 2);
+      r8 += __shfl_xor_sync(0xFFFFFFFFu, r8, 1);
+      static_assert(kChunk == 4, "the reduction layout assumes 4 entries x 8 components");
+      const int ke = lane >> 3;
+      const uint32_t my_id = ke == 0 ? ids[0] : ke == 1 ? ids[1] : ke == 2 ? ids[2] : ids[3];
+      const float r = v[0];
+      if (r != 0.f) atomicAdd(comp_base + (size_t)comp_stride * my_id, r);
+      if (comp == 0 && r8 != 0.f) atomicAdd(dL_dcolors + 3 * (size_t)my_id + 2, r8);
     }
     __syncwarp();
+    cur = nxt;
+    id_cur = id_next;
+    id_next = id_nn;
   }
 }
 
 }  // namespace
 
-int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const uint32_t* list,
-                        cudaStream_t st) {
+int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st) {
   dim3 grid((a.width + GS_TILE - 1) / GS_TILE, (a.height + GS_TILE - 1) / GS_TILE);
-  blend_fwd_kernel<<<grid, kWarps * 32, 0, st>>>(im.ranges, list, a.width, a.height, g.rec, a.background, im.final_T,
-                                                 im.n_contrib, a.out_color);
+  blend_fwd_kernel<<<grid, kWarps * 32, 0, st>>>(im.ranges, l.point_list, a.width, a.height, g.rec, a.background,
+                                                 im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt);
   return gs_check(cudaGetLastError());
 }
 
-int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage& im, const uint32_t* list,
-                        cudaStream_t st) {
-  dim3 grid((a.width + GS_TILE - 1) / GS_TILE, (a.height + GS_TILE - 1) / GS_TILE);
-  blend_bwd_kernel<<<grid, kWarps * 32, 0, st>>>(im.ranges, list, a.width, a.height, a.background, g.rec, im.final_T,
-                                                 im.n_contrib, a.dL_dpix, a.dL_dmean2D, a.dL_dconic, a.dL_dopacity,
-                                                 a.dL_dcolor);
+int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st) {
+  const int gx = (a.width + GS_TILE - 1) / GS_TILE, gy = (a.height + GS_TILE - 1) / GS_TILE;
+  blend_bwd_kernel<<<(unsigned)l.max_items, kWarps * 32, 0, st>>>(
+      im.ranges, l.point_list, a.width, a.height, gx, im.seg_off, gx * gy, l.items, l.ckpt, a.background, g.rec,
+      im.final_T, im.n_contrib, a.dL_dpix, a.dL_dmean2D, a.dL_dconic, a.dL_dopacity, a.dL_dcolor);
   return gs_check(cudaGetLastError());
 }

@@ -14,6 +14,7 @@
 
 #define GS_TILE 16          // BLOCK_X = BLOCK_Y = 16 (cuda_rasterizer/config.h:16-17); defines keys/ranges/n_contrib
 #define GS_ALIGN 256
+#define GS_SEG 256          // list entries per backward work item = spacing of the forward's per-pixel checkpoints
 
 // ---- workspace layouts (private; reached from outside only through gs_debug_read) ----
 struct GsHeader {            // first 256 bytes of the geom workspace
@@ -43,6 +44,15 @@ struct GsImage {
   uint2* ranges;            // [tiles]
   uint32_t* n_contrib;      // [H*W]
   float* final_T;           // [H*W]
+  uint32_t* seg_off;        // [tiles+1] exclusive prefix of ceil(len/GS_SEG) over tiles; [tiles] = number of work items
+};
+
+// The pair-capacity-sized workspace kept for backward (the reference's binningBuffer).
+struct GsList {
+  uint32_t* point_list;     // [cap] Gaussian index per (tile, depth)-sorted pair
+  uint2* items;             // [max_items] (tile, segment) work items of the backward blend
+  float4* ckpt;             // [(max_items + tiles) * 256] per-pixel (T, C.rgb) at every segment start + final state
+  size_t max_items;
 };
 
 struct GsScratch {
@@ -89,7 +99,20 @@ static inline __host__ size_t gs_carve_image(char* base, int W, int H, GsImage* 
   gs_carve(p, t.ranges, tiles);
   gs_carve(p, t.n_contrib, (size_t)W * H);
   gs_carve(p, t.final_T, (size_t)W * H);
+  gs_carve(p, t.seg_off, tiles + 1);
   if (im) *im = t;
+  return (size_t)(p - base);
+}
+
+static inline __host__ size_t gs_carve_list(char* base, int64_t cap, int W, int H, GsList* l) {
+  char* p = base;
+  GsList t;
+  size_t tiles = (size_t)((W + GS_TILE - 1) / GS_TILE) * ((H + GS_TILE - 1) / GS_TILE);
+  t.max_items = (size_t)cap / GS_SEG + tiles;  // sum over tiles of ceil(len/GS_SEG) <= N/GS_SEG + tiles
+  gs_carve(p, t.point_list, (size_t)cap);
+  gs_carve(p, t.items, t.max_items);
+  gs_carve(p, t.ckpt, (t.max_items + tiles) * 256);
+  if (l) *l = t;
   return (size_t)(p - base);
 }
 
@@ -154,12 +177,10 @@ __device__ __forceinline__ float gs_exp(float x) {
 
 // ---- launchers (one per translation unit) ----
 int gs_launch_preprocess(const GsForwardArgs& a, const GsGeom& g, const GsScratch& s, cudaStream_t st);
-int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsScratch& s, uint32_t* list,
+int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsScratch& s, const GsList& l,
                       int64_t cap, cudaStream_t st);
-int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const uint32_t* list,
-                        cudaStream_t st);
-int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage& im, const uint32_t* list,
-                        cudaStream_t st);
+int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st);
+int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st);
 int gs_launch_preprocess_bwd(const GsBackwardArgs& a, const GsGeom& g, cudaStream_t st);
 int gs_launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 int gs_check(cudaError_t e);

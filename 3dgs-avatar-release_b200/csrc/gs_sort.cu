@@ -51,12 +51,13 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
   if (base >= n) return;
 
   // ---- load keys (warp-striped inside a warp-contiguous chunk) and rank them ----
-  uint32_t key[GS_SORT_ITEMS], rank[GS_SORT_ITEMS];
+  uint32_t key[GS_SORT_ITEMS], val[GS_SORT_ITEMS], rank[GS_SORT_ITEMS];
   const unsigned long long wbase = base + (unsigned long long)w * (32 * GS_SORT_ITEMS);
 #pragma unroll
   for (int i = 0; i < GS_SORT_ITEMS; i++) {
     unsigned long long idx = wbase + i * 32 + lane;
     key[i] = idx < n ? keys_in[idx] : 0xFFFFFFFFu;
+    val[i] = idx < n ? vals_in[idx] : 0u;  // payload loaded up front: its latency hides behind the ranking
   }
   const uint32_t lt_mask = (1u << lane) - 1u;
 #pragma unroll
@@ -128,7 +129,7 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
       uint32_t digit = (key[i] >> shift) & 255u;
       uint32_t pos = s_digit_base[digit] + s_warp_hist[w][digit] + rank[i];
       if (keys_out) keys_out[pos] = key[i];
-      vals_out[pos] = vals_in[idx];
+      vals_out[pos] = val[i];
     }
   }
 }
@@ -166,30 +167,40 @@ emit_kernel(int P, const uint32_t* __restrict__ sorted_gid, const uint32_t* __re
   unsigned long long wpre = 0, total = 0;
 #pragma unroll
   for (int k = 0; k < WARPS; k++) { unsigned long long v = s_wsum[k]; if (k < w) wpre += v; total += v; }
-  if (tid == 0) {
+  if (w == 0) {  // warp-parallel decoupled look-back: 32 predecessors per step
     const unsigned long long F_LOCAL = 1ull << 62, F_INCL = 2ull << 62, VMASK = (1ull << 62) - 1;
     volatile unsigned long long* st = scan_status;
-    st[blk] = (blk == 0 ? F_INCL : F_LOCAL) | total;
+    if (lane == 0) st[blk] = (blk == 0 ? F_INCL : F_LOCAL) | total;
     unsigned long long excl = 0;
     if (blk > 0) {
-      long long t = (long long)blk - 1;
+      long long top = (long long)blk - 1;
       uint32_t spins = 0;
-      while (t >= 0) {
-        unsigned long long sv = st[t];
-        if (sv == 0) {
-          if (++spins > SPIN_LIMIT) { atomicExch(&hdr->error, 2u); break; }
+      while (true) {
+        const long long idx = top - lane;
+        const unsigned long long sv = idx >= 0 ? st[idx] : F_INCL;  // virtual inclusive 0 in front of block 0
+        const uint32_t ready = __ballot_sync(0xFFFFFFFFu, sv != 0);
+        const uint32_t incl_m = __ballot_sync(0xFFFFFFFFu, (sv & F_INCL) != 0);
+        const int fi = incl_m ? (__ffs(incl_m) - 1) : 32;  // nearest predecessor with an inclusive prefix
+        const uint32_t need = fi < 32 ? ((2u << fi) - 1u) : 0xFFFFFFFFu;
+        if ((ready & need) != need) {
+          if (++spins > SPIN_LIMIT) { if (lane == 0) atomicExch(&hdr->error, 2u); break; }
           continue;
         }
-        excl += sv & VMASK;
-        if (sv & F_INCL) break;
-        t--;
+        unsigned long long v = (lane <= fi) ? (sv & VMASK) : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+        excl += v;
+        if (fi < 32) break;
+        top -= 32;
       }
-      st[blk] = F_INCL | (excl + total);
+      if (lane == 0) st[blk] = F_INCL | (excl + total);
     }
-    s_base = excl;
-    if ((int)blk == nblocks - 1) {
-      hdr->num_rendered = excl + total;
-      hdr->overflow = (excl + total) > cap ? 1u : 0u;
+    if (lane == 0) {
+      s_base = excl;
+      if ((int)blk == nblocks - 1) {
+        hdr->num_rendered = excl + total;
+        hdr->overflow = (excl + total) > cap ? 1u : 0u;
+      }
     }
   }
   __syncthreads();
@@ -232,6 +243,49 @@ __global__ void tile_ranges_kernel(const uint32_t* __restrict__ tkey_sorted, con
   }
 }
 
+// Work plan of the backward blend: every tile list is cut into segments of GS_SEG entries; seg_off = exclusive prefix
+// of the segment counts over tiles (seg_off[tiles] = number of items), items[] = (tile, segment).  One CTA.
+__global__ void __launch_bounds__(1024)
+plan_kernel(int tiles, const uint2* __restrict__ ranges, uint32_t* __restrict__ seg_off, uint2* __restrict__ items,
+            uint32_t max_items) {
+  __shared__ uint32_t s_w[32];
+  __shared__ uint32_t s_carry;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  if (tid == 0) s_carry = 0;
+  __syncthreads();
+  for (int t0 = 0; t0 < tiles; t0 += 1024) {
+    const int t = t0 + tid;
+    uint32_t nseg = 0;
+    if (t < tiles) { uint2 r = ranges[t]; nseg = (r.y - r.x + GS_SEG - 1) / GS_SEG; }
+    uint32_t incl = nseg;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_w[w] = incl;
+    __syncthreads();
+    uint32_t wv = s_w[lane], wincl = wv;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t v = __shfl_up_sync(0xFFFFFFFFu, wincl, o);
+      if (lane >= o) wincl += v;
+    }
+    const uint32_t wpre = __shfl_sync(0xFFFFFFFFu, wincl - wv, w);
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, wincl, 31);
+    const uint32_t off = s_carry + wpre + incl - nseg;
+    if (t < tiles) {
+      seg_off[t] = off;
+      for (uint32_t k = 0; k < nseg; k++)
+        if (off + k < max_items) items[off + k] = make_uint2((uint32_t)t, k);
+    }
+    __syncthreads();
+    if (tid == 0) s_carry += total;
+    __syncthreads();
+  }
+  if (tid == 0) seg_off[tiles] = s_carry < max_items ? s_carry : max_items;
+}
+
 uint32_t higher_msb(uint32_t n) {  // rasterizer_impl.cu:35-50
   uint32_t msb = sizeof(n) * 4, step = msb;
   while (step > 1) {
@@ -244,8 +298,9 @@ uint32_t higher_msb(uint32_t n) {  // rasterizer_impl.cu:35-50
 
 }  // namespace
 
-int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsScratch& s, uint32_t* list,
+int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsScratch& s, const GsList& l,
                       int64_t cap, cudaStream_t st) {
+  uint32_t* list = l.point_list;
   const int P = a.P;
   const int gx = (a.width + GS_TILE - 1) / GS_TILE, gy = (a.height + GS_TILE - 1) / GS_TILE;
   const int tiles = gx * gy;
@@ -280,5 +335,7 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   if (rb > 148 * 16) rb = 148 * 16;
   if (rb < 1) rb = 1;
   tile_ranges_kernel<<<rb, 256, 0, st>>>(s.tkey[tile_passes & 1], &g.hdr->num_rendered, (unsigned long long)cap, im.ranges);
+  // 5. backward work plan (segments of GS_SEG entries per tile)
+  plan_kernel<<<1, 1024, 0, st>>>(tiles, im.ranges, im.seg_off, l.items, (uint32_t)l.max_items);
   return gs_check(cudaGetLastError());
 }

@@ -68,14 +68,16 @@ def lib():
         L.gs_image_bytes.restype = sz
         L.gs_image_bytes.argtypes = [ctypes.c_int32, ctypes.c_int32]
         L.gs_list_bytes.restype = sz
-        L.gs_list_bytes.argtypes = [ctypes.c_int64]
+        L.gs_list_bytes.argtypes = [ctypes.c_int64, ctypes.c_int32, ctypes.c_int32]
+        L.gs_list_capacity.restype = ctypes.c_int64
+        L.gs_list_capacity.argtypes = [sz, ctypes.c_int32, ctypes.c_int32]
         L.gs_scratch_bytes.restype = sz
         L.gs_scratch_bytes.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int64]
         vp = ctypes.c_void_p
         L.gs_forward.restype = ctypes.c_int
         L.gs_forward.argtypes = [ctypes.POINTER(GsForwardArgs), vp, sz, vp, sz, vp, sz, vp, sz, ctypes.c_int64, vp, vp]
         L.gs_backward.restype = ctypes.c_int
-        L.gs_backward.argtypes = [ctypes.POINTER(GsBackwardArgs), vp, sz, vp, sz, vp, sz, vp]
+        L.gs_backward.argtypes = [ctypes.POINTER(GsBackwardArgs), vp, sz, vp, sz, vp, sz, ctypes.c_int64, vp]
         L.gs_mark_visible.restype = ctypes.c_int
         L.gs_mark_visible.argtypes = [ctypes.c_int32, vp, vp, vp, vp, vp]
         L.gs_read_num_rendered.restype = ctypes.c_int
@@ -176,8 +178,9 @@ def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_m
         if st.capacity == 0:
             st.capacity = max(4 * P, 1 << 18)
         while True:
-            cap = st.capacity
-            lst = torch.empty(L.gs_list_bytes(cap), **u8)
+            # capacities live on the 4096 lattice so that backward can recover them from the buffer size
+            cap = st.capacity = (st.capacity + 4095) // 4096 * 4096
+            lst = torch.empty(L.gs_list_bytes(cap, W, H), **u8)
             need = L.gs_scratch_bytes(P, W, H, cap)
             if st.scratch is None or st.scratch.numel() < need or st.scratch.device != dev:
                 st.scratch = torch.empty(int(need * 1.1) + 1024, **u8)
@@ -242,8 +245,9 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, scales, rotations, 
                            dcolors.data_ptr(), dmeans3D.data_ptr(), dcov3D.data_ptr(),
                            dsh.data_ptr() if M else None, dscales.data_ptr(), drot.data_ptr())
         stream = torch.cuda.current_stream(dev).cuda_stream
+        cap = L.gs_list_capacity(binningBuffer.numel(), W, H)
         status = L.gs_backward(ctypes.byref(a), geomBuffer.data_ptr(), geomBuffer.numel(), imageBuffer.data_ptr(),
-                               imageBuffer.numel(), binningBuffer.data_ptr(), binningBuffer.numel(), stream)
+                               imageBuffer.numel(), binningBuffer.data_ptr(), binningBuffer.numel(), cap, stream)
         _check(status, "gs_backward")
         stats["backward_calls"] += 1
     return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot

@@ -98,11 +98,14 @@ typedef struct GsBackwardArgs {
 } GsBackwardArgs;
 
 /* Workspace sizes.  geom and image are kept for backward (like geomBuffer / imgBuffer); `list` holds the
- * sorted Gaussian index per (Gaussian, tile) pair (like binningBuffer) and is kept too; `scratch` is only
- * used inside gs_forward and may be reused by the next call. */
+ * sorted Gaussian index per (Gaussian, tile) pair (like binningBuffer) plus the backward work-item table and the
+ * forward's per-pixel checkpoints, and is kept too (gs_backward must be given the same pair_capacity); `scratch`
+ * is only used inside gs_forward and may be reused by the next call. */
 size_t gs_geom_bytes(int32_t P);
 size_t gs_image_bytes(int32_t width, int32_t height);
-size_t gs_list_bytes(int64_t pair_capacity);
+size_t gs_list_bytes(int64_t pair_capacity, int32_t width, int32_t height);
+/* inverse of gs_list_bytes for capacities that are multiples of 4096 (the largest one that fits list_bytes) */
+int64_t gs_list_capacity(size_t list_bytes, int32_t width, int32_t height);
 size_t gs_scratch_bytes(int32_t P, int32_t width, int32_t height, int64_t pair_capacity);
 
 /* Forward.  Launches everything on `stream` without synchronising (unless args->debug).  The number of
@@ -118,7 +121,7 @@ int gs_forward(const GsForwardArgs* args, void* geom, size_t geom_bytes, void* i
 int gs_read_num_rendered(const void* geom, int64_t* num_rendered_host, void* stream);
 
 int gs_backward(const GsBackwardArgs* args, const void* geom, size_t geom_bytes, const void* image,
-                size_t image_bytes, const void* list, size_t list_bytes, void* stream);
+                size_t image_bytes, const void* list, size_t list_bytes, int64_t pair_capacity, void* stream);
 
 /* present[P] (bytes 0/1) = p_view.z > 0.2 */
 int gs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -32,7 +32,9 @@ def test_workspace_sizes(built_lib):
     L = _C.lib()
     assert L.gs_geom_bytes(1000) >= 1000 * 48 + 256
     assert L.gs_image_bytes(512, 512) >= 512 * 512 * 8 + 1024 * 8
-    assert L.gs_list_bytes(10) >= 40
+    assert L.gs_list_bytes(10, 512, 512) >= 40
+    for cap in (4096, 262144, 1 << 22):
+        assert L.gs_list_capacity(L.gs_list_bytes(cap, 512, 512), 512, 512) == cap
     a, b = L.gs_scratch_bytes(1000, 64, 64, 1 << 16), L.gs_scratch_bytes(1000, 64, 64, 1 << 20)
     assert b > a > 0
 

@@ -57,10 +57,12 @@ def test_pose_forward_backward(built_lib, deg, cano, mod):
     loss.backward()
     torch.cuda.synchronize()
     o32, _ = _oracle(t, deg, cano=cano, mod=mod)
-    assert float((means.cpu() - o32["means3D"]).abs().max()) <= 1e-5
+    assert float((means.detach().cpu() - o32["means3D"]).abs().max()) <= 1e-5
     assert float((col.cpu() - o32["colors"]).abs().max()) <= 1e-5
     assert float((op.cpu() - o32["opacity"]).abs().max()) <= 1e-6
-    assert rel(cov.detach().cpu(), o32["cov3D"].detach()) <= 1e-5
+    o64, _ = _oracle(t, deg, torch.float64, cano=cano, mod=mod)
+    e64, e32 = rel(cov.detach().cpu(), o64["cov3D"].detach()), rel(cov.detach().cpu(), o32["cov3D"].detach())
+    assert e64 <= 1e-5, f"cov3D: vs fp64 oracle {e64:.3e}, vs fp32 oracle {e32:.3e}"
     assert float((T_fwd.cpu() - o32["T_fwd"]).abs().max()) <= 1e-5
     assert float((Rbar.cpu() - o32["rotation_bar"]).abs().max()) <= 1e-5
     _, leaf = _oracle(t, deg, torch.float64, grads, cano=cano, mod=mod)
