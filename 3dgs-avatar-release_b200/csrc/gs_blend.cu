@@ -67,100 +67,246 @@ __device__ __forceinline__ Rec3 load_rec(const GsRec* __restrict__ rec, uint32_t
 
 constexpr int kChunk = 4;  // survivors evaluated together: their exp() chains are independent (ILP), only the T update is serial
 
-__global__ void __launch_bounds__(kWarps * 32)
+// ---- forward -------------------------------------------------------------------------------------------------------
+// The only serial dependency of front-to-back blending is the transmittance chain T <- T*(1-alpha); culling and the
+// alpha evaluation (the exp) of a batch do not depend on it.  kGroup warps therefore share one 8x4 pixel block and
+// take its 32-entry batches round-robin: each warp culls its batch and evaluates alpha for the survivors into shared
+// memory WITHOUT waiting, then takes the block's turn, applies its survivors to the running (T, C, last, done) state in
+// list order -- exactly the reference's operation sequence, so results stay bit-identical -- and passes the turn on.
+// One CTA = one pixel block of one tile (grid.z = 8 blocks): the eight blocks of a deep tile land on different SMs, so
+// a tile list of 6000 entries (few tiles, deep lists: the avatar case) is evaluated by 32 warps on 8 SMs instead of
+// 8 warps on one SM, whose issue slots were the bound.
+constexpr int kGroup = 4;
+constexpr int kFwdWarps = kGroup;
+constexpr uint32_t kTurnDone = 0x7FFFFFFFu;
+
+struct FwdWarpSmem {       // per warp
+  float4 q0[32], q1[32];   // staged records (see Slab)
+  float q2[32];
+  float alpha[32][32];     // [survivor][pixel lane]; 0 = the reference's skip tests failed
+  float4 row[32];          // [survivor] r, g, b, 1-based list position (int bits): what the serial part reads per survivor
+};
+struct FwdBlockState {     // per pixel block, handed from warp to warp
+  float T[32], C0[32], C1[32], C2[32];
+  uint32_t last[32];
+  uint32_t done[32];
+  uint32_t turn;           // kTurnDone once every pixel of the block has terminated, else 0
+  uint32_t pad;
+  unsigned long long bar[kGroup];  // mbarrier of warp g: completes a phase when the batch in front of g's next batch is applied
+  unsigned long long bar_fin;      // completes when the last batch is applied or every pixel has terminated
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_cta(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"((uint32_t)__cvta_generic_to_shared(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_cta(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+
+// mbarriers: waiting warps are suspended by the hardware instead of spinning on issue slots
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.acquire.cta.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
+}
+
+// warp-uniform reads of the turn word: lane 0 loads (acquire), the value is broadcast, __syncwarp orders the other
+// lanes' subsequent shared-memory reads after it
+__device__ __forceinline__ uint32_t turn_now(const uint32_t* turn, int lane) {
+  uint32_t t = 0;
+  if (lane == 0) t = ld_acquire_cta(turn);
+  t = __shfl_sync(0xFFFFFFFFu, t, 0);
+  __syncwarp();
+  return t;
+}
+#ifdef GS_FWD_TRACE
+__device__ long long g_fwd_trace[512 * 4];
+#define TRACE(b, i) do { if (trace_on && lane == 0 && (b) < 512) g_fwd_trace[(b) * 4 + (i)] = clock64(); } while (0)
+#else
+#define TRACE(b, i) do { } while (0)
+#endif
+
+__global__ void __launch_bounds__(kFwdWarps * 32)
 blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H,
                  const GsRec* __restrict__ rec, const float* __restrict__ bg, float* __restrict__ final_T,
                  uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                  const uint32_t* __restrict__ seg_off, float4* __restrict__ ckpt) {
-  __shared__ Slab s_slab[kWarps];
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  Slab& sl = s_slab[w];
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  FwdBlockState& bs = *reinterpret_cast<FwdBlockState*>(smem_raw);
+  FwdWarpSmem* const wsmem = reinterpret_cast<FwdWarpSmem*>(smem_raw + sizeof(FwdBlockState));
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;  // g = position in the block's warp group
+  const int blk = blockIdx.z;                               // pixel block of the tile
+  FwdWarpSmem& ws = wsmem[g];
   const int tile = blockIdx.y * gridDim.x + blockIdx.x;
   const uint2 range = ranges[tile];
+  const int len = (int)(range.y - range.x);
+  const int nb = (len + 31) >> 5;
   // checkpoint slots of this tile: one per segment start + one final (backward work items restart from them)
-  float4* const ck = ckpt + ((size_t)seg_off[tile] + tile) * 256 + threadIdx.x;
-  const int bx = blockIdx.x * GS_TILE + (w & 1) * 8, by = blockIdx.y * GS_TILE + (w >> 1) * 4;
+  float4* const ck = ckpt + ((size_t)seg_off[tile] + tile) * 256 + blk * 32 + lane;
+  const int bx = blockIdx.x * GS_TILE + (blk & 1) * 8, by = blockIdx.y * GS_TILE + (blk >> 1) * 4;
   const int px = bx + (lane & 7), py = by + (lane >> 3);
   const bool inside = px < W && py < H;
   const float pfx = (float)px, pfy = (float)py;
   const float X0 = (float)bx, X1 = (float)(bx + 7), Y0 = (float)by, Y1 = (float)(by + 3);
-  bool done = !inside;
-  float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
-  uint32_t last = 0;
+  if (g == 0) {
+    bs.T[lane] = 1.0f; bs.C0[lane] = 0.f; bs.C1[lane] = 0.f; bs.C2[lane] = 0.f;
+    bs.last[lane] = 0; bs.done[lane] = inside ? 0u : 1u;
+    if (lane == 0) {
+      bs.turn = 0;
+      for (int i = 0; i < kGroup; i++) mbar_init(&bs.bar[i], 1);
+      mbar_init(&bs.bar_fin, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+  }
+  __syncthreads();
+  uint32_t waits = 0;  // completed waits on this warp's barrier -> parity of the next one
 
-  // software pipeline: records of batch b and list indices of batch b+1 are in registers when batch b is processed
+#ifdef GS_FWD_TRACE
+  const bool trace_on = len >= 6000 && blk == 3;
+#endif
+  const uint32_t* const tl = list + range.x;
   Rec3 cur;
   cur.a = cur.b = cur.c = make_float4(0.f, 0.f, 0.f, 0.f);
   uint32_t id_next = 0;
   {
-    const uint32_t e = range.x + lane;
-    if (e < range.y) cur = load_rec(rec, list[e]);
-    if (e + 32 < range.y) id_next = list[e + 32];
+    const int e = g * 32 + lane;
+    if (e < len) cur = load_rec(rec, tl[e]);
+    if (e + kGroup * 32 < len) id_next = tl[e + kGroup * 32];
   }
-  for (uint32_t base = range.x; base < range.y; base += 32) {
-    if (__all_sync(0xFFFFFFFFu, done)) break;
-    const uint32_t e = base + lane;
-    if (((base - range.x) & (GS_SEG - 1)) == 0) ck[(size_t)((base - range.x) / GS_SEG) * 256] = make_float4(T, C0, C1, C2);
+  for (int b = g; b < nb; b += kGroup) {
+    if (turn_now(&bs.turn, lane) == kTurnDone) break;  // every pixel of the block has terminated
+    TRACE(b, 0);
+    const int e = b * 32 + lane;
     bool keep = false;
-    if (e < range.y) {
+    if (e < len) {
       keep = may_contribute(cur.a.x, cur.a.y, cur.b.x, cur.b.y, cur.b.z, cur.a.z, X0, X1, Y0, Y1);
-      sl.q0[lane] = make_float4(cur.a.x, cur.a.y, cur.b.x, cur.b.y);
-      sl.q1[lane] = make_float4(cur.b.z, cur.b.w, cur.c.x, cur.c.y);
-      sl.q2[lane] = cur.c.z;
+      ws.q0[lane] = make_float4(cur.a.x, cur.a.y, cur.b.x, cur.b.y);
+      ws.q1[lane] = make_float4(cur.b.z, cur.b.w, cur.c.x, cur.c.y);
+      ws.q2[lane] = cur.c.z;
     }
-    // prefetch: records of the next batch, indices of the one after
+    // prefetch: records of this warp's next batch, indices of the one after
     Rec3 nxt = cur;
-    if (e + 32 < range.y) nxt = load_rec(rec, id_next);
+    if (e + kGroup * 32 < len) nxt = load_rec(rec, id_next);
     uint32_t id_nn = 0;
-    if (e + 64 < range.y) id_nn = list[e + 64];
+    if (e + 2 * kGroup * 32 < len) id_nn = tl[e + 2 * kGroup * 32];
     __syncwarp();
-    uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
-    while (mask) {
-      float al[kChunk], cr[kChunk], cg[kChunk], cb_[kChunk];
-      bool okk[kChunk];
-      int jj[kChunk];
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
+    // ---- parallel part: alpha of every survivor for this lane's pixel (reference tests, forward.cu:325-345) ----
+    {
+      uint32_t m = mask;
+      int k = 0;
+      while (m) {
 #pragma unroll
-      for (int k = 0; k < kChunk; k++) {
-        const bool valid = mask != 0;
-        const int j = valid ? (__ffs(mask) - 1) : 0;
-        mask &= mask - 1;  // 0 stays 0
-        jj[k] = j;
-        const float4 q0 = sl.q0[j], q1 = sl.q1[j];
-        // reference test sequence, forward.cu:325-361, in the reference's FP32 operation order
-        const float dx = __fsub_rn(q0.x, pfx), dy = __fsub_rn(q0.y, pfy);
-        const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x))), -0.5f,
-                                      -__fmul_rn(dy, __fmul_rn(dx, q0.w)));  // SASS: FFMA q*-0.5 - cross
-        const float alpha = fminf(0.99f, __fmul_rn(q1.y, gs_exp(power)));
-        al[k] = alpha; cr[k] = q1.z; cg[k] = q1.w; cb_[k] = sl.q2[j];
-        okk[k] = valid && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+        for (int u = 0; u < kChunk; u++) {
+          const bool valid = m != 0;
+          const int j = valid ? (__ffs(m) - 1) : 0;
+          m &= m - 1;
+          const float4 q0 = ws.q0[j], q1 = ws.q1[j];
+          const float dx = __fsub_rn(q0.x, pfx), dy = __fsub_rn(q0.y, pfy);
+          const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x))), -0.5f,
+                                        -__fmul_rn(dy, __fmul_rn(dx, q0.w)));  // SASS: FFMA q*-0.5 - cross
+          const float alpha = fminf(0.99f, __fmul_rn(q1.y, gs_exp(power)));
+          const bool ok = !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+          if (valid) {
+            ws.alpha[k + u][lane] = ok ? alpha : 0.0f;
+            if (lane == 0) ws.row[k + u] = make_float4(q1.z, q1.w, ws.q2[j], __int_as_float(b * 32 + j + 1));
+          }
+        }
+        k += kChunk;
       }
+    }
+    // ---- serial part: wait for the block's turn, apply the survivors in list order, pass the turn on ----
+    TRACE(b, 1);
+    if (b > 0) { mbar_wait(&bs.bar[g], waits & 1u); waits++; }  // batch b-1 applied (or every pixel terminated)
+    __syncwarp();
+    if (turn_now(&bs.turn, lane) == kTurnDone) break;
+    TRACE(b, 2);
+    float T = bs.T[lane], C0 = bs.C0[lane], C1 = bs.C1[lane], C2 = bs.C2[lane];
+    uint32_t last = bs.last[lane];
+    bool done = bs.done[lane] != 0;
+    if ((b & (GS_SEG / 32 - 1)) == 0) ck[(size_t)(b / (GS_SEG / 32)) * 256] = make_float4(T, C0, C1, C2);
+    {
+      // rows 0..cnt-1 of ws.alpha / ws.row in list order: loads of a chunk are issued together, only the T chain is serial
+      const int cnt = __popc(mask);
+      __syncwarp();  // ws.row was written by lane 0
+      // The transmittance runs on unconditionally (one FMUL per survivor on the critical chain: a skipped entry multiplies
+      // by exactly 1.0f); the first entry that would push it below 1e-4 freezes a copy.  Same values, same order as
+      // forward.cu:335-361, but the compare no longer sits between two multiplies.
+      float Tr = T;
+      for (int k0 = 0; k0 < cnt; k0 += kChunk) {
+        float al[kChunk];
+        float4 rw[kChunk];
 #pragma unroll
-      for (int k = 0; k < kChunk; k++) {
-        bool ok = okk[k] && !done;
-        const float test_T = __fmul_rn(T, __fsub_rn(1.0f, al[k]));
-        if (ok && test_T < 0.0001f) { done = true; ok = false; }
-        if (ok) {
-          C0 = __fmaf_rn(T, __fmul_rn(al[k], cr[k]), C0);
-          C1 = __fmaf_rn(T, __fmul_rn(al[k], cg[k]), C1);
-          C2 = __fmaf_rn(T, __fmul_rn(al[k], cb_[k]), C2);
-          T = test_T;
-          last = base + jj[k] - range.x + 1;  // 1-based position in the tile list (contributor, forward.cu:328)
+        for (int u = 0; u < kChunk; u++) {
+          const int k = k0 + u;  // <= 31 because cnt <= 32 and k0 is a multiple of kChunk
+          const float a_ = ws.alpha[k][lane];
+          al[u] = (k < cnt) ? a_ : 0.0f;
+          rw[u] = ws.row[k];
+        }
+#pragma unroll
+        for (int u = 0; u < kChunk; u++) {
+          const bool nz = al[u] != 0.0f;
+          const float m = nz ? __fsub_rn(1.0f, al[u]) : 1.0f;
+          const float test_T = __fmul_rn(Tr, m);
+          const bool term = nz && !done && (test_T < 0.0001f);
+          const bool ok = nz && !done && !term;
+          if (term) { T = Tr; done = true; }
+          if (ok) {
+            C0 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].x), C0);
+            C1 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].y), C1);
+            C2 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].z), C2);
+            last = (uint32_t)__float_as_int(rw[u].w);  // 1-based position in the tile list (contributor, forward.cu:328)
+          }
+          Tr = test_T;
         }
       }
-      if (__all_sync(0xFFFFFFFFu, done)) mask = 0;
+      if (!done) T = Tr;
     }
+    bs.T[lane] = T; bs.C0[lane] = C0; bs.C1[lane] = C1; bs.C2[lane] = C2;
+    bs.last[lane] = last; bs.done[lane] = done ? 1u : 0u;
+    const bool all_done = __all_sync(0xFFFFFFFFu, done);
     __syncwarp();
+    if (lane == 0) {
+      if (all_done) {
+        st_release_cta(&bs.turn, kTurnDone);
+        for (int i = 0; i < kGroup; i++) if (i != g) mbar_arrive(&bs.bar[i]);  // wake whoever waits; they see kTurnDone
+      } else {
+        mbar_arrive(&bs.bar[(g + 1) % kGroup]);
+      }
+      if (all_done || b == nb - 1) mbar_arrive(&bs.bar_fin);
+    }
+    TRACE(b, 3);
+    if (all_done) break;
     cur = nxt;
     id_next = id_nn;
   }
-  ck[(size_t)((range.y - range.x + GS_SEG - 1) / GS_SEG) * 256] = make_float4(T, C0, C1, C2);
-  if (inside) {
-    const size_t pix = (size_t)py * W + px, hw = (size_t)H * W;
-    final_T[pix] = T;
-    n_contrib[pix] = last;
-    out_color[pix] = __fmaf_rn(T, bg[0], C0);
-    out_color[hw + pix] = __fmaf_rn(T, bg[1], C1);
-    out_color[2 * hw + pix] = __fmaf_rn(T, bg[2], C2);
+  if (g == 0) {  // the block's first warp waits for the last batch and writes the pixel results
+    if (nb > 0) mbar_wait(&bs.bar_fin, 0);
+    __syncwarp();
+    const float T = bs.T[lane], C0 = bs.C0[lane], C1 = bs.C1[lane], C2 = bs.C2[lane];
+    ck[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256] = make_float4(T, C0, C1, C2);
+    if (inside) {
+      const size_t pix = (size_t)py * W + px, hw = (size_t)H * W;
+      final_T[pix] = T;
+      n_contrib[pix] = bs.last[lane];
+      out_color[pix] = __fmaf_rn(T, bg[0], C0);
+      out_color[hw + pix] = __fmaf_rn(T, bg[1], C1);
+      out_color[2 * hw + pix] = __fmaf_rn(T, bg[2], C2);
+    }
   }
 }
 
@@ -352,8 +498,16 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 
 int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st) {
   dim3 grid((a.width + GS_TILE - 1) / GS_TILE, (a.height + GS_TILE - 1) / GS_TILE);
-  blend_fwd_kernel<<<grid, kWarps * 32, 0, st>>>(im.ranges, l.point_list, a.width, a.height, g.rec, a.background,
-                                                 im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt);
+  const size_t smem = sizeof(FwdBlockState) + kFwdWarps * sizeof(FwdWarpSmem);
+  grid.z = kWarps;  // one CTA per 8x4 pixel block of a tile
+  static bool configured = false;
+  if (!configured) {
+    if (gs_check(cudaFuncSetAttribute(blend_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != GS_OK)
+      return GS_ERR_CUDA;
+    configured = true;
+  }
+  blend_fwd_kernel<<<grid, kFwdWarps * 32, smem, st>>>(im.ranges, l.point_list, a.width, a.height, g.rec, a.background,
+                                                       im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt);
   return gs_check(cudaGetLastError());
 }
 
@@ -364,3 +518,9 @@ int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage&
       im.final_T, im.n_contrib, a.dL_dpix, a.dL_dmean2D, a.dL_dconic, a.dL_dopacity, a.dL_dcolor);
   return gs_check(cudaGetLastError());
 }
+
+#ifdef GS_FWD_TRACE
+extern "C" int gs_debug_fwd_trace(long long* host, int n) {
+  return gs_check(cudaMemcpyFromSymbol(host, g_fwd_trace, sizeof(long long) * n));
+}
+#endif

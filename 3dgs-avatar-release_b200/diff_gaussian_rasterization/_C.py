@@ -127,6 +127,7 @@ class _DeviceState:
 
     def __init__(self):
         self.scratch = None
+        self.graph_keepalive = []
         self.capacity = 0
         self.pinned = torch.empty(2, dtype=torch.int64).pin_memory()
         self.pinned_np = self.pinned.numpy()
@@ -190,6 +191,12 @@ def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_m
                                   st.pinned.data_ptr(), stream)
             _check(status, "gs_forward")
             stats["forward_calls"] += 1
+            if torch.cuda.is_current_stream_capturing():
+                # CUDA-graph capture: no host round trip.  The pair count lands in pinned memory on every replay;
+                # the caller checks it with graph_overflow() after a replay (capacity is fixed inside a graph).
+                st.graph_capacity = cap
+                st.graph_keepalive.append(st.scratch)  # a later regrow must not free what the graph points at
+                return -1, out_color, radii, geom, lst, img
             # The pair count N is produced on the device; the async copy into pinned memory lands while the blend
             # kernel is still running, so this wait overlaps GPU work (the reference blocks the pipeline instead,
             # rasterizer_impl.cu:281).
@@ -210,6 +217,22 @@ def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_m
             st.capacity = int(N * _GROW) + 4096  # overflow: the image is invalid -> regrow and rerun
             stats["capacity_regrows"] += 1
         return N, out_color, radii, geom, lst, img
+
+
+def graph_overflow(device=None):
+    """After replaying a CUDA graph that contains rasterize_gaussians (and synchronising): returns (N, overflowed).
+    overflowed means the captured pair capacity was too small, the frame is invalid, and the graph must be re-captured
+    (the capacity high-water mark has already been raised)."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    st = _dev_state(dev)
+    N, flags = int(st.pinned_np[0]), int(st.pinned_np[1])
+    if (flags >> 32) != 0:
+        raise GsError(f"gs_forward: internal look-back timeout (error flag {flags >> 32})")
+    over = N > getattr(st, "graph_capacity", st.capacity)
+    if over:
+        st.capacity = int(N * _GROW) + 4096
+        stats["capacity_regrows"] += 1
+    return N, over
 
 
 def rasterize_gaussians_backward(bg, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,

@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--height", type=int, default=H_DEFAULT)
     ap.add_argument("--cpu-steps", type=int, default=3, help="steps of the cpu_baseline sample inside the ours arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--eager", action="store_true", help="time the eager Python path instead of CUDA-graph replay of the same step")
     ap.add_argument("--profile-only", action="store_true", help="run warmup+steps training steps and exit (for ncu)")
     return ap.parse_args()
 
@@ -136,6 +137,20 @@ class HotPath:
         tgt = pf["target"].to(self.dev, non_blocking=True)
         return dict(bones=s[:384].view(24, 4, 4), view=s[384:400].view(4, 4), proj=s[400:416].view(4, 4), campos=s[416:419],
                     target=tgt, tanx=pf["tanx"], tany=pf["tany"])
+
+    def static_frame(self, fr):
+        """Per-frame inputs in fixed device storage (what a CUDA graph reads); `load_static` overwrites them."""
+        cam = fr["cam"]
+        small = torch.zeros(419, device=self.dev)
+        target = torch.zeros(3, self.H, self.W, device=self.dev)
+        f = dict(small=small, bones=small[:384].view(24, 4, 4), view=small[384:400].view(4, 4), proj=small[400:416].view(4, 4),
+                 campos=small[416:419], target=target, tanx=cam["tanfovx"], tany=cam["tanfovy"])
+        self.load_static(f, self.frame_to_pinned(fr))
+        return f
+
+    def load_static(self, f, pf):
+        f["small"].copy_(pf["small"], non_blocking=True)
+        f["target"].copy_(pf["target"], non_blocking=True)
 
     def forward(self, f):
         p = self.params
@@ -365,8 +380,14 @@ def ours_main(args):
     f_pin = hp.frame_to_pinned(frames[rank])
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2, written between timed steps
 
+    from avatar_pose.graphs import GraphedStep
+    f_static = hp.static_frame(frames[rank])
+    eager = args.eager
+    g_train = None if eager else GraphedStep(lambda: hp.train_step(f_static))
+    g_render = None if eager else GraphedStep(lambda: hp.render(f_static))
+
     def train_resident():
-        loss = hp.train_step(f_dev)
+        loss = hp.train_step(f_dev) if eager else g_train.replay()
         if world > 1:
             dist.all_reduce(avatar_pose.last_grad_slab())
         return loss
@@ -374,8 +395,11 @@ def ours_main(args):
     loss_host = torch.empty(1).pin_memory()
 
     def train_e2e():
-        f = hp.upload(f_pin)
-        loss = hp.train_step(f)
+        if eager:
+            loss = hp.train_step(hp.upload(f_pin))
+        else:
+            hp.load_static(f_static, f_pin)
+            loss = g_train.replay()
         if world > 1:
             dist.all_reduce(avatar_pose.last_grad_slab())
         loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
@@ -384,11 +408,15 @@ def ours_main(args):
     img_host = torch.empty(3, H, W).pin_memory()
 
     def render_resident():
-        return hp.render(f_dev)
+        return hp.render(f_dev) if eager else g_render.replay()
 
     def render_e2e():
-        f = hp.upload(f_pin)
-        img_host.copy_(hp.render(f), non_blocking=True)
+        if eager:
+            img = hp.render(hp.upload(f_pin))
+        else:
+            hp.load_static(f_static, f_pin)
+            img = g_render.replay()
+        img_host.copy_(img, non_blocking=True)
         torch.cuda.current_stream(dev).synchronize()
 
     def timed(fn, steps, warmup):
@@ -420,6 +448,11 @@ def ours_main(args):
     # hot-cache numbers (no L2 flush), for information
     torch.cuda.synchronize(dev)
     hot = time_steps(train_resident, max(args.steps // 2, 5), 3, None, dev)
+    ms_eager = float(np.mean(time_steps(lambda: hp.train_step(f_dev), max(args.steps // 2, 5), 3, flush, dev)))
+    if not eager:
+        torch.cuda.synchronize(dev)
+        n_graph, over = _C.graph_overflow(dev)
+        assert not over, f"the captured pair capacity overflowed (N={n_graph}): timed frames were invalid"
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -478,7 +511,8 @@ def ours_main(args):
         except Exception as ex:
             ref_cuda = {"unavailable": str(ex)[:200]}
     tile_passes = (max((((W + 15) // 16) * ((H + 15) // 16)).bit_length(), 1) + 7) // 8
-    launches = args.steps * (1 + (1 + 4 + 1 + tile_passes + 1 + 1) + 2 + 1)
+    # pose_fwd | preprocess, 4 depth passes, emit, tile passes, ranges, plan, blend_fwd | blend_bwd, preprocess_bwd | pose_bwd
+    launches = args.steps * (1 + (1 + 4 + 1 + tile_passes + 1 + 1 + 1) + 2 + 1)
     h2d = int(f_pin["small"].numel() * 4 + f_pin["target"].numel() * 4)
     line = {"metric": METRIC, "value": world * 1e3 / ms_train, "unit": "iter/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_train, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -486,13 +520,14 @@ def ours_main(args):
             "config": {"workload": f"training step fwd+bwd, {W}x{H}, {P} random-init Gaussians, SH deg 3, rigid LBS posing + tile "
                                    "rasterizer (BASELINE.json configs[2]); one camera/pose per rank", "N_pairs": N, "E_fwd": E_fwd,
                        "E_bwd": E_bwd, "l2": "flushed between timed steps (256 MiB write, outside the per-step events)",
+                       "launch": "eager Python calls" if eager else "one CUDA-graph replay per step (avatar_pose.graphs.GraphedStep); eager_ms_per_step is the same step launched op by op",
                        "parallelism": f"dp{world} (frame-sharded; NCCL all-reduce of the flat gradient slab)" if world > 1 else "single GPU"},
             "e2e": {"value": world * 1e3 / ms_train_e2e, "unit": "iter/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": ms_train_e2e},
             "render_fps": world * 1e3 / ms_render,
             "render_e2e": {"value": world * 1e3 / ms_render_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d - 3 * H * W * 4,
                            "d2h_bytes_per_step": 3 * H * W * 4},
-            "ms_per_step_hot_l2": float(np.mean(hot)), "ms_per_step_p10_p90": [float(np.percentile(ts_train, 10)), float(np.percentile(ts_train, 90))],
+            "eager_ms_per_step": ms_eager, "ms_per_step_hot_l2": float(np.mean(hot)), "ms_per_step_p10_p90": [float(np.percentile(ts_train, 10)), float(np.percentile(ts_train, 90))],
             "gpu_launches": launches, "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": fp32_peak,
             "cpu_baseline": cpu, "ref_cuda": ref_cuda, "clocks": sampler.summary(), "regrows": _C.stats["capacity_regrows"]}
     print(json.dumps(line))
