@@ -69,31 +69,39 @@ constexpr int kChunk = 4;  // survivors evaluated together: their exp() chains a
 
 // ---- forward -------------------------------------------------------------------------------------------------------
 // The only serial dependency of front-to-back blending is the transmittance chain T <- T*(1-alpha); culling and the
-// alpha evaluation (the exp) of a batch do not depend on it.  kGroup warps therefore share one 8x4 pixel block and
-// take its 32-entry batches round-robin: each warp culls its batch and evaluates alpha for the survivors into shared
-// memory WITHOUT waiting, then takes the block's turn, applies its survivors to the running (T, C, last, done) state in
-// list order -- exactly the reference's operation sequence, so results stay bit-identical -- and passes the turn on.
-// One CTA = one pixel block of one tile (grid.z = 8 blocks): the eight blocks of a deep tile land on different SMs, so
-// a tile list of 6000 entries (few tiles, deep lists: the avatar case) is evaluated by 32 warps on 8 SMs instead of
-// 8 warps on one SM, whose issue slots were the bound.
-constexpr int kGroup = 4;
-constexpr int kFwdWarps = kGroup;
-constexpr uint32_t kTurnDone = 0x7FFFFFFFu;
+// alpha evaluation (the exp) of a batch do not depend on it.  One CTA = one 8x4 pixel block of one tile (the eight
+// blocks of a deep tile land on different SMs: one SM's issue slots were the bound), warp-specialised:
+//   * kProducers producer warps take the block's 32-entry batches round-robin; each culls its batch against the block,
+//     evaluates alpha for every survivor and pixel (the reference's tests, forward.cu:325-345) and leaves the rows in
+//     its shared-memory buffer, in list order;
+//   * ONE consumer warp keeps (T, C, last, done) in registers and applies the rows batch by batch in list order --
+//     exactly the reference's operation sequence, so final_T / n_contrib / image stay bit-identical.
+// full/empty mbarriers per producer buffer: waiting warps are suspended by the hardware instead of spinning on issue
+// slots.  A tile list of 6000 entries (few tiles, deep lists: the avatar case) costs ~500 cycles per batch on the
+// consumer's chain instead of ~2200 in a one-warp-does-everything loop.
+#ifndef GS_FWD_PRODUCERS
+#define GS_FWD_PRODUCERS 7
+#endif
+#ifndef GS_FWD_PCHUNK
+#define GS_FWD_PCHUNK 4
+#endif
+constexpr int kProducers = GS_FWD_PRODUCERS;
+constexpr int kFwdWarps = kProducers + 1;
+constexpr int kPChunk = GS_FWD_PCHUNK;  // survivors whose alpha is evaluated together (ILP) by a producer
 
-struct FwdWarpSmem {       // per warp
+struct FwdBuf {            // one per producer warp
   float4 q0[32], q1[32];   // staged records (see Slab)
   float q2[32];
-  float alpha[32][32];     // [survivor][pixel lane]; 0 = the reference's skip tests failed
-  float4 row[32];          // [survivor] r, g, b, 1-based list position (int bits): what the serial part reads per survivor
+  float alpha[32][32];     // [survivor row][pixel lane]; 0 = the reference's skip tests failed
+  float4 row[32];          // [survivor row] r, g, b, 1-based list position (int bits)
+  uint32_t cnt;            // rows in this batch
+  uint32_t pad[3];
 };
-struct FwdBlockState {     // per pixel block, handed from warp to warp
-  float T[32], C0[32], C1[32], C2[32];
-  uint32_t last[32];
-  uint32_t done[32];
-  uint32_t turn;           // kTurnDone once every pixel of the block has terminated, else 0
-  uint32_t pad;
-  unsigned long long bar[kGroup];  // mbarrier of warp g: completes a phase when the batch in front of g's next batch is applied
-  unsigned long long bar_fin;      // completes when the last batch is applied or every pixel has terminated
+struct FwdCtl {
+  unsigned long long full[kProducers];   // producer -> consumer: rows of the buffer are ready
+  unsigned long long empty[kProducers];  // consumer -> producer: buffer may be overwritten
+  uint32_t done;                         // every pixel of the block has terminated
+  uint32_t pad[3];
 };
 
 __device__ __forceinline__ uint32_t ld_acquire_cta(const uint32_t* p) {
@@ -104,13 +112,14 @@ __device__ __forceinline__ uint32_t ld_acquire_cta(const uint32_t* p) {
 __device__ __forceinline__ void st_release_cta(uint32_t* p, uint32_t v) {
   asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
 }
-
-// mbarriers: waiting warps are suspended by the hardware instead of spinning on issue slots
 __device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
 }
-__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {  // release: prior shared-memory writes are visible
   asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_relaxed(unsigned long long* bar) {  // WAR hand-back: the reads were consumed
+  asm volatile("mbarrier.arrive.relaxed.cta.shared::cta.b64 _, [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
   asm volatile(
@@ -123,19 +132,17 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t pari
       "DONE_%=:\n"
       "}\n" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
 }
-
-// warp-uniform reads of the turn word: lane 0 loads (acquire), the value is broadcast, __syncwarp orders the other
-// lanes' subsequent shared-memory reads after it
-__device__ __forceinline__ uint32_t turn_now(const uint32_t* turn, int lane) {
+// warp-uniform read of a shared flag: lane 0 loads (acquire), the value is broadcast
+__device__ __forceinline__ uint32_t flag_now(const uint32_t* f, int lane) {
   uint32_t t = 0;
-  if (lane == 0) t = ld_acquire_cta(turn);
+  if (lane == 0) t = ld_acquire_cta(f);
   t = __shfl_sync(0xFFFFFFFFu, t, 0);
-  __syncwarp();
   return t;
 }
+
 #ifdef GS_FWD_TRACE
-__device__ long long g_fwd_trace[512 * 4];
-#define TRACE(b, i) do { if (trace_on && lane == 0 && (b) < 512) g_fwd_trace[(b) * 4 + (i)] = clock64(); } while (0)
+__device__ long long g_fwd_trace[512 * 8];
+#define TRACE(b, i) do { if (trace_on && lane == 0 && (b) < 512) s_trace[(b) * 8 + (i)] = clock64(); } while (0)
 #else
 #define TRACE(b, i) do { } while (0)
 #endif
@@ -146,72 +153,68 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                  const uint32_t* __restrict__ seg_off, float4* __restrict__ ckpt) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  FwdBlockState& bs = *reinterpret_cast<FwdBlockState*>(smem_raw);
-  FwdWarpSmem* const wsmem = reinterpret_cast<FwdWarpSmem*>(smem_raw + sizeof(FwdBlockState));
-  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;  // g = position in the block's warp group
-  const int blk = blockIdx.z;                               // pixel block of the tile
-  FwdWarpSmem& ws = wsmem[g];
-  const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+  FwdCtl& ctl = *reinterpret_cast<FwdCtl*>(smem_raw);
+  FwdBuf* const bufs = reinterpret_cast<FwdBuf*>(smem_raw + sizeof(FwdCtl));
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;  // warp 0 = consumer, 1..kProducers = producers
+  const int blk = blockIdx.x & 7;                              // pixel block of the tile
+  const int tile_x = blockIdx.x >> 3;
+  const int tile = blockIdx.y * (gridDim.x >> 3) + tile_x;
   const uint2 range = ranges[tile];
   const int len = (int)(range.y - range.x);
   const int nb = (len + 31) >> 5;
-  // checkpoint slots of this tile: one per segment start + one final (backward work items restart from them)
-  float4* const ck = ckpt + ((size_t)seg_off[tile] + tile) * 256 + blk * 32 + lane;
-  const int bx = blockIdx.x * GS_TILE + (blk & 1) * 8, by = blockIdx.y * GS_TILE + (blk >> 1) * 4;
+  const int bx = tile_x * GS_TILE + (blk & 1) * 8, by = blockIdx.y * GS_TILE + (blk >> 1) * 4;
   const int px = bx + (lane & 7), py = by + (lane >> 3);
   const bool inside = px < W && py < H;
-  const float pfx = (float)px, pfy = (float)py;
-  const float X0 = (float)bx, X1 = (float)(bx + 7), Y0 = (float)by, Y1 = (float)(by + 3);
-  if (g == 0) {
-    bs.T[lane] = 1.0f; bs.C0[lane] = 0.f; bs.C1[lane] = 0.f; bs.C2[lane] = 0.f;
-    bs.last[lane] = 0; bs.done[lane] = inside ? 0u : 1u;
-    if (lane == 0) {
-      bs.turn = 0;
-      for (int i = 0; i < kGroup; i++) mbar_init(&bs.bar[i], 1);
-      mbar_init(&bs.bar_fin, 1);
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-  }
-  __syncthreads();
-  uint32_t waits = 0;  // completed waits on this warp's barrier -> parity of the next one
-
 #ifdef GS_FWD_TRACE
+  __shared__ long long s_trace[512 * 8];
   const bool trace_on = len >= 6000 && blk == 3;
 #endif
-  const uint32_t* const tl = list + range.x;
-  Rec3 cur;
-  cur.a = cur.b = cur.c = make_float4(0.f, 0.f, 0.f, 0.f);
-  uint32_t id_next = 0;
-  {
-    const int e = g * 32 + lane;
-    if (e < len) cur = load_rec(rec, tl[e]);
-    if (e + kGroup * 32 < len) id_next = tl[e + kGroup * 32];
+  if (threadIdx.x == 0) {
+    ctl.done = 0;
+    for (int i = 0; i < kProducers; i++) { mbar_init(&ctl.full[i], 1); mbar_init(&ctl.empty[i], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  for (int b = g; b < nb; b += kGroup) {
-    if (turn_now(&bs.turn, lane) == kTurnDone) break;  // every pixel of the block has terminated
-    TRACE(b, 0);
-    const int e = b * 32 + lane;
-    bool keep = false;
-    if (e < len) {
-      keep = may_contribute(cur.a.x, cur.a.y, cur.b.x, cur.b.y, cur.b.z, cur.a.z, X0, X1, Y0, Y1);
-      ws.q0[lane] = make_float4(cur.a.x, cur.a.y, cur.b.x, cur.b.y);
-      ws.q1[lane] = make_float4(cur.b.z, cur.b.w, cur.c.x, cur.c.y);
-      ws.q2[lane] = cur.c.z;
-    }
-    // prefetch: records of this warp's next batch, indices of the one after
-    Rec3 nxt = cur;
-    if (e + kGroup * 32 < len) nxt = load_rec(rec, id_next);
-    uint32_t id_nn = 0;
-    if (e + 2 * kGroup * 32 < len) id_nn = tl[e + 2 * kGroup * 32];
-    __syncwarp();
-    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
-    // ---- parallel part: alpha of every survivor for this lane's pixel (reference tests, forward.cu:325-345) ----
+  __syncthreads();
+
+  if (wid > 0) {
+    // ------------------------------------------------ producer ------------------------------------------------
+    const int p = wid - 1;
+    FwdBuf& ws = bufs[p];
+    const float pfx = (float)px, pfy = (float)py;
+    const float X0 = (float)bx, X1 = (float)(bx + 7), Y0 = (float)by, Y1 = (float)(by + 3);
+    const uint32_t* const tl = list + range.x;
+    Rec3 cur;
+    cur.a = cur.b = cur.c = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint32_t id_next = 0;
     {
+      const int e = p * 32 + lane;
+      if (e < len) cur = load_rec(rec, tl[e]);
+      if (e + kProducers * 32 < len) id_next = tl[e + kProducers * 32];
+    }
+    uint32_t it = 0;
+    for (int b = p; b < nb; b += kProducers, it++) {
+      // software pipeline: records of this warp's next batch, list indices of the one after
+      const int e = b * 32 + lane;
+      Rec3 nxt = cur;
+      if (e + kProducers * 32 < len) nxt = load_rec(rec, id_next);
+      uint32_t id_nn = 0;
+      if (e + 2 * kProducers * 32 < len) id_nn = tl[e + 2 * kProducers * 32];
+      const bool keep = (e < len) && may_contribute(cur.a.x, cur.a.y, cur.b.x, cur.b.y, cur.b.z, cur.a.z, X0, X1, Y0, Y1);
+      if (it > 0) mbar_wait(&ctl.empty[p], (it - 1) & 1u);  // the consumer has finished with the previous rows
+      if (flag_now(&ctl.done, lane)) break;
+      TRACE(b, 0);
+      if (e < len) {
+        ws.q0[lane] = make_float4(cur.a.x, cur.a.y, cur.b.x, cur.b.y);
+        ws.q1[lane] = make_float4(cur.b.z, cur.b.w, cur.c.x, cur.c.y);
+        ws.q2[lane] = cur.c.z;
+      }
+      __syncwarp();
+      const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
       uint32_t m = mask;
       int k = 0;
       while (m) {
 #pragma unroll
-        for (int u = 0; u < kChunk; u++) {
+        for (int u = 0; u < kPChunk; u++) {
           const bool valid = m != 0;
           const int j = valid ? (__ffs(m) - 1) : 0;
           m &= m - 1;
@@ -220,93 +223,94 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x))), -0.5f,
                                         -__fmul_rn(dy, __fmul_rn(dx, q0.w)));  // SASS: FFMA q*-0.5 - cross
           const float alpha = fminf(0.99f, __fmul_rn(q1.y, gs_exp(power)));
-          const bool ok = !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-          if (valid) {
-            ws.alpha[k + u][lane] = ok ? alpha : 0.0f;
-            if (lane == 0) ws.row[k + u] = make_float4(q1.z, q1.w, ws.q2[j], __int_as_float(b * 32 + j + 1));
+          const bool ok = valid && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+          if (__any_sync(0xFFFFFFFFu, ok)) {  // rows no pixel of the block blends are dropped here, off the serial chain
+            ws.alpha[k][lane] = ok ? alpha : 0.0f;
+            if (lane == 0) ws.row[k] = make_float4(q1.z, q1.w, ws.q2[j], __int_as_float(b * 32 + j + 1));
+            k++;
           }
         }
-        k += kChunk;
       }
+      if (lane == 0) ws.cnt = (uint32_t)k;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ctl.full[p]);
+      TRACE(b, 1);
+      cur = nxt;
+      id_next = id_nn;
     }
-    // ---- serial part: wait for the block's turn, apply the survivors in list order, pass the turn on ----
-    TRACE(b, 1);
-    if (b > 0) { mbar_wait(&bs.bar[g], waits & 1u); waits++; }  // batch b-1 applied (or every pixel terminated)
-    __syncwarp();
-    if (turn_now(&bs.turn, lane) == kTurnDone) break;
-    TRACE(b, 2);
-    float T = bs.T[lane], C0 = bs.C0[lane], C1 = bs.C1[lane], C2 = bs.C2[lane];
-    uint32_t last = bs.last[lane];
-    bool done = bs.done[lane] != 0;
-    if ((b & (GS_SEG / 32 - 1)) == 0) ck[(size_t)(b / (GS_SEG / 32)) * 256] = make_float4(T, C0, C1, C2);
-    {
-      // rows 0..cnt-1 of ws.alpha / ws.row in list order: loads of a chunk are issued together, only the T chain is serial
-      const int cnt = __popc(mask);
-      __syncwarp();  // ws.row was written by lane 0
-      // The transmittance runs on unconditionally (one FMUL per survivor on the critical chain: a skipped entry multiplies
-      // by exactly 1.0f); the first entry that would push it below 1e-4 freezes a copy.  Same values, same order as
-      // forward.cu:335-361, but the compare no longer sits between two multiplies.
-      float Tr = T;
-      for (int k0 = 0; k0 < cnt; k0 += kChunk) {
-        float al[kChunk];
-        float4 rw[kChunk];
-#pragma unroll
-        for (int u = 0; u < kChunk; u++) {
-          const int k = k0 + u;  // <= 31 because cnt <= 32 and k0 is a multiple of kChunk
-          const float a_ = ws.alpha[k][lane];
-          al[u] = (k < cnt) ? a_ : 0.0f;
-          rw[u] = ws.row[k];
-        }
-#pragma unroll
-        for (int u = 0; u < kChunk; u++) {
-          const bool nz = al[u] != 0.0f;
-          const float m = nz ? __fsub_rn(1.0f, al[u]) : 1.0f;
-          const float test_T = __fmul_rn(Tr, m);
-          const bool term = nz && !done && (test_T < 0.0001f);
-          const bool ok = nz && !done && !term;
-          if (term) { T = Tr; done = true; }
-          if (ok) {
-            C0 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].x), C0);
-            C1 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].y), C1);
-            C2 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].z), C2);
-            last = (uint32_t)__float_as_int(rw[u].w);  // 1-based position in the tile list (contributor, forward.cu:328)
-          }
-          Tr = test_T;
-        }
-      }
-      if (!done) T = Tr;
-    }
-    bs.T[lane] = T; bs.C0[lane] = C0; bs.C1[lane] = C1; bs.C2[lane] = C2;
-    bs.last[lane] = last; bs.done[lane] = done ? 1u : 0u;
-    const bool all_done = __all_sync(0xFFFFFFFFu, done);
-    __syncwarp();
-    if (lane == 0) {
-      if (all_done) {
-        st_release_cta(&bs.turn, kTurnDone);
-        for (int i = 0; i < kGroup; i++) if (i != g) mbar_arrive(&bs.bar[i]);  // wake whoever waits; they see kTurnDone
-      } else {
-        mbar_arrive(&bs.bar[(g + 1) % kGroup]);
-      }
-      if (all_done || b == nb - 1) mbar_arrive(&bs.bar_fin);
-    }
-    TRACE(b, 3);
-    if (all_done) break;
-    cur = nxt;
-    id_next = id_nn;
+    return;
   }
-  if (g == 0) {  // the block's first warp waits for the last batch and writes the pixel results
-    if (nb > 0) mbar_wait(&bs.bar_fin, 0);
-    __syncwarp();
-    const float T = bs.T[lane], C0 = bs.C0[lane], C1 = bs.C1[lane], C2 = bs.C2[lane];
-    ck[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256] = make_float4(T, C0, C1, C2);
-    if (inside) {
-      const size_t pix = (size_t)py * W + px, hw = (size_t)H * W;
-      final_T[pix] = T;
-      n_contrib[pix] = bs.last[lane];
-      out_color[pix] = __fmaf_rn(T, bg[0], C0);
-      out_color[hw + pix] = __fmaf_rn(T, bg[1], C1);
-      out_color[2 * hw + pix] = __fmaf_rn(T, bg[2], C2);
+
+  // -------------------------------------------------- consumer --------------------------------------------------
+  // checkpoint slots of this tile: one per segment start + one final (backward work items restart from them)
+  float4* const ck = ckpt + ((size_t)seg_off[tile] + tile) * 256 + blk * 32 + lane;
+  float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
+  uint32_t last = 0;
+  bool done = !inside;
+  for (int b = 0; b < nb; b++) {
+    const int p = b % kProducers;
+    FwdBuf& ws = bufs[p];
+    TRACE(b, 2);
+    mbar_wait(&ctl.full[p], (uint32_t)(b / kProducers) & 1u);
+    TRACE(b, 3);
+    if ((b & (GS_SEG / 32 - 1)) == 0) ck[(size_t)(b / (GS_SEG / 32)) * 256] = make_float4(T, C0, C1, C2);
+    const int cnt = (int)ws.cnt;
+    // The transmittance runs on unconditionally (one FMUL per row on the critical chain: a skipped entry multiplies by
+    // exactly 1.0f); the first entry that would push it below 1e-4 freezes a copy.  Same values, same order as
+    // forward.cu:335-361, but the compare no longer sits between two multiplies.
+    float Tr = T;
+    for (int k0 = 0; k0 < cnt; k0 += kChunk) {
+      float al[kChunk];
+      float4 rw[kChunk];
+#pragma unroll
+      for (int u = 0; u < kChunk; u++) {
+        const int k = k0 + u;  // <= 31 because cnt <= 32 and k0 is a multiple of kChunk
+        const float a_ = ws.alpha[k][lane];
+        al[u] = (k < cnt) ? a_ : 0.0f;
+        rw[u] = ws.row[k];
+      }
+#pragma unroll
+      for (int u = 0; u < kChunk; u++) {
+        const bool nz = al[u] != 0.0f;
+        const float m = nz ? __fsub_rn(1.0f, al[u]) : 1.0f;
+        const float test_T = __fmul_rn(Tr, m);
+        const bool term = nz && !done && (test_T < 0.0001f);
+        const bool ok = nz && !done && !term;
+        if (term) { T = Tr; done = true; }
+        if (ok) {
+          C0 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].x), C0);
+          C1 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].y), C1);
+          C2 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].z), C2);
+          last = (uint32_t)__float_as_int(rw[u].w);  // 1-based position in the tile list (contributor, forward.cu:328)
+        }
+        Tr = test_T;
+      }
     }
+    if (!done) T = Tr;
+    const bool all_done = __all_sync(0xFFFFFFFFu, done);
+    if (lane == 0) {
+      if (all_done) {  // stop the producers: whoever waits on an empty barrier wakes and sees the flag
+        st_release_cta(&ctl.done, 1u);
+        for (int i = 0; i < kProducers; i++) mbar_arrive(&ctl.empty[i]);
+      } else {
+        mbar_arrive_relaxed(&ctl.empty[p]);
+      }
+    }
+    TRACE(b, 4);
+    if (all_done) break;
+  }
+#ifdef GS_FWD_TRACE
+  __syncwarp();
+  if (trace_on) for (int i = lane; i < 512 * 8; i += 32) g_fwd_trace[i] = s_trace[i];
+#endif
+  ck[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256] = make_float4(T, C0, C1, C2);
+  if (inside) {
+    const size_t pix = (size_t)py * W + px, hw = (size_t)H * W;
+    final_T[pix] = T;
+    n_contrib[pix] = last;
+    out_color[pix] = __fmaf_rn(T, bg[0], C0);
+    out_color[hw + pix] = __fmaf_rn(T, bg[1], C1);
+    out_color[2 * hw + pix] = __fmaf_rn(T, bg[2], C2);
   }
 }
 
@@ -498,8 +502,8 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 
 int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st) {
   dim3 grid((a.width + GS_TILE - 1) / GS_TILE, (a.height + GS_TILE - 1) / GS_TILE);
-  const size_t smem = sizeof(FwdBlockState) + kFwdWarps * sizeof(FwdWarpSmem);
-  grid.z = kWarps;  // one CTA per 8x4 pixel block of a tile
+  const size_t smem = sizeof(FwdCtl) + kProducers * sizeof(FwdBuf);
+  grid.x *= kWarps;  // one CTA per 8x4 pixel block of a tile (the 8 blocks of a tile are adjacent in launch order)
   static bool configured = false;
   if (!configured) {
     if (gs_check(cudaFuncSetAttribute(blend_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != GS_OK)

@@ -116,17 +116,25 @@ static inline __host__ size_t gs_carve_list(char* base, int64_t cap, int W, int 
   return (size_t)(p - base);
 }
 
-#define GS_SORT_ITEMS 16
+#define GS_SORT_ITEMS 16                                   // keys per thread, large inputs
+#define GS_SORT_ITEMS_SMALL 4                              // small inputs: more, shorter CTAs (latency-bound regime)
+#define GS_SORT_SMALL_MAX (1 << 19)                        // inputs up to this size use the small tile
 #define GS_SORT_THREADS 256
 #define GS_SORT_TILE (GS_SORT_ITEMS * GS_SORT_THREADS)   // 4096 keys per CTA
 #define GS_EMIT_THREADS 256
+
+static inline __host__ __device__ int gs_sort_items(unsigned long long n) { return n <= GS_SORT_SMALL_MAX ? GS_SORT_ITEMS_SMALL : GS_SORT_ITEMS; }
+static inline __host__ size_t gs_sort_blocks(unsigned long long n) {
+  const size_t tile = (size_t)gs_sort_items(n) * GS_SORT_THREADS;
+  return ((size_t)n + tile - 1) / tile;
+}
 
 static inline __host__ size_t gs_carve_scratch(char* base, int P, int W, int H, int64_t cap, GsScratch* s) {
   (void)W; (void)H;
   char* p = base;
   GsScratch t;
-  t.blocks_d = ((size_t)P + GS_SORT_TILE - 1) / GS_SORT_TILE + 1;
-  t.blocks_t = ((size_t)cap + GS_SORT_TILE - 1) / GS_SORT_TILE + 1;
+  t.blocks_d = gs_sort_blocks((unsigned long long)P) + 1;
+  t.blocks_t = gs_sort_blocks((unsigned long long)cap) + 1;
   t.blocks_e = ((size_t)P + GS_EMIT_THREADS - 1) / GS_EMIT_THREADS + 1;
   for (int i = 0; i < 2; i++) gs_carve(p, t.dkey[i], (size_t)P);
   for (int i = 0; i < 2; i++) gs_carve(p, t.dval[i], (size_t)P);

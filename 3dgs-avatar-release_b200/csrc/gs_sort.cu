@@ -28,6 +28,8 @@ __device__ __forceinline__ uint32_t ld_volatile(const uint32_t* p) { return *rei
 __device__ __forceinline__ void st_volatile(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
 
 // One stable 8-bit radix pass.  n is read from n_ptr when non-null (clipped to n_cap), else n = n_cap.
+// A pass whose digit is the same for every key (e.g. the top byte of avatar depths) degenerates to a straight copy.
+template <int ITEMS>
 __global__ void __launch_bounds__(GS_SORT_THREADS)
 onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
@@ -47,21 +49,33 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
   for (int i = 0; i < WARPS; i++) s_warp_hist[i][tid] = 0;
   __syncthreads();
   const uint32_t tile = s_ticket;
-  const unsigned long long base = (unsigned long long)tile * GS_SORT_TILE;
+  const unsigned long long base = (unsigned long long)tile * (ITEMS * GS_SORT_THREADS);
   if (base >= n) return;
 
-  // ---- load keys (warp-striped inside a warp-contiguous chunk) and rank them ----
-  uint32_t key[GS_SORT_ITEMS], val[GS_SORT_ITEMS], rank[GS_SORT_ITEMS];
-  const unsigned long long wbase = base + (unsigned long long)w * (32 * GS_SORT_ITEMS);
+  // ---- load keys (warp-striped inside a warp-contiguous chunk) ----
+  uint32_t key[ITEMS], val[ITEMS], rank[ITEMS];
+  const unsigned long long wbase = base + (unsigned long long)w * (32 * ITEMS);
 #pragma unroll
-  for (int i = 0; i < GS_SORT_ITEMS; i++) {
+  for (int i = 0; i < ITEMS; i++) {
     unsigned long long idx = wbase + i * 32 + lane;
     key[i] = idx < n ? keys_in[idx] : 0xFFFFFFFFu;
     val[i] = idx < n ? vals_in[idx] : 0u;  // payload loaded up front: its latency hides behind the ranking
   }
+  // constant digit: the pass is the identity permutation
+  if (__syncthreads_or((unsigned long long)hist[tid] == n)) {
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      unsigned long long idx = wbase + i * 32 + lane;
+      if (idx < n) {
+        if (keys_out) keys_out[idx] = key[i];
+        vals_out[idx] = val[i];
+      }
+    }
+    return;
+  }
   const uint32_t lt_mask = (1u << lane) - 1u;
 #pragma unroll
-  for (int i = 0; i < GS_SORT_ITEMS; i++) {
+  for (int i = 0; i < ITEMS; i++) {
     unsigned long long idx = wbase + i * 32 + lane;
     bool valid = idx < n;
     uint32_t digit = (key[i] >> shift) & 255u;
@@ -123,7 +137,7 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
 
   // ---- scatter ----
 #pragma unroll
-  for (int i = 0; i < GS_SORT_ITEMS; i++) {
+  for (int i = 0; i < ITEMS; i++) {
     unsigned long long idx = wbase + i * 32 + lane;
     if (idx < n) {
       uint32_t digit = (key[i] >> shift) & 255u;
@@ -305,9 +319,11 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   const int gx = (a.width + GS_TILE - 1) / GS_TILE, gy = (a.height + GS_TILE - 1) / GS_TILE;
   const int tiles = gx * gy;
   // 1. depth sort of the P Gaussians: 4 passes, dkey/dval ping-pong, ends in buffer 0
-  const int blocks_d = (P + GS_SORT_TILE - 1) / GS_SORT_TILE;
+  const int blocks_d = (int)gs_sort_blocks((unsigned long long)P);
+  const bool small_d = gs_sort_items((unsigned long long)P) == GS_SORT_ITEMS_SMALL;
   for (int p = 0; p < 4; p++) {
-    onesweep_pass_kernel<<<blocks_d, GS_SORT_THREADS, 0, st>>>(
+    auto kern = small_d ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL> : onesweep_pass_kernel<GS_SORT_ITEMS>;
+    kern<<<blocks_d, GS_SORT_THREADS, 0, st>>>(
         s.dkey[p & 1], s.dkey[(p + 1) & 1], s.dval[p & 1], s.dval[(p + 1) & 1], nullptr, (unsigned long long)P, 8 * p,
         s.hist + p * 256, s.status_d + (size_t)p * s.blocks_d * 256, s.counters + p, &g.hdr->error);
   }
@@ -323,15 +339,17 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
                                                     s.tkey[0], vbuf[0], s.hist + 4 * 256, tile_passes, s.scan_status,
                                                     s.counters + 8, g.hdr);
   // 3. stable sort of the pairs by tile id
-  const int blocks_t = (int)((cap + GS_SORT_TILE - 1) / GS_SORT_TILE);
+  const int blocks_t = (int)gs_sort_blocks((unsigned long long)cap);
+  const bool small_t = gs_sort_items((unsigned long long)cap) == GS_SORT_ITEMS_SMALL;
   for (int p = 0; p < tile_passes; p++) {
     uint32_t* vout = (p == tile_passes - 1) ? list : vbuf[(p + 1) & 1];
-    onesweep_pass_kernel<<<blocks_t, GS_SORT_THREADS, 0, st>>>(
+    auto kern = small_t ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL> : onesweep_pass_kernel<GS_SORT_ITEMS>;
+    kern<<<blocks_t, GS_SORT_THREADS, 0, st>>>(
         s.tkey[p & 1], s.tkey[(p + 1) & 1], vbuf[p & 1], vout, &g.hdr->num_rendered, (unsigned long long)cap, 8 * p,
         s.hist + (4 + p) * 256, s.status_t + (size_t)p * s.blocks_t * 256, s.counters + 4 + p, &g.hdr->error);
   }
   // 4. tile ranges
-  int rb = blocks_t * (GS_SORT_TILE / 256);
+  int rb = (int)((cap + 255) / 256);
   if (rb > 148 * 16) rb = 148 * 16;
   if (rb < 1) rb = 1;
   tile_ranges_kernel<<<rb, 256, 0, st>>>(s.tkey[tile_passes & 1], &g.hdr->num_rendered, (unsigned long long)cap, im.ranges);

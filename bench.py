@@ -24,6 +24,9 @@ for _p in (os.path.join(ROOT, "3dgs-avatar-release_b200"), ROOT):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+    os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line (NCCL prints its version banner there)
+
 import numpy as np
 import torch
 
