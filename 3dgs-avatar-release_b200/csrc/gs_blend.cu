@@ -151,18 +151,19 @@ __global__ void __launch_bounds__(kFwdWarps * 32)
 blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H,
                  const GsRec* __restrict__ rec, const float* __restrict__ bg, float* __restrict__ final_T,
                  uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
-                 const uint32_t* __restrict__ seg_off, float4* __restrict__ ckpt) {
+                 const uint32_t* __restrict__ seg_off, float4* __restrict__ ckpt, const uint32_t* __restrict__ order,
+                 int grid_x) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FwdCtl& ctl = *reinterpret_cast<FwdCtl*>(smem_raw);
   FwdBuf* const bufs = reinterpret_cast<FwdBuf*>(smem_raw + sizeof(FwdCtl));
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;  // warp 0 = consumer, 1..kProducers = producers
   const int blk = blockIdx.x & 7;                              // pixel block of the tile
-  const int tile_x = blockIdx.x >> 3;
-  const int tile = blockIdx.y * (gridDim.x >> 3) + tile_x;
+  const int tile = (int)order[blockIdx.x >> 3];                // longest lists first
+  const int tile_x = tile % grid_x, tile_y = tile / grid_x;
   const uint2 range = ranges[tile];
   const int len = (int)(range.y - range.x);
   const int nb = (len + 31) >> 5;
-  const int bx = tile_x * GS_TILE + (blk & 1) * 8, by = blockIdx.y * GS_TILE + (blk >> 1) * 4;
+  const int bx = tile_x * GS_TILE + (blk & 1) * 8, by = tile_y * GS_TILE + (blk >> 1) * 4;
   const int px = bx + (lane & 7), py = by + (lane >> 3);
   const bool inside = px < W && py < H;
 #ifdef GS_FWD_TRACE
@@ -503,7 +504,8 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st) {
   dim3 grid((a.width + GS_TILE - 1) / GS_TILE, (a.height + GS_TILE - 1) / GS_TILE);
   const size_t smem = sizeof(FwdCtl) + kProducers * sizeof(FwdBuf);
-  grid.x *= kWarps;  // one CTA per 8x4 pixel block of a tile (the 8 blocks of a tile are adjacent in launch order)
+  const int gx = (int)grid.x;
+  grid = dim3(grid.x * grid.y * kWarps);  // one CTA per 8x4 pixel block of a tile, tiles in im.order
   static bool configured = false;
   if (!configured) {
     if (gs_check(cudaFuncSetAttribute(blend_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != GS_OK)
@@ -511,7 +513,7 @@ int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& 
     configured = true;
   }
   blend_fwd_kernel<<<grid, kFwdWarps * 32, smem, st>>>(im.ranges, l.point_list, a.width, a.height, g.rec, a.background,
-                                                       im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt);
+                                                       im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt, im.order, gx);
   return gs_check(cudaGetLastError());
 }
 

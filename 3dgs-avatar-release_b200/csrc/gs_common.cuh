@@ -45,6 +45,7 @@ struct GsImage {
   uint32_t* n_contrib;      // [H*W]
   float* final_T;           // [H*W]
   uint32_t* seg_off;        // [tiles+1] exclusive prefix of ceil(len/GS_SEG) over tiles; [tiles] = number of work items
+  uint32_t* order;          // [tiles] tile ids, longest lists first (launch order of the forward blend)
 };
 
 // The pair-capacity-sized workspace kept for backward (the reference's binningBuffer).
@@ -100,6 +101,7 @@ static inline __host__ size_t gs_carve_image(char* base, int W, int H, GsImage* 
   gs_carve(p, t.n_contrib, (size_t)W * H);
   gs_carve(p, t.final_T, (size_t)W * H);
   gs_carve(p, t.seg_off, tiles + 1);
+  gs_carve(p, t.order, tiles);
   if (im) *im = t;
   return (size_t)(p - base);
 }

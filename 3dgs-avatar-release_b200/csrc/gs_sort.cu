@@ -261,16 +261,22 @@ __global__ void tile_ranges_kernel(const uint32_t* __restrict__ tkey_sorted, con
 // of the segment counts over tiles (seg_off[tiles] = number of items), items[] = (tile, segment).  One CTA.
 __global__ void __launch_bounds__(1024)
 plan_kernel(int tiles, const uint2* __restrict__ ranges, uint32_t* __restrict__ seg_off, uint2* __restrict__ items,
-            uint32_t max_items) {
+            uint32_t max_items, uint32_t* __restrict__ order) {
   __shared__ uint32_t s_w[32];
   __shared__ uint32_t s_carry;
+  __shared__ uint32_t s_bucket[33], s_cursor[33];
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   if (tid == 0) s_carry = 0;
+  if (tid < 33) s_bucket[tid] = 0;
   __syncthreads();
   for (int t0 = 0; t0 < tiles; t0 += 1024) {
     const int t = t0 + tid;
     uint32_t nseg = 0;
-    if (t < tiles) { uint2 r = ranges[t]; nseg = (r.y - r.x + GS_SEG - 1) / GS_SEG; }
+    if (t < tiles) {
+      uint2 r = ranges[t];
+      nseg = (r.y - r.x + GS_SEG - 1) / GS_SEG;
+      atomicAdd(&s_bucket[32 - __clz(r.y - r.x)], 1u);  // length class = bit length of the list length
+    }
     uint32_t incl = nseg;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -298,6 +304,17 @@ plan_kernel(int tiles, const uint2* __restrict__ ranges, uint32_t* __restrict__ 
     __syncthreads();
   }
   if (tid == 0) seg_off[tiles] = s_carry < max_items ? s_carry : max_items;
+  // launch order of the forward blend: longest lists first (bucketed by bit length), so that the deep tiles -- the
+  // critical path of avatar frames -- start in the first wave
+  if (tid == 0) {
+    uint32_t run = 0;
+    for (int bk = 32; bk >= 0; bk--) { s_cursor[bk] = run; run += s_bucket[bk]; }
+  }
+  __syncthreads();
+  for (int t = tid; t < tiles; t += 1024) {
+    uint2 r = ranges[t];
+    order[atomicAdd(&s_cursor[32 - __clz(r.y - r.x)], 1u)] = (uint32_t)t;
+  }
 }
 
 uint32_t higher_msb(uint32_t n) {  // rasterizer_impl.cu:35-50
@@ -354,6 +371,6 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   if (rb < 1) rb = 1;
   tile_ranges_kernel<<<rb, 256, 0, st>>>(s.tkey[tile_passes & 1], &g.hdr->num_rendered, (unsigned long long)cap, im.ranges);
   // 5. backward work plan (segments of GS_SEG entries per tile)
-  plan_kernel<<<1, 1024, 0, st>>>(tiles, im.ranges, im.seg_off, l.items, (uint32_t)l.max_items);
+  plan_kernel<<<1, 1024, 0, st>>>(tiles, im.ranges, im.seg_off, l.items, (uint32_t)l.max_items, im.order);
   return gs_check(cudaGetLastError());
 }
