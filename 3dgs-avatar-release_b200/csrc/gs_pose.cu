@@ -72,12 +72,36 @@ struct PoseCore {
   float xb[3];             // posed mean
 };
 
+// Per-warp coalesced staging of the SH rows of the warp's 32 Gaussians (a contiguous chunk of up to 32*45 floats): 45
+// independent coalesced loads in flight per lane instead of 45 dependent-latency strided ones; the rows are then read
+// back lane-private with an odd stride (conflict-free).
+#define POSE_MAXREST 45
+__device__ __forceinline__ void warp_stage_in(float* __restrict__ s, const float* __restrict__ g, int n, int lane) {
+  float v[POSE_MAXREST];
+#pragma unroll
+  for (int k = 0; k < POSE_MAXREST; k++) { const int e = k * 32 + lane; v[k] = e < n ? __ldg(g + e) : 0.f; }
+#pragma unroll
+  for (int k = 0; k < POSE_MAXREST; k++) { const int e = k * 32 + lane; if (e < n) s[e] = v[k]; }
+  __syncwarp();
+}
+__device__ __forceinline__ void warp_stage_out(float* __restrict__ g, const float* __restrict__ s, int n, int lane) {
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < POSE_MAXREST; k++) { const int e = k * 32 + lane; if (e < n) g[e] = s[e]; }
+  __syncwarp();
+}
+
 __device__ __forceinline__ void pose_core(const PoseArgs& a, int i, const float* __restrict__ s_bones, PoseCore& c) {
   float T[12];
 #pragma unroll
   for (int k = 0; k < 12; k++) T[k] = 0.f;
-  const float* w = a.weights + (size_t)i * 24;
-#pragma unroll 4
+  float w[24];
+  {
+    const float4* wp = reinterpret_cast<const float4*>(a.weights + (size_t)i * 24);  // 96-byte rows: 16-byte aligned
+#pragma unroll
+    for (int k = 0; k < 6; k++) { const float4 t = __ldg(wp + k); w[4 * k] = t.x; w[4 * k + 1] = t.y; w[4 * k + 2] = t.z; w[4 * k + 3] = t.w; }
+  }
+#pragma unroll
   for (int j = 0; j < 24; j++) {
     const float wj = w[j];
 #pragma unroll
@@ -117,8 +141,9 @@ __device__ __forceinline__ void view_dir(const PoseArgs& a, const PoseCore& c, c
   n = sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
 }
 
-__device__ __forceinline__ float sh_coef(const PoseArgs& a, int i, int k, int ch) {
-  return k == 0 ? a.features_dc[3 * (size_t)i + ch] : a.features_rest[((size_t)i * (a.M - 1) + (k - 1)) * 3 + ch];
+// SH coefficient k of channel ch: dc from global (12 B per thread), the rest from this lane's staged row
+__device__ __forceinline__ float sh_coef(const PoseArgs& a, int i, const float* __restrict__ rest_row, int k, int ch) {
+  return k == 0 ? a.features_dc[3 * (size_t)i + ch] : rest_row[(k - 1) * 3 + ch];
 }
 
 __global__ void __launch_bounds__(128) pose_fwd_kernel(PoseArgs a) {
@@ -126,8 +151,16 @@ __global__ void __launch_bounds__(128) pose_fwd_kernel(PoseArgs a) {
   __shared__ float s_cam[3];
   for (int k = threadIdx.x; k < 24 * 16; k += blockDim.x) s_bones[k] = a.bone_transforms[k];
   if (threadIdx.x < 3) s_cam[threadIdx.x] = a.camera_center[threadIdx.x];
+  __shared__ float s_rest_all[4][32 * POSE_MAXREST];
   __syncthreads();
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.P; i += gridDim.x * blockDim.x) {
+  const int lane = threadIdx.x & 31;
+  float* const s_rest = s_rest_all[threadIdx.x >> 5];
+  const int nrest = (a.M - 1) * 3;  // floats per Gaussian in features_rest (<= 45)
+  for (int i0 = blockIdx.x * blockDim.x + threadIdx.x - lane; i0 < a.P; i0 += gridDim.x * blockDim.x) {  // warp-uniform
+    const int i = i0 + lane;
+    if (nrest) warp_stage_in(s_rest, a.features_rest + (size_t)i0 * nrest, min(32, a.P - i0) * nrest, lane);
+    const float* rest_row = s_rest + lane * nrest;
+    if (i < a.P) {
     PoseCore c;
     pose_core(a, i, s_bones, c);
     a.means3D[3 * (size_t)i] = c.xb[0]; a.means3D[3 * (size_t)i + 1] = c.xb[1]; a.means3D[3 * (size_t)i + 2] = c.xb[2];
@@ -153,7 +186,7 @@ __global__ void __launch_bounds__(128) pose_fwd_kernel(PoseArgs a) {
 #pragma unroll
     for (int ch = 0; ch < 3; ch++) {
       float acc = 0.f;
-      for (int k = 0; k < nb; k++) acc += b[k] * sh_coef(a, i, k, ch);
+      for (int k = 0; k < nb; k++) acc += b[k] * sh_coef(a, i, rest_row, k, ch);
       a.colors[3 * (size_t)i + ch] = fmaxf(acc + 0.5f, 0.0f);
     }
     if (a.T_fwd) {
@@ -174,6 +207,8 @@ __global__ void __launch_bounds__(128) pose_fwd_kernel(PoseArgs a) {
 #pragma unroll
         for (int k = 0; k < 3; k++) a.rotation_bar[9 * (size_t)i + 3 * r + k] = c.Rb[r][k];
     }
+    }  // i < P
+    __syncwarp();  // rows are re-staged in the next iteration
   }
 }
 
@@ -183,8 +218,17 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
   __shared__ float s_cam[3];
   for (int k = threadIdx.x; k < 24 * 16; k += blockDim.x) s_bones[k] = a.bone_transforms[k];
   if (threadIdx.x < 3) s_cam[threadIdx.x] = a.camera_center[threadIdx.x];
+  __shared__ float s_rest_all[4][32 * POSE_MAXREST];  // SH coefficients in, their gradients out
   __syncthreads();
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.P; i += gridDim.x * blockDim.x) {
+  const int lane = threadIdx.x & 31;
+  float* const s_rest = s_rest_all[threadIdx.x >> 5];
+  const int nrest = (a.M - 1) * 3;
+  for (int i0 = blockIdx.x * blockDim.x + threadIdx.x - lane; i0 < a.P; i0 += gridDim.x * blockDim.x) {  // warp-uniform
+    const int i = i0 + lane;
+    const int nstaged = min(32, a.P - i0) * nrest;
+    if (nrest) warp_stage_in(s_rest, a.features_rest + (size_t)i0 * nrest, nstaged, lane);
+    float* rest_row = s_rest + lane * nrest;
+    if (i < a.P) {
     PoseCore c;
     pose_core(a, i, s_bones, c);
     float gxb[3] = {ba.dL_dmeans3D[3 * (size_t)i], ba.dL_dmeans3D[3 * (size_t)i + 1], ba.dL_dmeans3D[3 * (size_t)i + 2]};
@@ -202,12 +246,12 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
 #pragma unroll
       for (int ch = 0; ch < 3; ch++) {
         float acc = 0.f;
-        for (int k = 0; k < nb; k++) acc += b[k] * sh_coef(a, i, k, ch);
+        for (int k = 0; k < nb; k++) acc += b[k] * sh_coef(a, i, rest_row, k, ch);
         const float gc = (acc + 0.5f < 0.0f) ? 0.f : ba.dL_dcolors[3 * (size_t)i + ch];
         ba.dL_dfeatures_dc[3 * (size_t)i + ch] = b[0] * gc;
         for (int k = 1; k < a.M; k++) {
-          const float coef = k < nb ? sh_coef(a, i, k, ch) : 0.f;
-          ba.dL_dfeatures_rest[((size_t)i * (a.M - 1) + (k - 1)) * 3 + ch] = k < nb ? b[k] * gc : 0.f;
+          const float coef = k < nb ? rest_row[(k - 1) * 3 + ch] : 0.f;
+          rest_row[(k - 1) * 3 + ch] = k < nb ? b[k] * gc : 0.f;  // the staged coefficient is consumed: its slot takes the gradient
           if (k < nb) { gu[0] += bx[k] * coef * gc; gu[1] += by[k] * coef * gc; gu[2] += bz[k] * coef * gc; }
         }
       }
@@ -286,6 +330,8 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
         gw[j] = acc;
       }
     }
+    }  // i < P
+    if (nrest) warp_stage_out(ba.dL_dfeatures_rest + (size_t)i0 * nrest, s_rest, nstaged, lane);
   }
 }
 
