@@ -132,6 +132,16 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t pari
       "DONE_%=:\n"
       "}\n" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
 }
+__device__ __forceinline__ bool mbar_try_wait(unsigned long long* bar, uint32_t parity) {  // bounded suspend, then returns
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.acquire.cta.shared::cta.b64 p, [%1], %2, %3;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n" : "=r"(ok) : "r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity), "r"(1000u) : "memory");
+  return ok != 0;
+}
 // warp-uniform read of a shared flag: lane 0 loads (acquire), the value is broadcast
 __device__ __forceinline__ uint32_t flag_now(const uint32_t* f, int lane) {
   uint32_t t = 0;
@@ -201,7 +211,14 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       uint32_t id_nn = 0;
       if (e + 2 * kProducers * 32 < len) id_nn = tl[e + 2 * kProducers * 32];
       const bool keep = (e < len) && may_contribute(cur.a.x, cur.a.y, cur.b.x, cur.b.y, cur.b.z, cur.a.z, X0, X1, Y0, Y1);
-      if (it > 0) mbar_wait(&ctl.empty[p], (it - 1) & 1u);  // the consumer has finished with the previous rows
+      // the consumer has finished with the previous rows -- or every pixel has terminated: the flag is polled inside the
+      // wait because the consumer's wake-up arrivals at termination can put the barrier two phases ahead (parity alias)
+      if (it > 0) {
+        while (!mbar_try_wait(&ctl.empty[p], (it - 1) & 1u)) {
+          if (ld_acquire_cta(&ctl.done)) break;
+        }
+      }
+      __syncwarp();
       if (flag_now(&ctl.done, lane)) break;
       TRACE(b, 0);
       if (e < len) {

@@ -118,3 +118,80 @@ def test_lower_sh_degrees(built_lib, deg):
     fw = scenes.oracle_forward(sc, sh_degree=deg)
     out = run_cuda(sc, sh_degree=deg)
     check_forward_exact(fw, out)
+
+
+def test_bench_config_50k_512(built_lib):
+    """BASELINE.json configs[1]/[2] at full size (50k random-init Gaussians, 512x512): every integer artefact and the image
+    bit-exact vs the oracle, gradients <= 1e-4 relative."""
+    from oracle import gs_oracle
+    sc = scenes.avatar_scene(P=50000, W=512, H=512, random_init=True)
+    fw = scenes.oracle_forward(sc)
+    dL = scenes.l1_grad(fw["color"])
+    out = run_cuda(sc, dL=dL)
+    check_forward_exact(fw, out)
+    bw = gs_oracle.backward(fw, dL)
+    g = out["grads"]
+    for k, v in (("means3D", "dL_dmeans3D"), ("means2D", "dL_dmeans2D"), ("colors_precomp", "dL_dcolors"),
+                 ("opacities", "dL_dopacity"), ("cov3D_precomp", "dL_dcov3D")):
+        assert rel_err(g[k], bw[v]) <= 1e-4, k
+
+
+def test_trained_like_opaque_scene(built_lib):
+    """High-opacity Gaussians: pixels terminate early (T < 1e-4), exercising the done / early-exit paths of the pipelined
+    forward and the checkpoint restarts of the segmented backward."""
+    from oracle import gs_oracle
+    sc = scenes.avatar_scene(P=30000, W=256, H=256)
+    sc["opacities"] = np.clip(sc["opacities"] * 0 + 0.97, 0, 1).astype(np.float32)
+    sc["cov3D_precomp"] = (sc["cov3D_precomp"] * 9.0).astype(np.float32)  # 3x larger splats: deep, opaque lists
+    fw = scenes.oracle_forward(sc)
+    assert (fw["final_T"] < 1e-3).sum() > 1000 and (fw["ranges"][:, 1] - fw["ranges"][:, 0]).max() > 4 * 256
+    dL = scenes.l1_grad(fw["color"])
+    out = run_cuda(sc, dL=dL)
+    check_forward_exact(fw, out)
+    bw = gs_oracle.backward(fw, dL)
+    g = out["grads"]
+    for k, v in (("means3D", "dL_dmeans3D"), ("means2D", "dL_dmeans2D"), ("colors_precomp", "dL_dcolors"),
+                 ("opacities", "dL_dopacity"), ("cov3D_precomp", "dL_dcov3D")):
+        assert rel_err(g[k], bw[v]) <= 1e-4, k
+
+
+def test_stress_1m_1080p_properties(built_lib):
+    """BASELINE.json configs[4] size (1M Gaussians, 1920x1080): size-independent properties instead of the oracle --
+    sortedness of the (tile | depth) keys, ranges partition the list, sum(tiles_touched) = N, contributor counts within the
+    tile lists, run-to-run bit-identical forward, finite gradients."""
+    from diff_gaussian_rasterization import _C
+    rng = np.random.default_rng(0)
+    P, W, H = 1_000_000, 1920, 1080
+    import synth
+    cam = synth.camera(W=W, H=H, fx=1600.0, fy=1600.0, dist=3.5)
+    means = (rng.normal(0, 1, size=(P, 3)) * np.array([1.2, 0.7, 0.5]) + np.array([0, 0.9, 0])).astype(np.float32)
+    s = np.exp(rng.uniform(-6.0, -4.3, size=(P, 3))).astype(np.float32)
+    q = rng.normal(size=(P, 4)).astype(np.float32)
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    sc = dict(cam=cam, W=W, H=H, bg=np.array([0.1, 0.2, 0.3], np.float32), means3D=means, scales=s, rotations=q,
+              opacities=rng.uniform(0.05, 0.9, size=(P, 1)).astype(np.float32),
+              colors_precomp=rng.uniform(0, 1, size=(P, 3)).astype(np.float32))
+    dL = (rng.normal(size=(3, H, W)) / (3 * H * W)).astype(np.float32)
+    out = run_cuda(sc, dL=dL)
+    N, dbg = out["N"], out["dbg"]
+    assert N > 2_000_000
+    keys = dbg["keys"].view(np.uint64)
+    assert np.all(keys[1:] >= keys[:-1]), "keys not sorted"
+    assert int(dbg["tiles_touched"].view(np.uint32).astype(np.int64).sum()) == N
+    ranges = dbg["ranges"].view(np.uint32).reshape(-1, 2).astype(np.int64)
+    ne = ranges[ranges[:, 1] > ranges[:, 0]]
+    assert ne[0, 0] == 0 and ne[-1, 1] == N and np.all(ne[1:, 0] == ne[:-1, 1]), "ranges do not partition the list"
+    tiles_of_keys = (keys >> np.uint64(32)).astype(np.int64)
+    tix = np.nonzero(ranges[:, 1] > ranges[:, 0])[0]
+    assert np.all(tiles_of_keys[ne[:, 0]] == tix) and np.all(tiles_of_keys[ne[:, 1] - 1] == tix)
+    gx = (W + 15) // 16
+    ncon = dbg["n_contrib"].view(np.uint32).reshape(H, W).astype(np.int64)
+    lens = (ranges[:, 1] - ranges[:, 0]).reshape(-1, gx)
+    assert np.all(ncon <= np.kron(lens, np.ones((16, 16), np.int64))[:H, :W])
+    assert np.isfinite(out["img"]).all() and out["img"].min() >= 0
+    for k, v in out["grads"].items():
+        if v is not None:
+            assert np.isfinite(v).all(), k
+    out2 = run_cuda(sc)
+    assert np.array_equal(out2["img"].view(np.uint32), out["img"].view(np.uint32)), "forward not run-to-run identical"
+    assert out2["N"] == N and np.array_equal(out2["dbg"]["point_list"], dbg["point_list"])
