@@ -1,0 +1,352 @@
+// gs_nonrigid.cu -- non-rigid deformation of the canonical Gaussians: multiresolution hash-grid encoding + conditional
+// MLP + delta application (replaces HashGridwithMLP.forward, models/deformer/non_rigid.py:226-286; see
+// include/gsplat_b200.h for the reference lines of every piece).
+//
+// The MLP is the only dense contraction of the hot path and the only place tensor cores are used: one CTA owns a tile
+// of 128 Gaussians (= the M dimension of a 128xNx16 tcgen05.mma), activations and weights sit in shared memory in the
+// canonical K-major no-swizzle core-matrix layout, accumulators live in TMEM, one elected thread issues the MMAs, and
+// the epilogue (tcgen05.ld -> bias -> LeakyReLU -> BF16 hi/lo split) writes the next layer's A operand straight back
+// into shared memory.  FP32 fidelity comes from a 2-way BF16 split of both operands (hi*hi + lo*hi + hi*lo).
+#include <cuda_bf16.h>
+
+#include "gs_common.cuh"
+
+namespace {
+
+constexpr int NR_TILE = 128;   // Gaussians per CTA = UMMA M
+constexpr int NR_H = 128;      // hidden width
+constexpr int NR_F = 32;       // hash-grid features (16 levels x 2), K of layer 0
+
+// element index of (row, k) in the canonical K-major no-swizzle layout of a [ROWS x K] BF16 operand:
+// core matrix = 8 rows x 16 bytes; core matrices of one 8-wide K slab are contiguous over the rows (SBO = 128 B),
+// consecutive K slabs are ROWS*16 bytes apart (LBO).
+__host__ __device__ inline int core_idx(int row, int k, int rows) { return (k >> 3) * (rows * 8) + row * 8 + (k & 7); }
+
+struct NrWs {  // prepared once per call by nr_prep_kernel
+  __nv_bfloat16 *w0_hi, *w0_lo;  // [128 x 32]
+  __nv_bfloat16 *w1_hi, *w1_lo;  // [128 x 128]
+  __nv_bfloat16 *w2_hi, *w2_lo;
+  __nv_bfloat16 *w3_hi, *w3_lo;  // [NOUT_PAD x 128]
+  float* bias0;                  // [128] b0 + W0[:, F:] . cond
+};
+
+__host__ inline int nout_pad(int n_out) { return n_out <= 16 ? 16 : 32; }
+
+__host__ size_t carve_ws(char* base, int n_out, NrWs* w) {
+  char* p = base;
+  NrWs t;
+  const size_t np = (size_t)nout_pad(n_out);
+  gs_carve(p, t.w0_hi, (size_t)NR_H * NR_F); gs_carve(p, t.w0_lo, (size_t)NR_H * NR_F);
+  gs_carve(p, t.w1_hi, (size_t)NR_H * NR_H); gs_carve(p, t.w1_lo, (size_t)NR_H * NR_H);
+  gs_carve(p, t.w2_hi, (size_t)NR_H * NR_H); gs_carve(p, t.w2_lo, (size_t)NR_H * NR_H);
+  gs_carve(p, t.w3_hi, np * NR_H); gs_carve(p, t.w3_lo, np * NR_H);
+  gs_carve(p, t.bias0, (size_t)NR_H);
+  if (w) *w = t;
+  return (size_t)(p - base);
+}
+
+__device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+  hi = __float2bfloat16_rn(v);
+  lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+}
+
+// Weights -> BF16 hi/lo in the operand layout; condition folded into the first bias.
+__global__ void nr_prep_kernel(NonRigidArgs a, NrWs w, int npad) {
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+  const int in0 = NR_F + a.n_cond;
+  for (int e = tid; e < NR_H * NR_F; e += nth) {
+    const int n = e / NR_F, k = e % NR_F;
+    split_bf16(a.W0[(size_t)n * in0 + k], w.w0_hi[core_idx(n, k, NR_H)], w.w0_lo[core_idx(n, k, NR_H)]);
+  }
+  for (int e = tid; e < NR_H * NR_H; e += nth) {
+    const int n = e / NR_H, k = e % NR_H;
+    split_bf16(a.W1[e], w.w1_hi[core_idx(n, k, NR_H)], w.w1_lo[core_idx(n, k, NR_H)]);
+    split_bf16(a.W2[e], w.w2_hi[core_idx(n, k, NR_H)], w.w2_lo[core_idx(n, k, NR_H)]);
+  }
+  for (int e = tid; e < npad * NR_H; e += nth) {
+    const int n = e / NR_H, k = e % NR_H;
+    const float v = n < a.n_out ? a.W3[(size_t)n * NR_H + k] : 0.f;
+    split_bf16(v, w.w3_hi[core_idx(n, k, npad)], w.w3_lo[core_idx(n, k, npad)]);
+  }
+  for (int n = tid; n < NR_H; n += nth) {
+    float acc = a.b0[n];
+    for (int c = 0; c < a.n_cond; c++) acc = fmaf(a.W0[(size_t)n * in0 + NR_F + c], a.cond[c], acc);
+    w.bias0[n] = acc;
+  }
+}
+
+// ---- multiresolution hash encoding (Mueller et al. 2022, as implemented by tiny-cuda-nn's GridEncoding) ----
+__device__ __forceinline__ uint32_t grid_index(uint32_t x, uint32_t y, uint32_t z, uint32_t res, uint32_t size) {
+  uint32_t stride = 1, index = 0;
+  const uint32_t pos[3] = {x, y, z};
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    if (stride <= size) { index += pos[d] * stride; stride *= res; }
+  }
+  if (size < stride) index = x ^ (y * 2654435761u) ^ (z * 805459861u);
+  return index % size;
+}
+
+__device__ __forceinline__ void hash_encode(const NonRigidArgs& a, float x, float y, float z, float* feat /*[2L]*/) {
+  for (int l = 0; l < a.n_levels; l++) {
+    const float scale = a.level_scale[l];
+    const uint32_t res = a.level_res[l];
+    const uint32_t off = a.level_offset[l], size = a.level_offset[l + 1] - off;
+    const float px = fmaf(x, scale, 0.5f), py = fmaf(y, scale, 0.5f), pz = fmaf(z, scale, 0.5f);
+    const float fx0 = floorf(px), fy0 = floorf(py), fz0 = floorf(pz);
+    const float wx = px - fx0, wy = py - fy0, wz = pz - fz0;
+    const uint32_t gx = (uint32_t)(int)fx0, gy = (uint32_t)(int)fy0, gz = (uint32_t)(int)fz0;
+    float f0 = 0.f, f1 = 0.f;
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+      const uint32_t dx = c & 1, dy = (c >> 1) & 1, dz = (c >> 2) & 1;
+      const float wgt = (dx ? wx : 1.f - wx) * (dy ? wy : 1.f - wy) * (dz ? wz : 1.f - wz);
+      const uint32_t idx = grid_index(gx + dx, gy + dy, gz + dz, res, size);
+      const float2 v = __ldg(reinterpret_cast<const float2*>(a.table) + off + idx);
+      f0 = fmaf(wgt, v.x, f0);
+      f1 = fmaf(wgt, v.y, f1);
+    }
+    feat[2 * l] = f0;
+    feat[2 * l + 1] = f1;
+  }
+}
+
+// ---- tcgen05 / TMEM / mbarrier wrappers (PTX) ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// shared-memory matrix descriptor, K-major, no swizzle (cute/arch/mma_sm100_desc.hpp: SmemDescriptor):
+// [0,14) start>>4 | [16,30) LBO>>4 (K-slab stride) | [32,46) SBO>>4 (8-row group stride) | [46,48) version = 1
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
+         (1ull << 46);
+}
+// instruction descriptor, kind::f16 (InstrDescriptor): D = F32 [4,6)=1, A = B = BF16 [7,10)=[10,13)=1, K-major both,
+// N>>3 at [17,23), M>>4 at [24,29)
+__device__ __forceinline__ uint32_t umma_idesc(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(unsigned long long* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void nr_mbar_init(unsigned long long* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void nr_mbar_wait(unsigned long long* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "NRW_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra NRD_%=;\n"
+      "bra NRW_%=;\n"
+      "NRD_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {  // 32 lanes x 32 columns: lane = this thread's row
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
+}
+
+// stores 8 consecutive-k activations of one row (one 16-byte core-matrix row) as BF16 hi and lo
+__device__ __forceinline__ void store_act8(__nv_bfloat16* A_hi, __nv_bfloat16* A_lo, int row, int k0, const float* v) {
+  __align__(16) __nv_bfloat16 h[8], l[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) split_bf16(v[i], h[i], l[i]);
+  const int idx = core_idx(row, k0, NR_TILE);
+  *reinterpret_cast<uint4*>(A_hi + idx) = *reinterpret_cast<const uint4*>(h);
+  *reinterpret_cast<uint4*>(A_lo + idx) = *reinterpret_cast<const uint4*>(l);
+}
+
+__device__ __forceinline__ void copy_weights(__nv_bfloat16* dst, const __nv_bfloat16* __restrict__ src, int elems) {
+  const uint4* s = reinterpret_cast<const uint4*>(src);
+  uint4* d = reinterpret_cast<uint4*>(dst);
+  for (int i = threadIdx.x; i < elems / 8; i += blockDim.x) d[i] = __ldg(s + i);
+}
+
+// D[128 x N] (TMEM) = A[128 x K] . W[N x K]^T with the 2-way BF16 split; issued by ONE thread
+__device__ __forceinline__ void issue_layer(uint32_t tmem_d, const __nv_bfloat16* A_hi, const __nv_bfloat16* A_lo,
+                                            const __nv_bfloat16* W_hi, const __nv_bfloat16* W_lo, int K, int N,
+                                            unsigned long long* bar) {
+  const uint32_t idesc = umma_idesc(NR_TILE, N);
+  const uint32_t lbo_a = NR_TILE * 16, lbo_w = (uint32_t)N * 16, sbo = 128;
+  const uint32_t a_hi = smem_u32(A_hi), a_lo = smem_u32(A_lo), w_hi = smem_u32(W_hi), w_lo = smem_u32(W_lo);
+  for (int ks = 0; ks < K / 16; ks++) {  // one instruction consumes K = 16: two 8-wide K slabs
+    const uint64_t dah = umma_desc(a_hi + ks * 2 * lbo_a, lbo_a, sbo), dal = umma_desc(a_lo + ks * 2 * lbo_a, lbo_a, sbo);
+    const uint64_t dwh = umma_desc(w_hi + ks * 2 * lbo_w, lbo_w, sbo), dwl = umma_desc(w_lo + ks * 2 * lbo_w, lbo_w, sbo);
+    umma_bf16(tmem_d, dah, dwh, idesc, ks > 0 ? 1u : 0u);
+    umma_bf16(tmem_d, dal, dwh, idesc, 1u);
+    umma_bf16(tmem_d, dah, dwl, idesc, 1u);
+  }
+  umma_commit(bar);  // implies tcgen05.fence::before_thread_sync
+}
+
+struct NrSmem {
+  __nv_bfloat16 A_hi[NR_TILE * NR_H], A_lo[NR_TILE * NR_H];  // activations, operand layout (32 KB each)
+  __nv_bfloat16 W_hi[NR_H * NR_H], W_lo[NR_H * NR_H];        // weights of the current layer
+  float bias[NR_H];
+  unsigned long long bar;
+  uint32_t tmem_base;
+};
+
+// bias + LeakyReLU(0.01) epilogue of a hidden layer: TMEM accumulators of this thread's row -> next layer's A operand
+__device__ __forceinline__ void hidden_epilogue(NrSmem& sm, uint32_t tmem_row, int row) {
+#pragma unroll 1
+  for (int c = 0; c < NR_H / 32; c++) {
+    float v[32];
+    tmem_ld32(tmem_row + c * 32, v);
+#pragma unroll
+    for (int j = 0; j < 32; j++) {
+      const float t = v[j] + sm.bias[c * 32 + j];
+      v[j] = t > 0.f ? t : 0.01f * t;  // nn.LeakyReLU() default slope
+    }
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) store_act8(sm.A_hi, sm.A_lo, row, c * 32 + j, v + j);
+  }
+}
+
+__global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs w, int npad) {
+  extern __shared__ __align__(1024) unsigned char nr_smem_raw[];
+  NrSmem& sm = *reinterpret_cast<NrSmem*>(nr_smem_raw);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int row = tid;                         // one Gaussian per thread = one row of the 128-row MMA tile
+  const int i = blockIdx.x * NR_TILE + row;
+  const bool live = i < a.P;
+
+  if (warp == 0) {  // TMEM: 128 columns x 128 lanes of FP32 accumulators
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (tid == 0) {
+    nr_mbar_init(&sm.bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  // ---- layer-0 operands: hash-grid features of this thread's Gaussian, W0, folded bias ----
+  float x = 0.f, y = 0.f, z = 0.f;
+  {
+    float feat[NR_F];
+#pragma unroll
+    for (int k = 0; k < NR_F; k++) feat[k] = 0.f;
+    if (live) {
+      x = a.xyz[3 * (size_t)i]; y = a.xyz[3 * (size_t)i + 1]; z = a.xyz[3 * (size_t)i + 2];
+      // AABB.normalize(sym=True) then HashGrid's (x+1)/2 (dataset_utils.py:66-71, network_utils.py:341-343)
+      const float nx = 2.f * ((x - a.aabb_min[0]) / (a.aabb_max[0] - a.aabb_min[0])) - 1.f;
+      const float ny = 2.f * ((y - a.aabb_min[1]) / (a.aabb_max[1] - a.aabb_min[1])) - 1.f;
+      const float nz = 2.f * ((z - a.aabb_min[2]) / (a.aabb_max[2] - a.aabb_min[2])) - 1.f;
+      hash_encode(a, (nx + 1.f) * 0.5f, (ny + 1.f) * 0.5f, (nz + 1.f) * 0.5f, feat);
+      if (a.features)
+        for (int k = 0; k < 2 * a.n_levels; k++) a.features[(size_t)i * 2 * a.n_levels + k] = feat[k];
+    }
+#pragma unroll
+    for (int k = 0; k < NR_F; k += 8) store_act8(sm.A_hi, sm.A_lo, row, k, feat + k);
+  }
+  copy_weights(sm.W_hi, w.w0_hi, NR_H * NR_F);
+  copy_weights(sm.W_lo, w.w0_lo, NR_H * NR_F);
+  sm.bias[tid] = w.bias0[tid];
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to the tensor core
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = sm.tmem_base;
+  const uint32_t tmem_row = tmem + ((uint32_t)(warp * 32) << 16);  // this warp's 32-lane quadrant
+
+  const __nv_bfloat16* next_hi[3] = {w.w1_hi, w.w2_hi, w.w3_hi};
+  const __nv_bfloat16* next_lo[3] = {w.w1_lo, w.w2_lo, w.w3_lo};
+  const float* next_b[3] = {a.b1, a.b2, a.b3};
+#pragma unroll 1
+  for (int layer = 0; layer < 3; layer++) {  // three hidden layers (N = 128); K = 32 for the first
+    if (tid == 0) issue_layer(tmem, sm.A_hi, sm.A_lo, sm.W_hi, sm.W_lo, layer == 0 ? NR_F : NR_H, NR_H, &sm.bar);
+    nr_mbar_wait(&sm.bar, (uint32_t)layer & 1u);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    hidden_epilogue(sm, tmem_row, row);  // A and W are free: the MMAs that read them have completed
+    const int nrows = layer == 2 ? npad : NR_H;
+    copy_weights(sm.W_hi, next_hi[layer], nrows * NR_H);
+    copy_weights(sm.W_lo, next_lo[layer], nrows * NR_H);
+    __syncthreads();  // everyone has read the old bias
+    if (layer < 2) sm.bias[tid] = next_b[layer][tid];
+    else sm.bias[tid] = tid < a.n_out ? a.b3[tid] : 0.f;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  }
+  // ---- output layer: N = npad (16 or 32) ----
+  if (tid == 0) issue_layer(tmem, sm.A_hi, sm.A_lo, sm.W_hi, sm.W_lo, NR_H, npad, &sm.bar);
+  nr_mbar_wait(&sm.bar, 1u);
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  float d[32];
+  tmem_ld32(tmem_row, d);  // columns >= npad hold stale values of the previous layer: never used
+  if (live) {
+#pragma unroll
+    for (int k = 0; k < 32; k++) d[k] += sm.bias[k];
+    if (a.deltas)
+      for (int k = 0; k < a.n_out; k++) a.deltas[(size_t)i * a.n_out + k] = d[k];
+    a.xyz_out[3 * (size_t)i] = x + d[0]; a.xyz_out[3 * (size_t)i + 1] = y + d[1]; a.xyz_out[3 * (size_t)i + 2] = z + d[2];
+#pragma unroll
+    for (int k = 0; k < 3; k++) a.scaling_out[3 * (size_t)i + k] = a.scaling[3 * (size_t)i + k] + d[3 + k];  // scale_offset: logit
+    // rot_offset: mult -- q1 = (1, d7, d8, d9) (non_rigid.py:276-277 overwrites the real part), Hamilton product q1 * q2
+    const float4 q2 = *reinterpret_cast<const float4*>(a.rotation + 4 * (size_t)i);
+    const float aw = 1.f, ax = d[7], ay = d[8], az = d[9];
+    float4 o;
+    o.x = aw * q2.x - ax * q2.y - ay * q2.z - az * q2.w;
+    o.y = aw * q2.y + ax * q2.x + ay * q2.w - az * q2.z;
+    o.z = aw * q2.z - ax * q2.w + ay * q2.x + az * q2.y;
+    o.w = aw * q2.w + ax * q2.z - ay * q2.y + az * q2.x;
+    *reinterpret_cast<float4*>(a.rotation_out + 4 * (size_t)i) = o;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(128u) : "memory");
+}
+
+}  // namespace
+
+static int nr_args_ok(const NonRigidArgs& a) {
+  if (a.P < 0 || a.n_feat != 2 || a.hidden != NR_H || a.n_levels * a.n_feat != NR_F) return 0;
+  if (a.n_out < 10 || a.n_out > 32 || a.n_cond < 0) return 0;
+  if (!a.aabb_min || !a.aabb_max || !a.xyz || !a.scaling || !a.rotation || !a.table) return 0;
+  if ((a.n_cond > 0 && !a.cond) || !a.W0 || !a.b0 || !a.W1 || !a.b1 || !a.W2 || !a.b2 || !a.W3 || !a.b3) return 0;
+  if (!a.xyz_out || !a.scaling_out || !a.rotation_out) return 0;
+  return 1;
+}
+
+extern "C" size_t nonrigid_workspace_bytes(const NonRigidArgs* args) {
+  return carve_ws(nullptr, args ? args->n_out : 10, nullptr);
+}
+
+extern "C" int nonrigid_forward(const NonRigidArgs* args, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!args || !workspace || !nr_args_ok(*args)) return GS_ERR_BAD_ARG;
+  const NonRigidArgs& a = *args;
+  if (a.P == 0) return GS_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  NrWs w;
+  if (carve_ws((char*)workspace, a.n_out, &w) > workspace_bytes) return GS_ERR_WORKSPACE_SMALL;
+  const int npad = nout_pad(a.n_out);
+  nr_prep_kernel<<<64, 256, 0, st>>>(a, w, npad);
+  static bool configured = false;
+  if (!configured) {
+    if (gs_check(cudaFuncSetAttribute(nr_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NrSmem) + 1024)) != GS_OK)
+      return GS_ERR_CUDA;
+    configured = true;
+  }
+  nr_fwd_kernel<<<(a.P + NR_TILE - 1) / NR_TILE, NR_TILE, sizeof(NrSmem) + 1024, st>>>(a, w, npad);
+  return gs_check(cudaGetLastError());
+}

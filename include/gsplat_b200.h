@@ -179,6 +179,48 @@ typedef struct PoseBackwardArgs {
 int pose_forward(const PoseArgs* args, void* stream);
 int pose_backward(const PoseBackwardArgs* args, void* stream);
 
+/* ---- non-rigid deformation: multiresolution hash grid + conditional MLP (forward) ----
+ * Replaces HashGridwithMLP.forward, models/deformer/non_rigid.py:226-286: AABB.normalize (utils/dataset_utils.py:66-76),
+ * HashGrid (models/network_utils.py:329-344; tiny-cuda-nn's multiresolution hash encoding, Mueller et al. 2022 -- the
+ * dependency is not vendored, so the published algorithm is restated: parity unpinned), VanillaCondMLP
+ * (models/network_utils.py:182-249: lin0 (F+C)->H, lin1, lin2 H->H, lin3 H->n_out, LeakyReLU(0.01) between) and the
+ * delta application (xyz += d[0:3]; scaling += d[3:6]; rotation = (1, d[7:10]) * rotation, Hamilton product).
+ * The four linear layers run on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM) with a 2-way BF16
+ * split of activations and weights (hi*hi + lo*hi + hi*lo, FP32 accumulate): ~2^-16 relative error per product.
+ * The per-frame condition (pose feature, C floats) is constant over the Gaussians and is folded into the first bias. */
+#define NR_MAX_LEVELS 32
+typedef struct NonRigidArgs {
+  int32_t P;
+  int32_t n_levels;        /* L (16) */
+  int32_t n_feat;          /* features per level: must be 2 */
+  int32_t hidden;          /* H: must be 128 */
+  int32_t n_cond;          /* C (144) */
+  int32_t n_out;           /* 10 + feature_dim, <= 32 */
+  uint32_t level_offset[NR_MAX_LEVELS + 1]; /* entry offsets of the levels in `table` (entries of n_feat floats) */
+  uint32_t level_res[NR_MAX_LEVELS];        /* grid resolution per level */
+  float level_scale[NR_MAX_LEVELS];         /* base_resolution * per_level_scale^l - 1 */
+  const float* aabb_min;   /* [3] */
+  const float* aabb_max;   /* [3] */
+  const float* xyz;        /* [P,3] canonical means */
+  const float* scaling;    /* [P,3] */
+  const float* rotation;   /* [P,4] */
+  const float* table;      /* [level_offset[L], n_feat] hash-grid parameters (FP32) */
+  const float* cond;       /* [C] per-frame pose feature */
+  const float* W0; const float* b0;  /* [H, L*n_feat + C], [H] */
+  const float* W1; const float* b1;  /* [H, H], [H] */
+  const float* W2; const float* b2;
+  const float* W3; const float* b3;  /* [n_out, H], [n_out] */
+  /* outputs */
+  float* xyz_out;          /* [P,3] */
+  float* scaling_out;      /* [P,3] */
+  float* rotation_out;     /* [P,4] */
+  float* deltas;           /* [P,n_out] raw MLP output (delta_rot[:,0] left as produced), or NULL */
+  float* features;         /* [P, L*n_feat] hash-grid encoding, or NULL (debug / tests) */
+} NonRigidArgs;
+
+size_t nonrigid_workspace_bytes(const NonRigidArgs* args);
+int nonrigid_forward(const NonRigidArgs* args, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Bench support (no reference counterpart): per-stage CUDA-event timing of the last forward/backward call, and an
  * FP32 FMA throughput probe (8 independent FMA chains per thread, `iters` rounds: 16*iters flop per thread). */
 void gs_profile_enable(int on);
