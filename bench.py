@@ -215,6 +215,26 @@ def fp32_peak_tflops(dev):
     return best
 
 
+def ncu_traffic(stage):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernel, from the newest committed
+    `ncu --set full` summary under profiles/ (profiles/summarize.py); None when there is none."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_kernels.json")))
+    if not files:
+        return None
+    mult = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0}
+    try:
+        with open(files[-1]) as f:
+            ks = json.load(f)
+        for k in ks:
+            if k["kernel"].startswith(stage + "_kernel") or k["kernel"].startswith(stage.replace("_fwd", "") + "_kernel"):
+                return (k.get("dram_read", 0.0) * mult.get(k.get("dram_read_unit", "byte"), 1.0) +
+                        k.get("dram_write", 0.0) * mult.get(k.get("dram_write_unit", "byte"), 1.0))
+    except Exception:
+        return None
+    return None
+
+
 def stage_times(hp, f, reps, dev):
     """Average per-stage kernel durations (CUDA events on the launching stream, recorded inside the library)."""
     from diff_gaussian_rasterization import _C
@@ -498,7 +518,7 @@ def ours_main(args):
         stages[k] = ent
     dom = max(st, key=lambda k: st[k])
     roof = dict(stages[dom])
-    roof.update(kernel=dom, traffic=None, peak_source=(f"{peak_kind} MEASURED_PEAKS.json hbm_gbs" if roof["bound"] == "hbm" else
+    roof.update(kernel=dom, traffic=ncu_traffic(dom), peak_source=(f"{peak_kind} MEASURED_PEAKS.json hbm_gbs" if roof["bound"] == "hbm" else
                                                         "FP32 FMA probe measured live in bench.py (gs_fma_probe)"))
     roof.pop("ms", None)
     ref = load_ref_cuda()

@@ -8,6 +8,6 @@ timeout 600 python bench.py --steps 100 --warmup 10 > gpurun_out/${TAG}_bench.js
 tail -c 600 gpurun_out/${TAG}_bench.err
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 120 --csv --log-file gpurun_out/${TAG}_launches.csv \
   python bench.py --profile-only --steps 2 --warmup 2 > gpurun_out/${TAG}_ncu1.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:"${KRE}" -s 8 -c 6 -o gpurun_out/${TAG}_full -f \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"${KRE}" -s 30 -c 16 -o gpurun_out/${TAG}_full -f \
   python bench.py --profile-only --steps 3 --warmup 3 > gpurun_out/${TAG}_ncu2.log 2>&1
 ls -la gpurun_out | tail
