@@ -350,3 +350,188 @@ extern "C" int nonrigid_forward(const NonRigidArgs* args, void* workspace, size_
   nr_fwd_kernel<<<(a.P + NR_TILE - 1) / NR_TILE, NR_TILE, sizeof(NrSmem) + 1024, st>>>(a, w, npad);
   return gs_check(cudaGetLastError());
 }
+
+// ================================= skinning field (SkinningField, rigid.py:160-171) =================================
+namespace {
+
+constexpr int SK_K0 = 16;   // 3 input coordinates padded to one K = 16 MMA step
+constexpr int SK_NOUT = 32; // 25 (or 24) logits padded to N = 32
+
+struct SkWs {
+  __nv_bfloat16 *w0_hi, *w0_lo;     // [128 x 16]
+  __nv_bfloat16 *wh_hi[3], *wh_lo[3];  // lin1..lin3 [128 x 128]
+  __nv_bfloat16 *w4_hi, *w4_lo;     // [32 x 128]
+};
+
+__host__ size_t carve_sk(char* base, SkWs* w) {
+  char* p = base;
+  SkWs t;
+  gs_carve(p, t.w0_hi, (size_t)NR_H * SK_K0); gs_carve(p, t.w0_lo, (size_t)NR_H * SK_K0);
+  for (int i = 0; i < 3; i++) { gs_carve(p, t.wh_hi[i], (size_t)NR_H * NR_H); gs_carve(p, t.wh_lo[i], (size_t)NR_H * NR_H); }
+  gs_carve(p, t.w4_hi, (size_t)SK_NOUT * NR_H); gs_carve(p, t.w4_lo, (size_t)SK_NOUT * NR_H);
+  if (w) *w = t;
+  return (size_t)(p - base);
+}
+
+
+__global__ void sk_prep_kernel_impl(SkinArgs a, SkWs w) {
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+  for (int e = tid; e < NR_H * SK_K0; e += nth) {
+    const int n = e / SK_K0, k = e % SK_K0;
+    const float v = k < 3 ? a.W[0][n * 3 + k] : 0.f;
+    split_bf16(v, w.w0_hi[core_idx(n, k, NR_H)], w.w0_lo[core_idx(n, k, NR_H)]);
+  }
+  for (int l = 0; l < 3; l++)
+    for (int e = tid; e < NR_H * NR_H; e += nth) {
+      const int n = e / NR_H, k = e % NR_H;
+      split_bf16(a.W[1 + l][e], w.wh_hi[l][core_idx(n, k, NR_H)], w.wh_lo[l][core_idx(n, k, NR_H)]);
+    }
+  for (int e = tid; e < SK_NOUT * NR_H; e += nth) {
+    const int n = e / NR_H, k = e % NR_H;
+    const float v = n < a.n_out ? a.W[4][(size_t)n * NR_H + k] : 0.f;
+    split_bf16(v, w.w4_hi[core_idx(n, k, SK_NOUT)], w.w4_lo[core_idx(n, k, SK_NOUT)]);
+  }
+}
+
+__device__ __forceinline__ float sigmoidf_(float v) { return 1.0f / (1.0f + expf(-v)); }
+
+// rigid.py:85-129, statement by statement (x = 25 logits, p = 24 joint probabilities)
+__device__ __forceinline__ void hierarchical_softmax(const float* x, float* p) {
+  float s[25];
+#pragma unroll
+  for (int k = 0; k < 25; k++) s[k] = sigmoidf_(x[k]);
+  auto softmax3 = [](float a, float b, float c, float* o) {
+    const float m = fmaxf(a, fmaxf(b, c));
+    const float ea = expf(a - m), eb = expf(b - m), ec = expf(c - m), inv = 1.0f / (ea + eb + ec);
+    o[0] = ea * inv; o[1] = eb * inv; o[2] = ec * inv;
+  };
+  float sm[3];
+  softmax3(x[1], x[2], x[3], sm);
+  for (int k = 0; k < 3; k++) p[1 + k] = s[0] * sm[k];
+  p[0] = 1.f - s[0];
+  for (int k = 0; k < 3; k++) { p[4 + k] = p[1 + k] * s[4 + k]; p[1 + k] = p[1 + k] * (1.f - s[4 + k]); }
+  for (int k = 0; k < 3; k++) { p[7 + k] = p[4 + k] * s[7 + k]; p[4 + k] = p[4 + k] * (1.f - s[7 + k]); }
+  for (int k = 0; k < 2; k++) { p[10 + k] = p[7 + k] * s[10 + k]; p[7 + k] = p[7 + k] * (1.f - s[10 + k]); }
+  softmax3(x[12], x[13], x[14], sm);
+  for (int k = 0; k < 3; k++) p[12 + k] = p[9] * s[24] * sm[k];
+  p[9] = p[9] * (1.f - s[24]);
+  p[15] = p[12] * s[15]; p[12] = p[12] * (1.f - s[15]);
+  for (int k = 0; k < 2; k++) { p[16 + k] = p[13 + k] * s[16 + k]; p[13 + k] = p[13 + k] * (1.f - s[16 + k]); }
+  for (int k = 0; k < 2; k++) { p[18 + k] = p[16 + k] * s[18 + k]; p[16 + k] = p[16 + k] * (1.f - s[18 + k]); }
+  for (int k = 0; k < 2; k++) { p[20 + k] = p[18 + k] * s[20 + k]; p[18 + k] = p[18 + k] * (1.f - s[20 + k]); }
+  for (int k = 0; k < 2; k++) { p[22 + k] = p[20 + k] * s[22 + k]; p[20 + k] = p[20 + k] * (1.f - s[22 + k]); }
+}
+
+__global__ void __launch_bounds__(NR_TILE, 1) sk_fwd_kernel(SkinArgs a, SkWs w) {
+  extern __shared__ __align__(1024) unsigned char nr_smem_raw[];
+  NrSmem& sm = *reinterpret_cast<NrSmem*>(nr_smem_raw);
+  const int tid = threadIdx.x, warp = tid >> 5, row = tid;
+  const int i = blockIdx.x * NR_TILE + row;
+  const bool live = i < a.P;
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (tid == 0) {
+    nr_mbar_init(&sm.bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  {
+    float in[SK_K0];
+#pragma unroll
+    for (int k = 0; k < SK_K0; k++) in[k] = 0.f;
+    if (live) {
+#pragma unroll
+      for (int k = 0; k < 3; k++)  // AABB.normalize(sym=True), dataset_utils.py:66-71
+        in[k] = 2.f * ((a.xyz[3 * (size_t)i + k] - a.aabb_min[k]) / (a.aabb_max[k] - a.aabb_min[k])) - 1.f;
+    }
+    store_act8(sm.A_hi, sm.A_lo, row, 0, in);
+    store_act8(sm.A_hi, sm.A_lo, row, 8, in + 8);
+  }
+  copy_weights(sm.W_hi, w.w0_hi, NR_H * SK_K0);
+  copy_weights(sm.W_lo, w.w0_lo, NR_H * SK_K0);
+  sm.bias[tid] = a.b[0][tid];
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = sm.tmem_base;
+  const uint32_t tmem_row = tmem + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+  for (int layer = 0; layer < 4; layer++) {  // four hidden layers
+    if (tid == 0) issue_layer(tmem, sm.A_hi, sm.A_lo, sm.W_hi, sm.W_lo, layer == 0 ? SK_K0 : NR_H, NR_H, &sm.bar);
+    nr_mbar_wait(&sm.bar, (uint32_t)layer & 1u);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    hidden_epilogue(sm, tmem_row, row);
+    if (layer < 3) {
+      copy_weights(sm.W_hi, w.wh_hi[layer], NR_H * NR_H);
+      copy_weights(sm.W_lo, w.wh_lo[layer], NR_H * NR_H);
+    } else {
+      copy_weights(sm.W_hi, w.w4_hi, SK_NOUT * NR_H);
+      copy_weights(sm.W_lo, w.w4_lo, SK_NOUT * NR_H);
+    }
+    __syncthreads();
+    if (layer < 3) sm.bias[tid] = a.b[layer + 1][tid];
+    else sm.bias[tid] = tid < a.n_out ? a.b[4][tid] : 0.f;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  }
+  if (tid == 0) issue_layer(tmem, sm.A_hi, sm.A_lo, sm.W_hi, sm.W_lo, NR_H, SK_NOUT, &sm.bar);
+  nr_mbar_wait(&sm.bar, 0u);  // fifth commit
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  float x[32];
+  tmem_ld32(tmem_row, x);
+  if (live) {
+#pragma unroll
+    for (int k = 0; k < 32; k++) x[k] += sm.bias[k];
+    if (a.logits)
+      for (int k = 0; k < a.n_out; k++) a.logits[(size_t)i * a.n_out + k] = x[k];
+    float p[24];
+    if (a.n_out == 25) {
+      hierarchical_softmax(x, p);
+    } else {  // F.softmax over 24 logits
+      float m = x[0];
+#pragma unroll
+      for (int k = 1; k < 24; k++) m = fmaxf(m, x[k]);
+      float sum = 0.f;
+#pragma unroll
+      for (int k = 0; k < 24; k++) { p[k] = expf(x[k] - m); sum += p[k]; }
+      const float inv = 1.0f / sum;
+#pragma unroll
+      for (int k = 0; k < 24; k++) p[k] *= inv;
+    }
+    float4* o = reinterpret_cast<float4*>(a.weights + (size_t)i * 24);
+#pragma unroll
+    for (int k = 0; k < 6; k++) o[k] = make_float4(p[4 * k], p[4 * k + 1], p[4 * k + 2], p[4 * k + 3]);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(128u) : "memory");
+}
+
+}  // namespace
+
+extern "C" size_t skinning_workspace_bytes(const SkinArgs* args) { (void)args; return carve_sk(nullptr, nullptr); }
+
+extern "C" int skinning_forward(const SkinArgs* args, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!args || !workspace) return GS_ERR_BAD_ARG;
+  const SkinArgs& a = *args;
+  if (a.P < 0 || a.hidden != NR_H || (a.n_out != 25 && a.n_out != 24) || !a.aabb_min || !a.aabb_max || !a.xyz || !a.weights)
+    return GS_ERR_BAD_ARG;
+  for (int l = 0; l < 5; l++) if (!a.W[l] || !a.b[l]) return GS_ERR_BAD_ARG;
+  if (a.P == 0) return GS_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  SkWs w;
+  if (carve_sk((char*)workspace, &w) > workspace_bytes) return GS_ERR_WORKSPACE_SMALL;
+  sk_prep_kernel_impl<<<64, 256, 0, st>>>(a, w);
+  static bool configured = false;
+  if (!configured) {
+    if (gs_check(cudaFuncSetAttribute(sk_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NrSmem) + 1024)) != GS_OK)
+      return GS_ERR_CUDA;
+    configured = true;
+  }
+  sk_fwd_kernel<<<(a.P + NR_TILE - 1) / NR_TILE, NR_TILE, sizeof(NrSmem) + 1024, st>>>(a, w);
+  return gs_check(cudaGetLastError());
+}

@@ -221,6 +221,28 @@ typedef struct NonRigidArgs {
 size_t nonrigid_workspace_bytes(const NonRigidArgs* args);
 int nonrigid_forward(const NonRigidArgs* args, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- skinning field: per-Gaussian LBS weights from the skinning MLP (forward) ----
+ * Replaces SkinningField.get_forward_transform's weight part, models/deformer/rigid.py:160-171,189-196 (non-distilled
+ * path): AABB.normalize(sym=True) -> VanillaCondMLP(3 -> H x4 -> n_out) (models/network_utils.py:182-249,251-257;
+ * configs/rigid/skinning_field.yaml) -> hierarchical_softmax over the kinematic tree when n_out == 25
+ * (rigid.py:85-129; logit 24 gates joint 9 -> {12,13,14}) or a plain softmax when n_out == 24.  The [P,24] result is the
+ * `weights` input of pose_forward.  Same tensor-core building block as nonrigid_forward (tcgen05, 2-way BF16 split). */
+typedef struct SkinArgs {
+  int32_t P;
+  int32_t hidden;          /* must be 128 */
+  int32_t n_out;           /* 25 (hierarchical softmax) or 24 (softmax) */
+  int32_t pad_;
+  const float* aabb_min;   /* [3] */
+  const float* aabb_max;   /* [3] */
+  const float* xyz;        /* [P,3] canonical (non-rigidly displaced) means */
+  const float* W[5];       /* lin0 [H,3], lin1..lin3 [H,H], lin4 [n_out,H] */
+  const float* b[5];
+  float* weights;          /* [P,24] */
+  float* logits;           /* [P,n_out] or NULL */
+} SkinArgs;
+size_t skinning_workspace_bytes(const SkinArgs* args);
+int skinning_forward(const SkinArgs* args, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Bench support (no reference counterpart): per-stage CUDA-event timing of the last forward/backward call, and an
  * FP32 FMA throughput probe (8 independent FMA chains per thread, `iters` rounds: 16*iters flop per thread). */
 void gs_profile_enable(int on);

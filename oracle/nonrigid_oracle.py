@@ -80,3 +80,43 @@ def nonrigid_forward(xyz, scaling, rotation, aabb_min, aabb_max, table, levels, 
     rot = torch.stack([aw * bw - ax * bx - ay * by - az * bz, aw * bx + ax * bw + ay * bz - az * by,
                        aw * by - ax * bz + ay * bw + az * bx, aw * bz + ax * by - ay * bx + az * bw], 1)
     return dict(xyz=xyz + d[:, :3], scaling=scaling + d[:, 3:6], rotation=rot, deltas=d, features=feat)
+
+
+def hierarchical_softmax(x):
+    """models/deformer/rigid.py:85-129, statement by statement (x [P,25] -> [P,24])."""
+    sig = torch.sigmoid(x)
+    sm = lambda t: torch.softmax(t, dim=-1)
+    p = torch.ones(x.shape[0], 24, dtype=x.dtype)
+    p[:, [1, 2, 3]] = sig[:, [0]] * sm(x[:, [1, 2, 3]])
+    p[:, [0]] = 1 - sig[:, [0]]
+    p[:, [4, 5, 6]] = p[:, [1, 2, 3]] * sig[:, [4, 5, 6]]
+    p[:, [1, 2, 3]] = p[:, [1, 2, 3]] * (1 - sig[:, [4, 5, 6]])
+    p[:, [7, 8, 9]] = p[:, [4, 5, 6]] * sig[:, [7, 8, 9]]
+    p[:, [4, 5, 6]] = p[:, [4, 5, 6]] * (1 - sig[:, [7, 8, 9]])
+    p[:, [10, 11]] = p[:, [7, 8]] * sig[:, [10, 11]]
+    p[:, [7, 8]] = p[:, [7, 8]] * (1 - sig[:, [10, 11]])
+    p[:, [12, 13, 14]] = p[:, [9]] * sig[:, [24]] * sm(x[:, [12, 13, 14]])
+    p[:, [9]] = p[:, [9]] * (1 - sig[:, [24]])
+    p[:, [15]] = p[:, [12]] * sig[:, [15]]
+    p[:, [12]] = p[:, [12]] * (1 - sig[:, [15]])
+    p[:, [16, 17]] = p[:, [13, 14]] * sig[:, [16, 17]]
+    p[:, [13, 14]] = p[:, [13, 14]] * (1 - sig[:, [16, 17]])
+    p[:, [18, 19]] = p[:, [16, 17]] * sig[:, [18, 19]]
+    p[:, [16, 17]] = p[:, [16, 17]] * (1 - sig[:, [18, 19]])
+    p[:, [20, 21]] = p[:, [18, 19]] * sig[:, [20, 21]]
+    p[:, [18, 19]] = p[:, [18, 19]] * (1 - sig[:, [20, 21]])
+    p[:, [22, 23]] = p[:, [20, 21]] * sig[:, [22, 23]]
+    p[:, [20, 21]] = p[:, [20, 21]] * (1 - sig[:, [22, 23]])
+    return p
+
+
+def skinning_weights_forward(xyz, aabb_min, aabb_max, W, b):
+    """SkinningField.get_forward_transform's weights (rigid.py:160-171, 189-196, non-distilled): AABB.normalize(sym) ->
+    VanillaCondMLP(3 -> H x4 -> n_out), LeakyReLU(0.01) -> hierarchical softmax (25 logits) / softmax (24)."""
+    h = 2.0 * ((xyz - aabb_min) / (aabb_max - aabb_min)) - 1.0
+    for l in range(len(W)):
+        h = h @ W[l].T + b[l]
+        if l < len(W) - 1:
+            h = torch.nn.functional.leaky_relu(h, 0.01)
+    w = hierarchical_softmax(h) if h.shape[1] == 25 else torch.softmax(h, -1)
+    return w, h

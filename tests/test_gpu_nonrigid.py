@@ -54,3 +54,36 @@ def test_nonrigid_delay_is_identity(built_lib):
     x = torch.randn(10, 3, device=dev)
     out = m.deform(x, x, torch.randn(10, 4, device=dev), torch.zeros(144, device=dev), iteration=100)
     assert out[0] is x and out[3] is None
+
+
+@pytest.mark.parametrize("P,d_out", [(6000, 25), (300, 24)])
+def test_skinning_field_weights(built_lib, P, d_out):
+    """Skinning MLP + hierarchical softmax on the tensor cores vs the fp64 oracle: logits <= 2e-5 of max|logit| + 1e-6,
+    weights <= 2e-5 abs, rows sum to 1; then the weights drive the fused posing kernel."""
+    from avatar_pose.skinning import SkinningFieldFused
+    from avatar_pose import fused_pose
+    dev = torch.device("cuda:0")
+    torch.manual_seed(5)
+    g = synth.canonical_gaussians(P, seed=1)
+    xyz = torch.from_numpy(g["xyz"])
+    lo, hi = xyz.min(0).values - 0.05, xyz.max(0).values + 0.05
+    m = SkinningFieldFused(d_out=d_out, aabb_min=lo.tolist(), aabb_max=hi.tolist())
+    with torch.no_grad():
+        m.lin4.weight.mul_(8.0)  # spread the logits as a trained field would
+    md = m.to(dev)
+    wts, logits = md.query_weights(xyz.to(dev), return_logits=True)
+    torch.cuda.synchronize()
+    d64 = lambda t: t.detach().cpu().double()
+    W = [d64(getattr(m, f"lin{l}").weight) for l in range(5)]
+    b = [d64(getattr(m, f"lin{l}").bias) for l in range(5)]
+    ref_w, ref_logits = nro.skinning_weights_forward(xyz.double(), d64(m.aabb_min), d64(m.aabb_max), W, b)
+    scale = float(ref_logits.abs().max())
+    assert scale > 0.5
+    assert float((logits.cpu().double() - ref_logits).abs().max()) <= 2e-5 * scale + 1e-6
+    assert float((wts.cpu().double() - ref_w).abs().max()) <= 2e-5
+    assert float((wts.sum(1) - 1).abs().max()) <= 1e-5
+    ps = synth.pose(1)
+    t = lambda k: torch.from_numpy(g[k]).to(dev)
+    means = fused_pose(t("xyz"), t("rotation"), t("scaling"), t("opacity"), t("features_dc"), t("features_rest"), wts,
+                       torch.from_numpy(ps["bone_transforms"]).to(dev), torch.zeros(3, device=dev), 3)[0]
+    assert torch.isfinite(means).all()
