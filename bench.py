@@ -387,6 +387,10 @@ def ours_main(args):
         raise SystemExit("bench.py (ours) needs a CUDA device; there is no CPU fallback")
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    # stdout carries exactly ONE JSON line: library banners (NCCL prints its version there) go to stderr
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     import __graft_entry__ as ge
@@ -406,25 +410,30 @@ def ours_main(args):
     from avatar_pose.graphs import GraphedStep
     f_static = hp.static_frame(frames[rank])
     eager = args.eager
-    g_train = None if eager else GraphedStep(lambda: hp.train_step(f_static))
+    from avatar_pose import dist as apd
+
+    def step_with_allreduce(f):
+        """One data-parallel training step: fwd + bwd, then ONE all-reduce of the flat per-Gaussian gradient slab."""
+        loss = hp.train_step(f)
+        if world > 1:
+            apd.allreduce_gradients(avatar_pose.last_grad_slab())
+        return loss
+
+    # the NCCL all-reduce is captured inside the graph too (one launch per step for everything)
+    g_train = None if eager else GraphedStep(lambda: step_with_allreduce(f_static))
     g_render = None if eager else GraphedStep(lambda: hp.render(f_static))
 
     def train_resident():
-        loss = hp.train_step(f_dev) if eager else g_train.replay()
-        if world > 1:
-            dist.all_reduce(avatar_pose.last_grad_slab())
-        return loss
+        return step_with_allreduce(f_dev) if eager else g_train.replay()
 
     loss_host = torch.empty(1).pin_memory()
 
     def train_e2e():
         if eager:
-            loss = hp.train_step(hp.upload(f_pin))
+            loss = step_with_allreduce(hp.upload(f_pin))
         else:
             hp.load_static(f_static, f_pin)
             loss = g_train.replay()
-        if world > 1:
-            dist.all_reduce(avatar_pose.last_grad_slab())
         loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
         torch.cuda.current_stream(dev).synchronize()  # the caller reads the loss
 
@@ -458,7 +467,8 @@ def ours_main(args):
         for _ in range(args.warmup + args.steps):
             train_resident()
         torch.cuda.synchronize(dev)
-        print(json.dumps({"profile_only": True, "steps": args.warmup + args.steps}))
+        os.dup2(saved_stdout, 1)
+        print(json.dumps({"profile_only": True, "steps": args.warmup + args.steps}), flush=True)
         return
     sampler = ClockSampler(local)
     if rank == 0:
@@ -477,9 +487,7 @@ def ours_main(args):
         n_graph, over = _C.graph_overflow(dev)
         assert not over, f"the captured pair capacity overflowed (N={n_graph}): timed frames were invalid"
     if rank != 0:
-        if world > 1:
-            dist.barrier()
-            dist.destroy_process_group()
+        finish(world, dev)
         return
 
     # ---- rank 0: stage times, roofline, baselines ----
@@ -553,10 +561,24 @@ def ours_main(args):
             "eager_ms_per_step": ms_eager, "ms_per_step_hot_l2": float(np.mean(hot)), "ms_per_step_p10_p90": [float(np.percentile(ts_train, 10)), float(np.percentile(ts_train, 90))],
             "gpu_launches": launches, "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": fp32_peak,
             "cpu_baseline": cpu, "ref_cuda": ref_cuda, "clocks": sampler.summary(), "regrows": _C.stats["capacity_regrows"]}
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        os.dup2(2, 1)
+    finish(world, dev)
+
+
+def finish(world, dev):
+    """End of a multi-rank run: final barrier, then leave WITHOUT tearing the process group down -- destroying an NCCL
+    communicator that live CUDA graphs still reference can hang, and the process is exiting anyway."""
+    import torch.distributed as dist
     if world > 1:
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize(dev)
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
