@@ -1,0 +1,84 @@
+"""nn.Module drop-ins for the posing side of 3DGS-Avatar, mirroring the reference's module boundary
+(models/gaussian_converter.py:41-59, models/deformer/deformer.py:13-19, registry keys of rigid.py:244-251,
+non_rigid.py:302-310, texture.py:128-134):
+
+    converter = FusedGaussianConverter(rigid=SMPLNNFused(smpl_verts, skinning_weights), non_rigid=None)
+    deformed, loss_reg, colors_precomp = converter(gaussians, camera, iteration, compute_loss)
+
+`gaussians` is the reference's GaussianModel (or anything exposing `_xyz, _rotation, _scaling, _opacity, _features_dc,
+_features_rest, active_sh_degree, max_sh_degree`); `camera` exposes `bone_transforms [24,4,4]`, `camera_center [3]` and,
+for the non-rigid stage, `rots`, `Jtrs`.  The returned object duck-types what gaussian_renderer/__init__.py:76-114 and
+utils/loss_utils.py:69-74 read from a deformed GaussianModel.  One fused kernel replaces non-rigid clone + rigid clone +
+LBS + build_rotation + covariance + activations + SH2RGB."""
+import torch
+import torch.nn as nn
+
+from . import fused_pose
+from .nonrigid import HashGridMLPFused
+from .skinning import SkinningFieldFused
+
+
+class PosedGaussians:
+    """Lazy views over the fused outputs (what render() reads: gaussian_renderer/__init__.py:76-114)."""
+
+    def __init__(self, means, cov, opacity, scaling_raw, rotation_raw, features, T_fwd, rotation_bar, active_sh_degree, max_sh_degree):
+        self._xyz, self._cov, self._opacity_act = means, cov, opacity
+        self._scaling, self._rotation, self._features = scaling_raw, rotation_raw, features
+        self.fwd_transform, self.rotation_precomp = T_fwd, rotation_bar
+        self.active_sh_degree, self.max_sh_degree = active_sh_degree, max_sh_degree
+
+    get_xyz = property(lambda s: s._xyz)
+    get_opacity = property(lambda s: s._opacity_act)
+    get_scaling = property(lambda s: torch.exp(s._scaling))                           # scene/gaussian_model.py:132-134
+    get_rotation = property(lambda s: torch.nn.functional.normalize(s._rotation))     # :136-138
+    get_features = property(lambda s: s._features)
+
+    def get_covariance(self, scaling_modifier=1):
+        """[P,6]; R_bar (mod*S)(mod*S)^T R_bar^T = mod^2 * the covariance the fused kernel wrote with mod = 1."""
+        return self._cov if scaling_modifier == 1 else self._cov * (scaling_modifier * scaling_modifier)
+
+
+class SMPLNNFused(nn.Module):
+    """`smpl_nn` (rigid.py:35-71): skinning weights of the nearest SMPL vertex; cached while `_xyz` is unchanged."""
+
+    def __init__(self, smpl_verts, skinning_weights):
+        super().__init__()
+        self.register_buffer("smpl_verts", torch.as_tensor(smpl_verts, dtype=torch.float32))
+        self.register_buffer("skinning_weights", torch.as_tensor(skinning_weights, dtype=torch.float32))
+        self._key, self._cached = None, None
+
+    @torch.no_grad()
+    def query_weights(self, xyz):
+        key = (xyz.data_ptr(), xyz._version, xyz.shape[0])
+        if key != self._key:
+            idx = torch.cat([torch.cdist(c, self.smpl_verts).argmin(1) for c in xyz.detach().split(8192)])  # exact 1-NN
+            self._cached, self._key = self.skinning_weights[idx].contiguous(), key
+        return self._cached
+
+
+class FusedGaussianConverter(nn.Module):
+    def __init__(self, rigid, non_rigid=None, pose_encoder=None, cano_view_dir=True):
+        """rigid: SMPLNNFused | SkinningFieldFused (anything with query_weights(xyz) -> [P,24]);
+        non_rigid: HashGridMLPFused or None; pose_encoder(rots, Jtrs) -> [1,C] (HierarchicalPoseEncoder) for its condition."""
+        super().__init__()
+        self.rigid, self.non_rigid, self.pose_encoder, self.cano_view_dir = rigid, non_rigid, pose_encoder, cano_view_dir
+
+    def forward(self, gaussians, camera, iteration, compute_loss=True):
+        g = gaussians
+        xyz, scaling, rotation = g._xyz, g._scaling, g._rotation
+        loss_reg = {}
+        if self.non_rigid is not None and iteration >= self.non_rigid.delay:  # non_rigid.py:227-232
+            cond = self.pose_encoder(camera.rots, camera.Jtrs) if self.pose_encoder is not None else \
+                torch.zeros(self.non_rigid.n_cond, device=xyz.device)
+            xyz, scaling, rotation, deltas = self.non_rigid.deform(xyz, scaling, rotation, cond)
+            if compute_loss:  # non_rigid.py:288-297
+                loss_reg = {"nr_xyz": deltas[:, :3].norm(p=2, dim=1).mean(), "nr_scale": deltas[:, 3:6].norm(p=1, dim=1).mean(),
+                            "nr_rot": deltas[:, 7:10].norm(p=1, dim=1).mean()}
+        weights = self.rigid.query_weights(xyz)  # evaluated at the non-rigidly displaced position (rigid.py:217-220)
+        means, cov, colors, opacity, T_fwd, Rbar = fused_pose(
+            xyz, rotation, scaling, g._opacity, g._features_dc, g._features_rest, weights, camera.bone_transforms,
+            camera.camera_center, g.active_sh_degree, 1.0, self.cano_view_dir, return_aux=True)
+        feats = torch.cat([g._features_dc, g._features_rest], 1)
+        deformed = PosedGaussians(means, cov, opacity, scaling, rotation, feats, T_fwd, Rbar, g.active_sh_degree,
+                                  getattr(g, "max_sh_degree", 3))
+        return deformed, loss_reg, colors
