@@ -56,10 +56,13 @@ def test_pose_forward_backward(built_lib, deg, cano, mod):
         (col * grads["colors"].to(dev)).sum() + (op * grads["opacity"].to(dev)).sum()
     loss.backward()
     torch.cuda.synchronize()
-    o32, _ = _oracle(t, deg, cano=cano, mod=mod)
-    assert float((means.detach().cpu() - o32["means3D"]).abs().max()) <= 1e-5
-    assert float((col.cpu() - o32["colors"]).abs().max()) <= 1e-5
-    assert float((op.cpu() - o32["opacity"]).abs().max()) <= 1e-6
+    # Forward truth in fp64: on some hosts the fp32 torch-CPU matmuls of the oracle chain run through reduced-precision
+    # oneDNN paths (observed ~1e-3 relative on AMX-capable Xeons), which is a property of the checker, not of the kernel.
+    o32, _ = _oracle(t, deg, torch.float64, cano=cano, mod=mod)
+    o32 = {k: (v.detach() if torch.is_tensor(v) else v) for k, v in o32.items()}
+    assert float((means.detach().cpu().double() - o32["means3D"]).abs().max()) <= 1e-5
+    assert float((col.detach().cpu().double() - o32["colors"]).abs().max()) <= 1e-5
+    assert float((op.detach().cpu().double() - o32["opacity"]).abs().max()) <= 1e-6
     o64, _ = _oracle(t, deg, torch.float64, cano=cano, mod=mod)
     e64, e32 = rel(cov.detach().cpu(), o64["cov3D"].detach()), rel(cov.detach().cpu(), o32["cov3D"].detach())
     if e64 > 1e-5:  # diagnose: is the GPU result reproducible, and which side moved?
@@ -72,8 +75,8 @@ def test_pose_forward_backward(built_lib, deg, cano, mod):
                              f"{rel(again.cpu(), cov.detach().cpu()):.3e}, rerun vs fp64 {rel(again.cpu(), o64['cov3D'].detach()):.3e}, "
                              f"o32 vs o64 {rel(o32['cov3D'].detach(), o64['cov3D'].detach()):.3e}, rows off: {(bad > 1e-9).sum().item()} "
                              f"worst row {bad.argmax().item()}")
-    assert float((T_fwd.cpu() - o32["T_fwd"]).abs().max()) <= 1e-5
-    assert float((Rbar.cpu() - o32["rotation_bar"]).abs().max()) <= 1e-5
+    assert float((T_fwd.cpu().double() - o32["T_fwd"]).abs().max()) <= 1e-5
+    assert float((Rbar.cpu().double() - o32["rotation_bar"]).abs().max()) <= 1e-5
     _, leaf = _oracle(t, deg, torch.float64, grads, cano=cano, mod=mod)
     for k in ("xyz", "rotation", "scaling", "opacity", "features_dc", "features_rest", "weights"):
         assert rel(d[k].grad.cpu(), leaf[k].grad) <= 1e-4, k
