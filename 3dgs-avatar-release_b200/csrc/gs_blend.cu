@@ -349,7 +349,10 @@ __device__ __forceinline__ void xpose_step(float* v, int lane) {
 // whose last contributor lies behind the segment restarts from the forward's checkpoint at the segment end:
 // T = T(seg end), accumulated colour behind it = (C_final - C(seg end)) / T(seg end); inside the segment the recurrences
 // are the reference's (backward.cu:497-534).  Deep tile lists thus spread over many SMs instead of one.
-__global__ void __launch_bounds__(kWarps * 32)
+#ifndef GS_BWD_MINBLOCKS
+#define GS_BWD_MINBLOCKS 2
+#endif
+__global__ void __launch_bounds__(kWarps * 32, GS_BWD_MINBLOCKS)
 blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H, int grid_x,
                  const uint32_t* __restrict__ seg_off, int tiles, const uint2* __restrict__ items,
                  const float4* __restrict__ ckpt,

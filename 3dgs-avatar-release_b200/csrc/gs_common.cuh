@@ -14,7 +14,9 @@
 
 #define GS_TILE 16          // BLOCK_X = BLOCK_Y = 16 (cuda_rasterizer/config.h:16-17); defines keys/ranges/n_contrib
 #define GS_ALIGN 256
-#define GS_SEG 256          // list entries per backward work item = spacing of the forward's per-pixel checkpoints
+#ifndef GS_SEG
+#define GS_SEG 128          // list entries per backward work item = spacing of the forward's per-pixel checkpoints
+#endif
 
 // ---- workspace layouts (private; reached from outside only through gs_debug_read) ----
 struct GsHeader {            // first 256 bytes of the geom workspace
