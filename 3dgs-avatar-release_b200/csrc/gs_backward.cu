@@ -103,6 +103,7 @@ __device__ void cov3d_backward(const float* __restrict__ s3, float mod, const fl
 
 __global__ void __launch_bounds__(256) preprocess_bwd_kernel(GsBackwardArgs a, const float* __restrict__ cov3Ds,
                                                              const uint8_t* __restrict__ clamped) {
+  GS_PDL_PROLOGUE();
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   if (threadIdx.x < 16) { s_view[threadIdx.x] = a.viewmatrix[threadIdx.x]; s_proj[threadIdx.x] = a.projmatrix[threadIdx.x]; }
   if (threadIdx.x < 3 && a.campos) s_cam[threadIdx.x] = a.campos[threadIdx.x];
@@ -209,6 +210,6 @@ int gs_launch_preprocess_bwd(const GsBackwardArgs& a, const GsGeom& g, cudaStrea
   int blocks = (a.P + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
   const float* cov = a.cov3D_precomp ? a.cov3D_precomp : g.cov3D;
-  preprocess_bwd_kernel<<<blocks, 256, 0, st>>>(a, cov, g.clamped);
+  gs_launch(preprocess_bwd_kernel, dim3(blocks), dim3(256), 0, st, a, cov, g.clamped);
   return gs_check(cudaGetLastError());
 }

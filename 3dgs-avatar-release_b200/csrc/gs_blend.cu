@@ -163,6 +163,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                  const uint32_t* __restrict__ seg_off, float4* __restrict__ ckpt, const uint32_t* __restrict__ order,
                  int grid_x) {
+  GS_PDL_PROLOGUE();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FwdCtl& ctl = *reinterpret_cast<FwdCtl*>(smem_raw);
   FwdBuf* const bufs = reinterpret_cast<FwdBuf*>(smem_raw + sizeof(FwdCtl));
@@ -360,6 +361,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
                  float* __restrict__ dL_dmean2D /*[P,3]*/, float* __restrict__ dL_dconic /*[P,4]*/,
                  float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors) {
+  GS_PDL_PROLOGUE();
   __shared__ Slab s_slab[kWarps];
   if (blockIdx.x >= seg_off[tiles]) return;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -532,14 +534,14 @@ int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& 
       return GS_ERR_CUDA;
     configured = true;
   }
-  blend_fwd_kernel<<<grid, kFwdWarps * 32, smem, st>>>(im.ranges, l.point_list, a.width, a.height, g.rec, a.background,
+  gs_launch(blend_fwd_kernel, grid, dim3(kFwdWarps * 32), smem, st, im.ranges, l.point_list, a.width, a.height, g.rec, a.background,
                                                        im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt, im.order, gx);
   return gs_check(cudaGetLastError());
 }
 
 int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st) {
   const int gx = (a.width + GS_TILE - 1) / GS_TILE, gy = (a.height + GS_TILE - 1) / GS_TILE;
-  blend_bwd_kernel<<<(unsigned)l.max_items, kWarps * 32, 0, st>>>(
+  gs_launch(blend_bwd_kernel, dim3((unsigned)l.max_items), dim3(kWarps * 32), 0, st,
       im.ranges, l.point_list, a.width, a.height, gx, im.seg_off, gx * gy, l.items, l.ckpt, a.background, g.rec,
       im.final_T, im.n_contrib, a.dL_dpix, a.dL_dmean2D, a.dL_dconic, a.dL_dopacity, a.dL_dcolor);
   return gs_check(cudaGetLastError());

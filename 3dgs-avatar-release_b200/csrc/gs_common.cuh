@@ -187,6 +187,28 @@ __device__ __forceinline__ float gs_exp(float x) {
 }
 #endif
 
+// ---- programmatic dependent launch: every hot-path kernel starts with GS_PDL_PROLOGUE() (wait for the previous grid's
+// results, then let the next grid be scheduled) and is launched through gs_launch(), so that inside a stream / CUDA graph
+// the launch latency of kernel k+1 overlaps the tail of kernel k.  The wait comes first, so no kernel touches memory
+// before its producer has completed. ----
+#ifdef __CUDACC__
+#define GS_PDL_PROLOGUE()                                          \
+  do {                                                             \
+    asm volatile("griddepcontrol.wait;" ::: "memory");             \
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); \
+  } while (0)
+template <typename... KArgs, typename... Args>
+static inline cudaError_t gs_launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#endif
+
 // ---- launchers (one per translation unit) ----
 int gs_launch_preprocess(const GsForwardArgs& a, const GsGeom& g, const GsScratch& s, cudaStream_t st);
 int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsScratch& s, const GsList& l,

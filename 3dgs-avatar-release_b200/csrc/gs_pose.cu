@@ -147,6 +147,7 @@ __device__ __forceinline__ float sh_coef(const PoseArgs& a, int i, const float* 
 }
 
 __global__ void __launch_bounds__(128) pose_fwd_kernel(PoseArgs a) {
+  GS_PDL_PROLOGUE();
   __shared__ float s_bones[24 * 16];
   __shared__ float s_cam[3];
   for (int k = threadIdx.x; k < 24 * 16; k += blockDim.x) s_bones[k] = a.bone_transforms[k];
@@ -213,6 +214,7 @@ __global__ void __launch_bounds__(128) pose_fwd_kernel(PoseArgs a) {
 }
 
 __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
+  GS_PDL_PROLOGUE();
   const PoseArgs& a = ba.fwd;
   __shared__ float s_bones[24 * 16];
   __shared__ float s_cam[3];
@@ -352,7 +354,7 @@ extern "C" int pose_forward(const PoseArgs* args, void* stream) {
   int blocks = (args->P + 127) / 128;
   if (blocks > 148 * 16) blocks = 148 * 16;
   gs_prof_mark(5, 0, (cudaStream_t)stream);
-  pose_fwd_kernel<<<blocks, 128, 0, (cudaStream_t)stream>>>(*args);
+  gs_launch(pose_fwd_kernel, dim3(blocks), dim3(128), 0, (cudaStream_t)stream, *args);
   gs_prof_mark(5, 1, (cudaStream_t)stream);
   return gs_check(cudaGetLastError());
 }
@@ -366,7 +368,7 @@ extern "C" int pose_backward(const PoseBackwardArgs* args, void* stream) {
   int blocks = (args->fwd.P + 127) / 128;
   if (blocks > 148 * 16) blocks = 148 * 16;
   gs_prof_mark(6, 0, (cudaStream_t)stream);
-  pose_bwd_kernel<<<blocks, 128, 0, (cudaStream_t)stream>>>(*args);
+  gs_launch(pose_bwd_kernel, dim3(blocks), dim3(128), 0, (cudaStream_t)stream, *args);
   gs_prof_mark(6, 1, (cudaStream_t)stream);
   return gs_check(cudaGetLastError());
 }

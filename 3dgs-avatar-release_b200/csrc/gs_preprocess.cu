@@ -116,6 +116,7 @@ __device__ __forceinline__ void color_from_sh(int deg, float px, float py, float
 
 __global__ void __launch_bounds__(256) preprocess_kernel(GsForwardArgs a, GsGeom g, uint32_t* __restrict__ dkey,
                                                          uint32_t* __restrict__ dval, uint32_t* __restrict__ hist) {
+  GS_PDL_PROLOGUE();
   __shared__ uint32_t s_hist[4 * 256];
   for (int i = threadIdx.x; i < 4 * 256; i += blockDim.x) s_hist[i] = 0;
   __shared__ float s_view[16], s_proj[16], s_cam[3];
@@ -249,7 +250,7 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
 int gs_launch_preprocess(const GsForwardArgs& a, const GsGeom& g, const GsScratch& s, cudaStream_t st) {
   int blocks = (a.P + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  preprocess_kernel<<<blocks, 256, 0, st>>>(a, g, s.dkey[0], s.dval[0], s.hist);
+  gs_launch(preprocess_kernel, dim3(blocks), dim3(256), 0, st, a, g, s.dkey[0], s.dval[0], s.hist);
   return gs_check(cudaGetLastError());
 }
 

@@ -36,6 +36,7 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
                      const unsigned long long* __restrict__ n_ptr, unsigned long long n_cap, int shift,
                      const uint32_t* __restrict__ hist, uint32_t* __restrict__ status, uint32_t* __restrict__ ticket,
                      unsigned int* __restrict__ error_flag) {
+  GS_PDL_PROLOGUE();
   constexpr int WARPS = GS_SORT_THREADS / 32;
   __shared__ uint32_t s_warp_hist[WARPS][256];
   __shared__ uint32_t s_digit_base[256];
@@ -105,17 +106,30 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
   st_volatile(my_status, (tile == 0 ? FLAG_INCL : FLAG_LOCAL) | run);
   uint32_t excl = 0;
   if (tile > 0) {
+    // Decoupled look-back, 8 predecessors per round trip: when all CTAs start together nobody has an inclusive prefix
+    // yet and a serial walk costs one L2 latency per predecessor (the whole pass at small sizes).
     long long t = (long long)tile - 1;
     uint32_t spins = 0;
-    while (t >= 0) {
-      uint32_t sv = ld_volatile(status + (size_t)t * 256 + d);
-      if (sv == 0) {
-        if (++spins > SPIN_LIMIT) { atomicExch(error_flag, 1u); break; }
-        continue;
+    bool finished = false;
+    while (!finished && t >= 0) {
+      uint32_t sv[8];
+#pragma unroll
+      for (int k = 0; k < 8; k++) sv[k] = (t - k >= 0) ? ld_volatile(status + (size_t)(t - k) * 256 + d) : FLAG_INCL;
+      int used = 8;
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        if (k < used) {
+          if (sv[k] == 0) { used = k; }           // not published yet: retry from this predecessor
+          else {
+            excl += sv[k] & VALUE_MASK;
+            if (sv[k] & FLAG_INCL) { finished = true; used = k; }
+          }
+        }
       }
-      excl += sv & VALUE_MASK;
-      if (sv & FLAG_INCL) break;
-      t--;
+      if (!finished) {
+        t -= used;
+        if (used == 0 && ++spins > SPIN_LIMIT) { atomicExch(error_flag, 1u); break; }
+      }
     }
     st_volatile(my_status, FLAG_INCL | (excl + run));
   }
@@ -155,6 +169,7 @@ emit_kernel(int P, const uint32_t* __restrict__ sorted_gid, const uint32_t* __re
             const uint32_t* __restrict__ rect, int grid_x, unsigned long long cap, uint32_t* __restrict__ tkey,
             uint32_t* __restrict__ tval, uint32_t* __restrict__ hist /* [4][256] tile-id digits */, int tile_passes,
             unsigned long long* __restrict__ scan_status, uint32_t* __restrict__ ticket, GsHeader* __restrict__ hdr) {
+  GS_PDL_PROLOGUE();
   constexpr int WARPS = GS_EMIT_THREADS / 32;
   __shared__ uint32_t s_hist[4 * 256];
   __shared__ unsigned long long s_wsum[WARPS];
@@ -243,6 +258,7 @@ emit_kernel(int P, const uint32_t* __restrict__ sorted_gid, const uint32_t* __re
 // identifyTileRanges, rasterizer_impl.cu:116-138 (ranges zeroed beforehand, :310)
 __global__ void tile_ranges_kernel(const uint32_t* __restrict__ tkey_sorted, const unsigned long long* __restrict__ n_ptr,
                                    unsigned long long cap, uint2* __restrict__ ranges) {
+  GS_PDL_PROLOGUE();
   unsigned long long n = *n_ptr;
   if (n > cap) n = cap;
   for (unsigned long long idx = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; idx < n;
@@ -262,6 +278,7 @@ __global__ void tile_ranges_kernel(const uint32_t* __restrict__ tkey_sorted, con
 __global__ void __launch_bounds__(1024)
 plan_kernel(int tiles, const uint2* __restrict__ ranges, uint32_t* __restrict__ seg_off, uint2* __restrict__ items,
             uint32_t max_items, uint32_t* __restrict__ order) {
+  GS_PDL_PROLOGUE();
   __shared__ uint32_t s_w[32];
   __shared__ uint32_t s_carry;
   __shared__ uint32_t s_bucket[33], s_cursor[33];
@@ -340,7 +357,7 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   const bool small_d = gs_sort_items((unsigned long long)P) == GS_SORT_ITEMS_SMALL;
   for (int p = 0; p < 4; p++) {
     auto kern = small_d ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL> : onesweep_pass_kernel<GS_SORT_ITEMS>;
-    kern<<<blocks_d, GS_SORT_THREADS, 0, st>>>(
+    gs_launch(kern, dim3(blocks_d), dim3(GS_SORT_THREADS), 0, st,
         s.dkey[p & 1], s.dkey[(p + 1) & 1], s.dval[p & 1], s.dval[(p + 1) & 1], nullptr, (unsigned long long)P, 8 * p,
         s.hist + p * 256, s.status_d + (size_t)p * s.blocks_d * 256, s.counters + p, &g.hdr->error);
   }
@@ -352,7 +369,7 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   // the LAST tile pass must write into `list`: choose the start buffer by parity
   uint32_t* vbuf[2] = {s.tval[0], s.tval[1]};
   const int blocks_e = (P + GS_EMIT_THREADS - 1) / GS_EMIT_THREADS;
-  emit_kernel<<<blocks_e, GS_EMIT_THREADS, 0, st>>>(P, s.dval[0], g.tiles_touched, g.rect, gx, (unsigned long long)cap,
+  gs_launch(emit_kernel, dim3(blocks_e), dim3(GS_EMIT_THREADS), 0, st, P, s.dval[0], g.tiles_touched, g.rect, gx, (unsigned long long)cap,
                                                     s.tkey[0], vbuf[0], s.hist + 4 * 256, tile_passes, s.scan_status,
                                                     s.counters + 8, g.hdr);
   // 3. stable sort of the pairs by tile id
@@ -361,7 +378,7 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   for (int p = 0; p < tile_passes; p++) {
     uint32_t* vout = (p == tile_passes - 1) ? list : vbuf[(p + 1) & 1];
     auto kern = small_t ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL> : onesweep_pass_kernel<GS_SORT_ITEMS>;
-    kern<<<blocks_t, GS_SORT_THREADS, 0, st>>>(
+    gs_launch(kern, dim3(blocks_t), dim3(GS_SORT_THREADS), 0, st,
         s.tkey[p & 1], s.tkey[(p + 1) & 1], vbuf[p & 1], vout, &g.hdr->num_rendered, (unsigned long long)cap, 8 * p,
         s.hist + (4 + p) * 256, s.status_t + (size_t)p * s.blocks_t * 256, s.counters + 4 + p, &g.hdr->error);
   }
@@ -369,8 +386,8 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   int rb = (int)((cap + 255) / 256);
   if (rb > 148 * 16) rb = 148 * 16;
   if (rb < 1) rb = 1;
-  tile_ranges_kernel<<<rb, 256, 0, st>>>(s.tkey[tile_passes & 1], &g.hdr->num_rendered, (unsigned long long)cap, im.ranges);
+  gs_launch(tile_ranges_kernel, dim3(rb), dim3(256), 0, st, s.tkey[tile_passes & 1], &g.hdr->num_rendered, (unsigned long long)cap, im.ranges);
   // 5. backward work plan (segments of GS_SEG entries per tile)
-  plan_kernel<<<1, 1024, 0, st>>>(tiles, im.ranges, im.seg_off, l.items, (uint32_t)l.max_items, im.order);
+  gs_launch(plan_kernel, dim3(1), dim3(1024), 0, st, tiles, im.ranges, im.seg_off, l.items, (uint32_t)l.max_items, im.order);
   return gs_check(cudaGetLastError());
 }
