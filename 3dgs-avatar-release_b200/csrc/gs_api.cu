@@ -155,6 +155,20 @@ int gs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, co
   return gs_launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
 }
 
+/* sizeof of the ABI structs (0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs):
+ * lets a binding check its own struct declarations against the library it loaded */
+size_t gs_sizeof(int32_t which) {
+  switch (which) {
+    case 0: return sizeof(GsForwardArgs);
+    case 1: return sizeof(GsBackwardArgs);
+    case 2: return sizeof(PoseArgs);
+    case 3: return sizeof(PoseBackwardArgs);
+    case 4: return sizeof(NonRigidArgs);
+    case 5: return sizeof(SkinArgs);
+    default: return 0;
+  }
+}
+
 void gs_profile_enable(int on) { g_prof_on = on; }
 
 /* ms[7] = preprocess, binning (sorts+emit+ranges), blend fwd, blend bwd, preprocess bwd, pose fwd, pose bwd of the LAST call

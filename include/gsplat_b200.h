@@ -249,6 +249,8 @@ void gs_profile_enable(int on);
 int gs_profile_read(float* ms_host /* [7]: preprocess, binning, blend fwd, blend bwd, preprocess bwd, pose fwd, pose bwd */);
 int gs_fma_probe(int blocks, int threads, int iters, float* out_dev, void* stream);
 
+/* sizeof of the ABI structs: 0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs */
+size_t gs_sizeof(int32_t which);
 int gs_last_cuda_error(void);
 const char* gs_version(void);
 

@@ -47,6 +47,15 @@ def test_struct_layout_matches_header(built_lib):
     assert ctypes.sizeof(_C.GsBackwardArgs) == 40 + 21 * 8
     assert ctypes.sizeof(avatar_pose.PoseArgs) == 24 + 15 * 8
     assert ctypes.sizeof(avatar_pose.PoseBackwardArgs) == ctypes.sizeof(avatar_pose.PoseArgs) + 11 * 8
+    # and against the library itself
+    from avatar_pose.nonrigid import NonRigidArgs
+    from avatar_pose.skinning import SkinArgs
+    L = _C.lib()
+    L.gs_sizeof.restype = ctypes.c_size_t
+    L.gs_sizeof.argtypes = [ctypes.c_int32]
+    for which, st in enumerate((_C.GsForwardArgs, _C.GsBackwardArgs, avatar_pose.PoseArgs, avatar_pose.PoseBackwardArgs,
+                                NonRigidArgs, SkinArgs)):
+        assert L.gs_sizeof(which) == ctypes.sizeof(st), st.__name__
 
 
 def test_no_cpu_fallback(built_lib):

@@ -195,3 +195,42 @@ def test_stress_1m_1080p_properties(built_lib):
     out2 = run_cuda(sc)
     assert np.array_equal(out2["img"].view(np.uint32), out["img"].view(np.uint32)), "forward not run-to-run identical"
     assert out2["N"] == N and np.array_equal(out2["dbg"]["point_list"], dbg["point_list"])
+
+
+def test_graph_capture_and_capacity_overflow_recapture(built_lib):
+    """CUDA-graph replay of forward+backward equals the eager result; a pair capacity that is too small for the frame is
+    detected after the replay, the step is re-captured with a larger capacity and re-run (avatar_pose.graphs.GraphedStep)."""
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, _C
+    from avatar_pose.graphs import GraphedStep
+    dev = _dev()
+    sc = scenes.avatar_scene(P=20000, W=256, H=256)
+    fw = scenes.oracle_forward(sc)
+    cam = sc["cam"]
+    d = lambda a: torch.as_tensor(np.ascontiguousarray(a)).to(dev)
+    rs = GaussianRasterizationSettings(256, 256, cam["tanfovx"], cam["tanfovy"], d(sc["bg"]), 1.0, d(cam["world_view_transform"]),
+                                       d(cam["full_proj_transform"]), 3, d(cam["camera_center"]), False, False)
+    means = d(sc["means3D"]).requires_grad_(True)
+    cols, cov, op = d(sc["colors_precomp"]).requires_grad_(True), d(sc["cov3D_precomp"]), d(sc["opacities"])
+
+    def step():
+        means.grad = None
+        cols.grad = None
+        img, radii = GaussianRasterizer(rs)(means3D=means, means2D=torch.zeros_like(means, requires_grad=True), opacities=op,
+                                            colors_precomp=cols, cov3D_precomp=cov)
+        img.mean().backward()
+        return img
+
+    g = GraphedStep(step)
+    img = g.replay(check=True).clone()
+    grad = means.grad.clone()
+    assert np.array_equal(img.detach().cpu().numpy().view(np.uint32), fw["color"].view(np.uint32))
+    # now force an overflow: shrink the capacity the NEXT capture will use, re-capture, replay with the check
+    st = _C._dev_state(dev)
+    assert fw["N"] > 8192
+    st.capacity = 4096
+    regrows = _C.stats["capacity_regrows"]
+    g.capture()
+    img2 = g.replay(check=True)
+    assert _C.stats["capacity_regrows"] > regrows and st.capacity >= fw["N"]
+    assert np.array_equal(img2.detach().cpu().numpy().view(np.uint32), fw["color"].view(np.uint32))
+    assert torch.allclose(means.grad, grad, rtol=1e-4, atol=1e-9)
