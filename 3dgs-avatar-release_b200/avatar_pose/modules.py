@@ -70,11 +70,13 @@ class FusedGaussianConverter(nn.Module):
         if self.non_rigid is not None and iteration >= self.non_rigid.delay:  # non_rigid.py:227-232
             cond = self.pose_encoder(camera.rots, camera.Jtrs) if self.pose_encoder is not None else \
                 torch.zeros(self.non_rigid.n_cond, device=xyz.device)
-            xyz, scaling, rotation, deltas = self.non_rigid.deform(xyz, scaling, rotation, cond)
+            deform = self.non_rigid.deform_autograd if torch.is_grad_enabled() else self.non_rigid.deform
+            xyz, scaling, rotation, deltas = deform(xyz, scaling, rotation, cond)
             if compute_loss:  # non_rigid.py:288-297
                 loss_reg = {"nr_xyz": deltas[:, :3].norm(p=2, dim=1).mean(), "nr_scale": deltas[:, 3:6].norm(p=1, dim=1).mean(),
                             "nr_rot": deltas[:, 7:10].norm(p=1, dim=1).mean()}
-        weights = self.rigid.query_weights(xyz)  # evaluated at the non-rigidly displaced position (rigid.py:217-220)
+        query = getattr(self.rigid, "query_weights_autograd", None) if torch.is_grad_enabled() else None
+        weights = (query or self.rigid.query_weights)(xyz)  # at the non-rigidly displaced position (rigid.py:217-220)
         means, cov, colors, opacity, T_fwd, Rbar = fused_pose(
             xyz, rotation, scaling, g._opacity, g._features_dc, g._features_rest, weights, camera.bone_transforms,
             camera.camera_center, g.active_sh_degree, 1.0, self.cano_view_dir, return_aux=True)

@@ -1,8 +1,10 @@
 """Non-rigid deformation (forward) of the canonical Gaussians on the tensor cores: host side of `nonrigid_forward`
 (include/gsplat_b200.h).  Mirrors HashGridwithMLP (models/deformer/non_rigid.py:203-300, registry key `hashgrid`):
 multiresolution hash grid (16 levels x 2 features) + VanillaCondMLP (32+C -> 128 -> 128 -> 128 -> 10+feature_dim,
-LeakyReLU) + delta application.  Forward only in this round (rendering / evaluation path; `iteration < delay` is the
-identity exactly as in the reference).  There is no CPU fallback."""
+LeakyReLU) + delta application; `iteration < delay` is the identity exactly as in the reference.  The forward is the
+tcgen05 kernel (`deform`); `deform_autograd` wraps it in an autograd.Function whose backward re-evaluates the stage with
+torch ops on the GPU (`_torch_ref.py`) to obtain parameter / input gradients -- a native backward is the next step.
+There is no CPU fallback."""
 import ctypes
 import math
 
@@ -11,6 +13,7 @@ import torch
 import torch.nn as nn
 
 from diff_gaussian_rasterization import _C as _gs
+from . import _torch_ref
 
 vp = ctypes.c_void_p
 NR_MAX_LEVELS = 32
@@ -116,3 +119,36 @@ class HashGridMLPFused(nn.Module):
         if return_features:
             return out_xyz, out_sc, out_rot, deltas, feats
         return out_xyz, out_sc, out_rot, deltas
+
+    def deform_autograd(self, xyz, scaling, rotation, cond, iteration=None):
+        """Differentiable `deform`: forward on the tcgen05 kernel, gradients to xyz / scaling / rotation / cond, the hash
+        table and the four linear layers (non_rigid.py:248-282 under autograd in the reference)."""
+        if iteration is not None and iteration < self.delay:
+            return xyz, scaling, rotation, None
+        params = [self.table] + [t for l in (self.lin0, self.lin1, self.lin2, self.lin3) for t in (l.weight, l.bias)]
+        return _NonRigidFn.apply(self, xyz, scaling, rotation, cond, *params)
+
+
+class _NonRigidFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mod, xyz, scaling, rotation, cond, *params):
+        ctx.mod = mod
+        ctx.save_for_backward(xyz, scaling, rotation, cond, *params)
+        return mod.deform(xyz, scaling, rotation, cond)
+
+    @staticmethod
+    def backward(ctx, g_xyz, g_sc, g_rot, g_d):
+        mod = ctx.mod
+        leaves = [t.detach().float().requires_grad_(True) for t in ctx.saved_tensors]
+        xyz, scaling, rotation, cond, table = leaves[:5]
+        Ws, bs = leaves[5::2], leaves[6::2]
+        with torch.enable_grad():
+            outs = _torch_ref.nonrigid(xyz, scaling, rotation, cond, table, Ws, bs, mod.aabb_min, mod.aabb_max, mod.levels)
+            pairs = [(o, g) for o, g in zip(outs, (g_xyz, g_sc, g_rot, g_d)) if g is not None]
+            need = [i for i, n in enumerate(ctx.needs_input_grad[1:]) if n]
+            grads = torch.autograd.grad([o for o, _ in pairs], [leaves[i] for i in need], [g for _, g in pairs],
+                                        allow_unused=True)
+        out = [None] * len(leaves)
+        for i, g in zip(need, grads):
+            out[i] = g
+        return (None, *out)

@@ -1,13 +1,16 @@
 """Skinning field (forward): per-Gaussian LBS weights from the skinning MLP on the tensor cores -- host side of
 `skinning_forward` (include/gsplat_b200.h).  Mirrors the weight part of SkinningField (models/deformer/rigid.py:131-236,
 registry key `skinning_field`, non-distilled path): `lbs_network` = VanillaCondMLP(3 -> 128 x4 -> 25), hierarchical
-softmax.  The result feeds `avatar_pose.fused_pose(..., weights, ...)`.  Forward only this round; no CPU fallback."""
+softmax.  The result feeds `avatar_pose.fused_pose(..., weights, ...)`.  `query_weights` is the tcgen05 forward;
+`query_weights_autograd` adds a backward that re-evaluates the MLP with torch ops on the GPU (`_torch_ref.py`; a native
+backward is the next step).  No CPU fallback."""
 import ctypes
 
 import torch
 import torch.nn as nn
 
 from diff_gaussian_rasterization import _C as _gs
+from . import _torch_ref
 
 vp = ctypes.c_void_p
 
@@ -74,3 +77,29 @@ class SkinningFieldFused(nn.Module):
                 _gs._check(L.skinning_forward(ctypes.byref(a), self._ws.data_ptr(), self._ws.numel(),
                                               torch.cuda.current_stream(dev).cuda_stream), "skinning_forward")
         return (weights, logits) if return_logits else weights
+
+    def query_weights_autograd(self, xyz):
+        """Differentiable `query_weights`: gradients to xyz and to the five linear layers (rigid.py:205-212)."""
+        params = [t for l in range(5) for t in (getattr(self, f"lin{l}").weight, getattr(self, f"lin{l}").bias)]
+        return _SkinFn.apply(self, xyz, *params)
+
+
+class _SkinFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mod, xyz, *params):
+        ctx.mod = mod
+        ctx.save_for_backward(xyz, *params)
+        return mod.query_weights(xyz)
+
+    @staticmethod
+    def backward(ctx, g_w):
+        mod = ctx.mod
+        leaves = [t.detach().float().requires_grad_(True) for t in ctx.saved_tensors]
+        with torch.enable_grad():
+            w = _torch_ref.skinning_weights(leaves[0], leaves[1::2], leaves[2::2], mod.aabb_min, mod.aabb_max)
+            need = [i for i, n in enumerate(ctx.needs_input_grad[1:]) if n]
+            grads = torch.autograd.grad([w], [leaves[i] for i in need], [g_w], allow_unused=True)
+        out = [None] * len(leaves)
+        for i, g in zip(need, grads):
+            out[i] = g
+        return (None, *out)

@@ -56,3 +56,58 @@ def test_converter_smpl_nn_matches_oracle_and_renders(built_lib):
     assert (radii > 0).sum() > 100 and torch.isfinite(img).all()
     assert gm._xyz.grad is not None and torch.isfinite(gm._xyz.grad).all() and float(gm._xyz.grad.abs().max()) > 0
     assert gm._features_rest.grad is not None and screenspace.grad is not None
+
+
+def test_converter_full_chain_trains_every_parameter(built_lib):
+    """non-rigid (hash grid + MLP) -> skinning field -> fused posing -> rasterizer -> loss.backward(): every trainable
+    tensor of the chain (Gaussians, hash table, both MLPs) receives a finite, non-zero gradient; a small step down the
+    gradient (max |delta| 1e-4 per tensor) lowers an L2 image loss against a perturbed target."""
+    from avatar_pose.modules import FusedGaussianConverter
+    from avatar_pose.nonrigid import HashGridMLPFused
+    from avatar_pose.skinning import SkinningFieldFused
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    dev = torch.device("cuda:0")
+    torch.manual_seed(0)
+    P = 4000
+    g = synth.canonical_gaussians(P, seed=3)
+    gm = types.SimpleNamespace(active_sh_degree=3, max_sh_degree=3)
+    for k in ("xyz", "rotation", "scaling", "opacity", "features_dc", "features_rest"):
+        setattr(gm, "_" + k, torch.from_numpy(g[k]).to(dev).requires_grad_(True))
+    lo, hi = (g["xyz"].min(0) - 0.05).tolist(), (g["xyz"].max(0) + 0.05).tolist()
+    nr = HashGridMLPFused(n_cond=144, aabb_min=lo, aabb_max=hi, delay=10)
+    sk = SkinningFieldFused(aabb_min=lo, aabb_max=hi)
+    with torch.no_grad():
+        nr.table.mul_(300.0)
+        nr.lin3.weight.mul_(0.05)
+        sk.lin4.weight.mul_(4.0)
+    enc = lambda rots, Jtrs: torch.full((1, 144), 0.1, device=dev)
+    conv = FusedGaussianConverter(sk, nr, enc).to(dev)
+    ps, cam = synth.pose(2), synth.camera(W=128, H=128, fx=134.0, fy=134.0)
+    camera = types.SimpleNamespace(bone_transforms=torch.from_numpy(ps["bone_transforms"]).to(dev),
+                                   camera_center=torch.from_numpy(cam["camera_center"]).to(dev), rots=None, Jtrs=None)
+    d = lambda a: torch.as_tensor(np.ascontiguousarray(a)).to(dev)
+    rs = GaussianRasterizationSettings(128, 128, cam["tanfovx"], cam["tanfovy"], torch.zeros(3, device=dev), 1.0,
+                                       d(cam["world_view_transform"]), d(cam["full_proj_transform"]), 3, d(cam["camera_center"]), False, False)
+
+    def render(iteration):
+        deformed, loss_reg, colors = conv(gm, camera, iteration)
+        img, _ = GaussianRasterizer(rs)(means3D=deformed.get_xyz, means2D=torch.zeros_like(deformed.get_xyz, requires_grad=True),
+                                        opacities=deformed.get_opacity, colors_precomp=colors,
+                                        cov3D_precomp=deformed.get_covariance(1.0))
+        return img, loss_reg
+
+    with torch.no_grad():
+        target = render(100)[0] * 0.8 + 0.05
+        assert render(0)[1] == {}  # before `delay`: identity, no regulariser
+    params = [p for p in conv.parameters()] + [getattr(gm, "_" + k) for k in ("xyz", "rotation", "scaling", "opacity", "features_dc", "features_rest")]
+    img, loss_reg = render(100)
+    assert set(loss_reg) == {"nr_xyz", "nr_scale", "nr_rot"}
+    loss0 = ((img - target) ** 2).mean()
+    (loss0 + 0.01 * sum(loss_reg.values())).backward()
+    for name, p in list(conv.named_parameters()) + [("xyz", gm._xyz), ("rot", gm._rotation), ("scale", gm._scaling)]:
+        assert p.grad is not None and torch.isfinite(p.grad).all() and float(p.grad.abs().max()) > 0, name
+    with torch.no_grad():
+        for p in params:
+            p -= p.grad * (1e-4 / float(p.grad.abs().max()))
+        loss1 = ((render(100)[0] - target) ** 2).mean()
+    assert float(loss1) < float(loss0.detach()), (float(loss0.detach()), float(loss1))

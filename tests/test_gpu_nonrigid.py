@@ -87,3 +87,75 @@ def test_skinning_field_weights(built_lib, P, d_out):
     means = fused_pose(t("xyz"), t("rotation"), t("scaling"), t("opacity"), t("features_dc"), t("features_rest"), wts,
                        torch.from_numpy(ps["bone_transforms"]).to(dev), torch.zeros(3, device=dev), 3)[0]
     assert torch.isfinite(means).all()
+
+
+def test_nonrigid_and_skinning_gradients(built_lib):
+    """deform_autograd / query_weights_autograd: forward values from the tcgen05 kernels, gradients (inputs, hash table,
+    linear layers) against fp64 autograd of the oracle, <= 2e-3 of each gradient's max (fp32 re-evaluation + FP32 hash
+    positions)."""
+    from avatar_pose.nonrigid import HashGridMLPFused
+    from avatar_pose.skinning import SkinningFieldFused
+    dev = torch.device("cuda:0")
+    torch.manual_seed(11)
+    P = 3000
+    g = synth.canonical_gaussians(P, seed=2)
+    xyz, sc, rot = (torch.from_numpy(g[k]) for k in ("xyz", "scaling", "rotation"))
+    lo, hi = xyz.min(0).values - 0.05, xyz.max(0).values + 0.05
+    m = HashGridMLPFused(n_cond=144, aabb_min=lo.tolist(), aabb_max=hi.tolist())
+    with torch.no_grad():
+        m.table.mul_(3000.0)
+        m.lin3.weight.mul_(0.3)
+    cond = torch.randn(144) * 0.5
+    gouts = [torch.randn(P, 3), torch.randn(P, 3), torch.randn(P, 4), torch.randn(P, 10) * 0.1]
+    # fp64 oracle under autograd
+    d64 = lambda t: t.detach().cpu().double().requires_grad_(True)
+    r_in = [d64(t) for t in (xyz, sc, rot, cond, m.table)]
+    rW = [d64(l.weight) for l in (m.lin0, m.lin1, m.lin2, m.lin3)]
+    rb = [d64(l.bias) for l in (m.lin0, m.lin1, m.lin2, m.lin3)]
+    ref = nro.nonrigid_forward(r_in[0], r_in[1], r_in[2], m.aabb_min.double(), m.aabb_max.double(), r_in[4], m.levels,
+                               r_in[3], rW, rb)
+    loss = sum((ref[k] * go.double()).sum() for k, go in zip(("xyz", "scaling", "rotation", "deltas"), gouts))
+    loss.backward()
+    # ours
+    md = m.to(dev)
+    ins = [t.to(dev).requires_grad_(True) for t in (xyz, sc, rot, cond)]
+    outs = md.deform_autograd(*ins)
+    sum((o * go.to(dev)).sum() for o, go in zip(outs, gouts)).backward()
+    torch.cuda.synchronize()
+
+    def close(a, b, name, robust=False):
+        a, b = a.detach().cpu().double(), b.detach().double()
+        s = float(b.abs().max())
+        assert s > 0, name
+        err = (a - b).abs().flatten()
+        if robust:  # d(feature)/d(position) is piecewise constant per cell: an FP32 position within ~1e-4 cells of a cell
+            # face of the finest levels (scale 2047) falls into the neighbouring cell of the fp64 oracle
+            assert float(err.quantile(0.995)) <= 2e-3 * s and float(err.max()) <= 5e-2 * s, (name, float(err.max()), s)
+        else:
+            assert float(err.max()) <= 2e-3 * s, (name, float(err.max()), s)
+
+    for a, b, name in zip(ins, r_in[:4], ("xyz", "scaling", "rotation", "cond")):
+        close(a.grad, b.grad, name, robust=(name == "xyz"))
+    close(md.table.grad, r_in[4].grad, "table", robust=True)  # same cell-face effect: the scatter lands next door
+    for l, (lin, w, bb) in enumerate(zip((md.lin0, md.lin1, md.lin2, md.lin3), rW, rb)):
+        close(lin.weight.grad, w.grad, f"W{l}")
+        close(lin.bias.grad, bb.grad, f"b{l}")
+
+    # skinning field
+    s = SkinningFieldFused(aabb_min=lo.tolist(), aabb_max=hi.tolist())
+    with torch.no_grad():
+        s.lin4.weight.mul_(8.0)
+    gw = torch.randn(P, 24)
+    x64 = d64(xyz)
+    sW = [d64(getattr(s, f"lin{l}").weight) for l in range(5)]
+    sb = [d64(getattr(s, f"lin{l}").bias) for l in range(5)]
+    w_ref, _ = nro.skinning_weights_forward(x64, s.aabb_min.double(), s.aabb_max.double(), sW, sb)
+    (w_ref * gw.double()).sum().backward()
+    sd = s.to(dev)
+    x = xyz.to(dev).requires_grad_(True)
+    w = sd.query_weights_autograd(x)
+    (w * gw.to(dev)).sum().backward()
+    close(x.grad, x64.grad, "skin xyz")
+    for l in range(5):
+        close(getattr(sd, f"lin{l}").weight.grad, sW[l].grad, f"skin W{l}")
+        close(getattr(sd, f"lin{l}").bias.grad, sb[l].grad, f"skin b{l}")
