@@ -70,6 +70,7 @@ struct GsScratch {
   uint32_t* status_d;       // [4][blocks_d][256] onesweep look-back status, depth passes
   uint32_t* status_t;       // [4][blocks_t][256] onesweep look-back status, tile passes
   unsigned long long* scan_status;  // [blocks_e] emit-kernel look-back
+  uint32_t* tile_total;     // [tiles] pairs per tile (direct placement)
   uint32_t* zero_end;
   size_t blocks_d, blocks_t, blocks_e;
 };
@@ -126,6 +127,10 @@ static inline __host__ size_t gs_carve_list(char* base, int64_t cap, int W, int 
 #define GS_SORT_THREADS 256
 #define GS_SORT_TILE (GS_SORT_ITEMS * GS_SORT_THREADS)   // 4096 keys per CTA
 #define GS_EMIT_THREADS 256
+#define GS_BIN_THREADS 1024                                // direct placement: Gaussians per block
+#define GS_BIN_FUSED_MAX_BLOCKS 120                        // count+place in one co-resident grid up to this many blocks
+#define GS_BIN_TILE_BITS 11                                // log2(GS_BIN_MAX_TILES)
+#define GS_BIN_MAX_TILES 2048                              // ... and the largest tile grid it handles (68 B smem per tile)
 
 static inline __host__ __device__ int gs_sort_items(unsigned long long n) { return n <= GS_SORT_SMALL_MAX ? GS_SORT_ITEMS_SMALL : GS_SORT_ITEMS; }
 static inline __host__ size_t gs_sort_blocks(unsigned long long n) {
@@ -133,8 +138,13 @@ static inline __host__ size_t gs_sort_blocks(unsigned long long n) {
   return ((size_t)n + tile - 1) / tile;
 }
 
+// Direct placement needs the [blocks][tiles] count matrix to fit the pair-sized scratch it borrows.
+static inline __host__ bool gs_direct_binning(int P, int tiles, int64_t cap) {
+  const int64_t blocks = ((int64_t)P + GS_BIN_THREADS - 1) / GS_BIN_THREADS;
+  return tiles <= GS_BIN_MAX_TILES && blocks * tiles <= cap;
+}
+
 static inline __host__ size_t gs_carve_scratch(char* base, int P, int W, int H, int64_t cap, GsScratch* s) {
-  (void)W; (void)H;
   char* p = base;
   GsScratch t;
   t.blocks_d = gs_sort_blocks((unsigned long long)P) + 1;
@@ -150,6 +160,7 @@ static inline __host__ size_t gs_carve_scratch(char* base, int P, int W, int H, 
   gs_carve(p, t.status_d, 4 * t.blocks_d * 256);
   gs_carve(p, t.status_t, 4 * t.blocks_t * 256);
   gs_carve(p, t.scan_status, t.blocks_e);
+  gs_carve(p, t.tile_total, (size_t)((W + GS_TILE - 1) / GS_TILE) * ((H + GS_TILE - 1) / GS_TILE));
   t.zero_end = reinterpret_cast<uint32_t*>(p);
   if (s) *s = t;
   return (size_t)(p - base);

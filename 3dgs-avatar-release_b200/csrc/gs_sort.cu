@@ -12,11 +12,16 @@
 // Stability of step 3 preserves the depth order of step 1 inside each tile; ties in depth keep ascending Gaussian
 // index because step 1 is stable too, which is exactly the tie order of the reference's stable sort.
 //
+// When the tile grid is small enough for per-warp tile counters in shared memory (<= GS_BIN_MAX_TILES tiles: every avatar
+// configuration), steps 2-4 are replaced by DIRECT placement, with no pair sort at all: blocks of 1024 depth-sorted
+// Gaussians count their pairs per tile (count kernel), and the place kernel writes every Gaussian index straight to
+//   tile_start[tile] + (pairs of earlier blocks) + (pairs of earlier warps) + (rank inside the warp),
+// walking the Gaussians of a warp one after the other so that the order inside a tile stays the depth order.
+//
 // onesweep pass: one kernel per 8-bit digit; warp-level multi-split with __match_any_sync, per-warp digit counters
 // in shared memory, CTA-wide digit offsets, decoupled look-back across CTAs on a (flag|count) status word per
 // (CTA, digit); digit histograms come for free from the producing kernels (preprocess / emit).
 #include "gs_common.cuh"
-
 namespace {
 
 #define FLAG_LOCAL 0x40000000u
@@ -24,19 +29,37 @@ namespace {
 #define VALUE_MASK 0x3FFFFFFFu
 #define SPIN_LIMIT (1u << 26)
 
+// Lanes holding the same BITS-bit value (valid lanes only), from BITS ballots.  MATCH.ANY has a long, serialised
+// latency; with 32 warps per SM ranking at once (direct placement) the ballots are no slower and do not contend.
+template <int BITS>
+__device__ __forceinline__ uint32_t match_ballot(uint32_t v, bool valid) {
+  uint32_t m = __ballot_sync(0xFFFFFFFFu, valid);
+#pragma unroll
+  for (int b = 0; b < BITS; b++) {
+    const bool bit = (v >> b) & 1u;
+    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, bit);
+    m &= bit ? bal : ~bal;
+  }
+  return m;
+}
+
 __device__ __forceinline__ uint32_t ld_volatile(const uint32_t* p) { return *reinterpret_cast<const volatile uint32_t*>(p); }
 __device__ __forceinline__ void st_volatile(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
 
 // One stable 8-bit radix pass.  n is read from n_ptr when non-null (clipped to n_cap), else n = n_cap.
 // A pass whose digit is the same for every key (e.g. the top byte of avatar depths) degenerates to a straight copy.
+// chain_pass >= 0 (depth sort): the pass is link `chain_pass` of a chain over the ping-pong buffers (keys_in, keys_out) /
+// (vals_in, vals_out) = (buffer 0, buffer 1); constant-digit passes are skipped WITHOUT a copy, so a pass reads the buffer
+// selected by the number of effective passes before it (all histograms, `hist_chain`, exist before the first pass) and the
+// consumers locate the result with depth_result_buffer().  chain_pass < 0: fixed buffers, constant digit = plain copy.
 template <int ITEMS>
 __global__ void __launch_bounds__(GS_SORT_THREADS)
-onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
-                     const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
+onesweep_pass_kernel(const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
                      const unsigned long long* __restrict__ n_ptr, unsigned long long n_cap, int shift,
                      const uint32_t* __restrict__ hist, uint32_t* __restrict__ status, uint32_t* __restrict__ ticket,
-                     unsigned int* __restrict__ error_flag) {
+                     unsigned int* __restrict__ error_flag, int chain_pass, const uint32_t* __restrict__ hist_chain) {
   GS_PDL_PROLOGUE();
+  constexpr int LB = ITEMS <= 4 ? 32 : 8;  // look-back width: predecessors fetched per round trip
   constexpr int WARPS = GS_SORT_THREADS / 32;
   __shared__ uint32_t s_warp_hist[WARPS][256];
   __shared__ uint32_t s_digit_base[256];
@@ -45,6 +68,11 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   unsigned long long n = n_cap;
   if (n_ptr) { unsigned long long nn = *n_ptr; n = nn < n_cap ? nn : n_cap; }
+  // histogram words first: their latency overlaps the ticket round trip
+  const uint32_t h_own = hist[tid];
+  uint32_t h_prev[3] = {0u, 0u, 0u};
+#pragma unroll
+  for (int q = 0; q < 3; q++) if (q < chain_pass) h_prev[q] = hist_chain[q * 256 + tid];
   if (tid == 0) s_ticket = atomicAdd(ticket, 1u);
 #pragma unroll
   for (int i = 0; i < WARPS; i++) s_warp_hist[i][tid] = 0;
@@ -52,6 +80,18 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
   const uint32_t tile = s_ticket;
   const unsigned long long base = (unsigned long long)tile * (ITEMS * GS_SORT_THREADS);
   if (base >= n) return;
+  const bool constant = __syncthreads_or((unsigned long long)h_own == n);
+  if (chain_pass >= 0) {
+    if (constant) return;
+    int effective = 0;
+#pragma unroll
+    for (int q = 0; q < 3; q++)
+      if (q < chain_pass) effective += __syncthreads_or((unsigned long long)h_prev[q] == n) ? 0 : 1;
+    if (effective & 1) {
+      const uint32_t* t1 = keys_in; keys_in = keys_out; keys_out = const_cast<uint32_t*>(t1);
+      const uint32_t* t2 = vals_in; vals_in = vals_out; vals_out = const_cast<uint32_t*>(t2);
+    }
+  }
 
   // ---- load keys (warp-striped inside a warp-contiguous chunk) ----
   uint32_t key[ITEMS], val[ITEMS], rank[ITEMS];
@@ -63,7 +103,7 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
     val[i] = idx < n ? vals_in[idx] : 0u;  // payload loaded up front: its latency hides behind the ranking
   }
   // constant digit: the pass is the identity permutation
-  if (__syncthreads_or((unsigned long long)hist[tid] == n)) {
+  if (constant) {
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
       unsigned long long idx = wbase + i * 32 + lane;
@@ -106,18 +146,18 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
   st_volatile(my_status, (tile == 0 ? FLAG_INCL : FLAG_LOCAL) | run);
   uint32_t excl = 0;
   if (tile > 0) {
-    // Decoupled look-back, 8 predecessors per round trip: when all CTAs start together nobody has an inclusive prefix
+    // Decoupled look-back, LB predecessors per round trip: when all CTAs start together nobody has an inclusive prefix
     // yet and a serial walk costs one L2 latency per predecessor (the whole pass at small sizes).
     long long t = (long long)tile - 1;
     uint32_t spins = 0;
     bool finished = false;
     while (!finished && t >= 0) {
-      uint32_t sv[8];
+      uint32_t sv[LB];
 #pragma unroll
-      for (int k = 0; k < 8; k++) sv[k] = (t - k >= 0) ? ld_volatile(status + (size_t)(t - k) * 256 + d) : FLAG_INCL;
-      int used = 8;
+      for (int k = 0; k < LB; k++) sv[k] = (t - k >= 0) ? ld_volatile(status + (size_t)(t - k) * 256 + d) : FLAG_INCL;
+      int used = LB;
 #pragma unroll
-      for (int k = 0; k < 8; k++) {
+      for (int k = 0; k < LB; k++) {
         if (k < used) {
           if (sv[k] == 0) { used = k; }           // not published yet: retry from this predecessor
           else {
@@ -134,7 +174,7 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
     st_volatile(my_status, FLAG_INCL | (excl + run));
   }
   // exclusive scan of the global digit histogram over the 256 digits
-  uint32_t h = hist[d];
+  uint32_t h = h_own;
   uint32_t incl = h;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -162,10 +202,214 @@ onesweep_pass_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
   }
 }
 
+// Index (0/1) of the depth ping-pong buffer that holds the sorted result: the number of effective (non-constant) passes,
+// mod 2.  Block-wide call (>= 256 threads, all threads).
+__device__ __forceinline__ int depth_result_buffer(const uint32_t* __restrict__ hist_chain, unsigned long long n, int tid) {
+  int effective = 0;
+  for (int q = 0; q < 4; q++)
+    effective += __syncthreads_or(tid < 256 && (unsigned long long)hist_chain[q * 256 + tid] == n) ? 0 : 1;
+  return effective & 1;
+}
+
+// ---- direct placement (small tile grids) ----
+// A warp owns 32 depth-consecutive Gaussians.  Their (Gaussian, tile) pairs, in (Gaussian, row-major tile) order, are
+// handled 32 at a time, one pair per lane: the lane finds its Gaussian from the start positions of the rectangles inside
+// the 32-pair window (one warp-wide OR + popc), equal tiles inside the window are ranked with __match_any_sync, and the
+// first lane of every tile bumps this warp's per-tile counter (plain shared-memory read-modify-write).
+// COUNT: the counters end as the warp's pairs per tile.  PLACE: the counters start as the warp's exclusive offset inside
+// the block and every pair gets its slot.
+struct BinWarp {
+  uint32_t total;   // pairs of this warp
+  uint32_t excl;    // this lane: first pair index of its Gaussian
+  bool nz;          // this lane's Gaussian touches tiles
+};
+
+__device__ __forceinline__ BinWarp bin_load(int P, int i, const uint32_t* __restrict__ sorted_gid,
+                                            const uint32_t* __restrict__ tiles_touched, const uint32_t* __restrict__ rect,
+                                            uint4* __restrict__ stage_w, int lane) {
+  uint32_t gid = 0, cnt = 0;
+  uint2 r = make_uint2(0u, 0u);
+  if (i < P) {
+    gid = sorted_gid[i];
+    cnt = tiles_touched[gid];
+    if (cnt) r = *reinterpret_cast<const uint2*>(rect + 2 * (size_t)gid);
+  }
+  uint32_t incl = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  BinWarp bw;
+  bw.total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+  bw.excl = incl - cnt;
+  bw.nz = cnt != 0;
+  const uint32_t todo = __ballot_sync(0xFFFFFFFFu, bw.nz);
+  if (bw.nz) stage_w[__popc(todo & ((1u << lane) - 1u))] = make_uint4(bw.excl, gid, r.x, r.y);  // compacted
+  __syncwarp();
+  return bw;
+}
+
+template <bool PLACE>
+__device__ __forceinline__ void bin_warp_walk(const BinWarp bw, const uint4* __restrict__ stage_w, int grid_x,
+                                              uint16_t* __restrict__ s_off_w, const uint32_t* __restrict__ s_base,
+                                              uint32_t* __restrict__ list, unsigned long long cap, int lane) {
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  for (uint32_t B = 0; B < bw.total; B += 32) {
+    const uint32_t before = __popc(__ballot_sync(0xFFFFFFFFu, bw.nz && bw.excl < B));
+    const uint32_t bits = __reduce_or_sync(0xFFFFFFFFu, (bw.nz && bw.excl >= B && bw.excl < B + 32) ? (1u << (bw.excl - B)) : 0u);
+    const uint32_t k = B + lane;
+    const bool valid = k < bw.total;
+    uint32_t t = 0xFFFFFFFFu, gg = 0;
+    if (valid) {
+      const uint4 e = stage_w[before + __popc(bits & ((2u << lane) - 1u)) - 1];
+      const int x0 = e.z & 0xFFFF, y0 = e.z >> 16, wdt = (int)(e.w & 0xFFFF) - x0, j = (int)(k - e.x);
+      const int yy = __float2int_rz(__fdividef((float)j + 0.5f, (float)wdt));  // exact for these small integers
+      t = (uint32_t)((y0 + yy) * grid_x + x0 + (j - yy * wdt));
+      gg = e.y;
+    }
+    const uint32_t m = match_ballot<GS_BIN_TILE_BITS>(t, valid);
+    const int leader = __ffs(m) - 1;
+    uint32_t o = 0;
+    if (valid && lane == leader) {
+      o = s_off_w[t];
+      s_off_w[t] = (uint16_t)(o + __popc(m));
+    }
+    if (PLACE) {
+      o = __shfl_sync(0xFFFFFFFFu, o, leader) + __popc(m & lt_mask);
+      if (valid) {
+        const unsigned long long pos = (unsigned long long)s_base[t] + o;
+        if (pos < cap) list[pos] = gg;
+      }
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void __launch_bounds__(GS_BIN_THREADS)
+bin_count_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __restrict__ dval1,
+                 const uint32_t* __restrict__ hist_chain, const uint32_t* __restrict__ tiles_touched,
+                 const uint32_t* __restrict__ rect, int grid_x, int tiles, uint32_t* __restrict__ blockcount,
+                 uint32_t* __restrict__ tile_total) {
+  GS_PDL_PROLOGUE();
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  uint16_t* s_off = reinterpret_cast<uint16_t*>(s_raw);  // [32][tiles]
+  __shared__ uint4 s_stage[32][32];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  for (int k = tid; k < 16 * tiles; k += GS_BIN_THREADS) reinterpret_cast<uint32_t*>(s_off)[k] = 0;
+  const uint32_t* sorted_gid = depth_result_buffer(hist_chain, (unsigned long long)P, tid) ? dval1 : dval0;  // + barrier
+  const BinWarp bw = bin_load(P, blockIdx.x * GS_BIN_THREADS + tid, sorted_gid, tiles_touched, rect, s_stage[w], lane);
+  bin_warp_walk<false>(bw, s_stage[w], grid_x, s_off + (size_t)w * tiles, nullptr, nullptr, 0ull, lane);
+  __syncthreads();
+  for (int t = tid; t < tiles; t += GS_BIN_THREADS) {
+    uint32_t sum = 0;
+#pragma unroll 8
+    for (int k = 0; k < 32; k++) sum += s_off[(size_t)k * tiles + t];
+    blockcount[(size_t)blockIdx.x * tiles + t] = sum;
+    if (sum) atomicAdd(&tile_total[t], sum);
+  }
+}
+
+// tiles <= 2 * GS_BIN_THREADS.  Block 0 also publishes the tile ranges (identifyTileRanges, rasterizer_impl.cu:116-138:
+// empty tiles stay (0,0)) and the pair count.  FUSED: the grid is small enough to be co-resident (the launcher checks), the
+// kernel does the counting itself and crosses a grid-wide barrier instead of a kernel boundary; otherwise
+// bin_count_kernel has run before.
+template <bool FUSED>
+__global__ void __launch_bounds__(GS_BIN_THREADS)
+bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __restrict__ dval1,
+                 const uint32_t* __restrict__ hist_chain, const uint32_t* __restrict__ tiles_touched,
+                 const uint32_t* __restrict__ rect, int grid_x, int tiles, uint32_t* blockcount, uint32_t* tile_total,
+                 unsigned long long cap, uint32_t* __restrict__ list, uint2* __restrict__ ranges, GsHeader* __restrict__ hdr,
+                 uint32_t* grid_bar) {
+  GS_PDL_PROLOGUE();
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  uint16_t* s_off = reinterpret_cast<uint16_t*>(s_raw);                                  // [32][tiles]
+  uint32_t* s_base = reinterpret_cast<uint32_t*>(s_raw + (size_t)64 * tiles);            // [tiles]
+  __shared__ uint32_t s_wsum[32];
+  __shared__ uint4 s_stage[32][32];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  for (int k = tid; k < 16 * tiles; k += GS_BIN_THREADS) reinterpret_cast<uint32_t*>(s_off)[k] = 0;
+  const uint32_t* sorted_gid = depth_result_buffer(hist_chain, (unsigned long long)P, tid) ? dval1 : dval0;  // + barrier
+  const BinWarp bw = bin_load(P, blockIdx.x * GS_BIN_THREADS + tid, sorted_gid, tiles_touched, rect, s_stage[w], lane);
+  bin_warp_walk<false>(bw, s_stage[w], grid_x, s_off + (size_t)w * tiles, nullptr, nullptr, 0ull, lane);
+  if (FUSED) {
+    __syncthreads();
+    for (int t = tid; t < tiles; t += GS_BIN_THREADS) {
+      uint32_t sum = 0;
+#pragma unroll 8
+      for (int k = 0; k < 32; k++) sum += s_off[(size_t)k * tiles + t];
+      blockcount[(size_t)blockIdx.x * tiles + t] = sum;
+      if (sum) atomicAdd(&tile_total[t], sum);
+    }
+    __syncthreads();
+    if (tid == 0) {  // grid-wide barrier
+      __threadfence();
+      atomicAdd(grid_bar, 1u);
+      uint32_t spins = 0;
+      while (ld_volatile(grid_bar) < gridDim.x)
+        if (++spins > SPIN_LIMIT) { atomicExch(&hdr->error, 3u); break; }
+      __threadfence();
+    }
+    __syncthreads();
+  }
+
+  // tile starts: exclusive scan of the totals over tiles, two consecutive tiles per thread
+  const int ta = 2 * tid, tb = 2 * tid + 1;
+  const uint32_t ca = ta < tiles ? __ldcg(tile_total + ta) : 0u, cb = tb < tiles ? __ldcg(tile_total + tb) : 0u;
+  uint32_t pa = 0, pb = 0;  // pairs of the earlier blocks
+  for (unsigned b0 = 0; b0 < blockIdx.x; b0 += 16) {  // 32 independent loads in flight per round trip
+    uint32_t va[16], vb[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      const bool in = b0 + k < blockIdx.x;
+      va[k] = (in && ta < tiles) ? __ldcg(blockcount + (size_t)(b0 + k) * tiles + ta) : 0u;
+      vb[k] = (in && tb < tiles) ? __ldcg(blockcount + (size_t)(b0 + k) * tiles + tb) : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < 16; k++) { pa += va[k]; pb += vb[k]; }
+  }
+  uint32_t incl = ca + cb;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) s_wsum[w] = incl;
+  __syncthreads();  // also: every warp finished counting
+  uint32_t wpre = 0, total = 0;
+#pragma unroll
+  for (int k = 0; k < 32; k++) { const uint32_t v = s_wsum[k]; if (k < w) wpre += v; total += v; }
+  const uint32_t sa = wpre + incl - (ca + cb), sb = sa + ca;
+  if (ta < tiles) s_base[ta] = sa + pa;
+  if (tb < tiles) s_base[tb] = sb + pb;
+  if (blockIdx.x == 0) {
+    const uint32_t lim = (unsigned long long)total > cap ? (uint32_t)cap : total;
+    if (ta < tiles) ranges[ta] = ca ? make_uint2(min(sa, lim), min(sa + ca, lim)) : make_uint2(0u, 0u);
+    if (tb < tiles) ranges[tb] = cb ? make_uint2(min(sb, lim), min(sb + cb, lim)) : make_uint2(0u, 0u);
+    if (tid == 0) {
+      hdr->num_rendered = total;
+      hdr->overflow = (unsigned long long)total > cap ? 1u : 0u;
+    }
+  }
+  // per-warp counts -> exclusive offsets over the warps of this block
+  for (int t = tid; t < tiles; t += GS_BIN_THREADS) {
+    uint32_t run = 0;
+#pragma unroll 8
+    for (int k = 0; k < 32; k++) {
+      const uint32_t c = s_off[(size_t)k * tiles + t];
+      s_off[(size_t)k * tiles + t] = (uint16_t)run;
+      run += c;
+    }
+  }
+  __syncthreads();
+  bin_warp_walk<true>(bw, s_stage[w], grid_x, s_off + (size_t)w * tiles, s_base, list, cap, lane);
+}
+
 // Chained scan of tiles_touched over the depth-sorted Gaussians + pair emission (duplicateWithKeys,
 // rasterizer_impl.cu:70-111, without the 64-bit key: the depth order is already in the traversal order).
 __global__ void __launch_bounds__(GS_EMIT_THREADS)
-emit_kernel(int P, const uint32_t* __restrict__ sorted_gid, const uint32_t* __restrict__ tiles_touched,
+emit_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __restrict__ dval1,
+            const uint32_t* __restrict__ hist_chain, const uint32_t* __restrict__ tiles_touched,
             const uint32_t* __restrict__ rect, int grid_x, unsigned long long cap, uint32_t* __restrict__ tkey,
             uint32_t* __restrict__ tval, uint32_t* __restrict__ hist /* [4][256] tile-id digits */, int tile_passes,
             unsigned long long* __restrict__ scan_status, uint32_t* __restrict__ ticket, GsHeader* __restrict__ hdr) {
@@ -180,6 +424,7 @@ emit_kernel(int P, const uint32_t* __restrict__ sorted_gid, const uint32_t* __re
   for (int i = tid; i < tile_passes * 256; i += GS_EMIT_THREADS) s_hist[i] = 0;
   __syncthreads();
   const uint32_t blk = s_ticket;
+  const uint32_t* sorted_gid = depth_result_buffer(hist_chain, (unsigned long long)P, tid) ? dval1 : dval0;
   const int nblocks = (P + GS_EMIT_THREADS - 1) / GS_EMIT_THREADS;
   const int i = blk * GS_EMIT_THREADS + tid;
   uint32_t gid = 0, cnt = 0;
@@ -352,41 +597,72 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   const int P = a.P;
   const int gx = (a.width + GS_TILE - 1) / GS_TILE, gy = (a.height + GS_TILE - 1) / GS_TILE;
   const int tiles = gx * gy;
-  // 1. depth sort of the P Gaussians: 4 passes, dkey/dval ping-pong, ends in buffer 0
+  // 1. depth sort of the P Gaussians: up to 4 onesweep passes over the dkey/dval ping-pong; constant-digit passes are
+  //    skipped and the consumers find the result with depth_result_buffer().  (A single-cluster sort -- 8 CTAs, digit
+  //    counts over distributed shared memory, cluster barriers instead of kernel boundaries -- was measured at 40-58 us
+  //    for 50k keys against 26 us for these passes: 8 SMs at ~1 IPC lose to a latency chain spread over 49 SMs.)
   const int blocks_d = (int)gs_sort_blocks((unsigned long long)P);
   const bool small_d = gs_sort_items((unsigned long long)P) == GS_SORT_ITEMS_SMALL;
   for (int p = 0; p < 4; p++) {
     auto kern = small_d ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL> : onesweep_pass_kernel<GS_SORT_ITEMS>;
     gs_launch(kern, dim3(blocks_d), dim3(GS_SORT_THREADS), 0, st,
-        s.dkey[p & 1], s.dkey[(p + 1) & 1], s.dval[p & 1], s.dval[(p + 1) & 1], nullptr, (unsigned long long)P, 8 * p,
-        s.hist + p * 256, s.status_d + (size_t)p * s.blocks_d * 256, s.counters + p, &g.hdr->error);
+        (const uint32_t*)s.dkey[0], s.dkey[1], (const uint32_t*)s.dval[0], s.dval[1], (const unsigned long long*)nullptr,
+        (unsigned long long)P, 8 * p, (const uint32_t*)(s.hist + p * 256), s.status_d + (size_t)p * s.blocks_d * 256,
+        s.counters + p, &g.hdr->error, p, (const uint32_t*)s.hist);
   }
-  // 2. chained scan + pair emission in depth order
-  int bits = (int)higher_msb((uint32_t)tiles);
-  int tile_passes = (bits + 7) / 8;
-  if (tile_passes < 1) tile_passes = 1;
-  if (tile_passes > 4) tile_passes = 4;
-  // the LAST tile pass must write into `list`: choose the start buffer by parity
-  uint32_t* vbuf[2] = {s.tval[0], s.tval[1]};
-  const int blocks_e = (P + GS_EMIT_THREADS - 1) / GS_EMIT_THREADS;
-  gs_launch(emit_kernel, dim3(blocks_e), dim3(GS_EMIT_THREADS), 0, st, P, s.dval[0], g.tiles_touched, g.rect, gx, (unsigned long long)cap,
-                                                    s.tkey[0], vbuf[0], s.hist + 4 * 256, tile_passes, s.scan_status,
-                                                    s.counters + 8, g.hdr);
-  // 3. stable sort of the pairs by tile id
-  const int blocks_t = (int)gs_sort_blocks((unsigned long long)cap);
-  const bool small_t = gs_sort_items((unsigned long long)cap) == GS_SORT_ITEMS_SMALL;
-  for (int p = 0; p < tile_passes; p++) {
-    uint32_t* vout = (p == tile_passes - 1) ? list : vbuf[(p + 1) & 1];
-    auto kern = small_t ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL> : onesweep_pass_kernel<GS_SORT_ITEMS>;
-    gs_launch(kern, dim3(blocks_t), dim3(GS_SORT_THREADS), 0, st,
-        s.tkey[p & 1], s.tkey[(p + 1) & 1], vbuf[p & 1], vout, &g.hdr->num_rendered, (unsigned long long)cap, 8 * p,
-        s.hist + (4 + p) * 256, s.status_t + (size_t)p * s.blocks_t * 256, s.counters + 4 + p, &g.hdr->error);
+  const int blocks_c = (P + GS_BIN_THREADS - 1) / GS_BIN_THREADS;
+  if (gs_direct_binning(P, tiles, cap)) {
+    // 2-4 (direct): count pairs per (block of 1024 Gaussians, tile), then place every pair; no pair sort
+    static bool attr_done = false;
+    const size_t smem_c = (size_t)64 * tiles, smem_p = (size_t)68 * tiles;
+    if (!attr_done) {
+      const int max_smem = 68 * GS_BIN_MAX_TILES;
+      if (cudaFuncSetAttribute(bin_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess ||
+          cudaFuncSetAttribute(bin_place_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess ||
+          cudaFuncSetAttribute(bin_place_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess)
+        return gs_check(cudaGetLastError());
+      attr_done = true;
+    }
+    uint32_t* blockcount = s.tkey[0];  // [blocks_c][tiles] <= cap words
+    const bool fused = blocks_c <= GS_BIN_FUSED_MAX_BLOCKS;  // co-resident: one 1024-thread block per SM
+    if (!fused)
+      gs_launch(bin_count_kernel, dim3(blocks_c), dim3(GS_BIN_THREADS), smem_c, st, P, (const uint32_t*)s.dval[0],
+                (const uint32_t*)s.dval[1], (const uint32_t*)s.hist, (const uint32_t*)g.tiles_touched, (const uint32_t*)g.rect,
+                gx, tiles, blockcount, s.tile_total);
+    gs_launch(fused ? bin_place_kernel<true> : bin_place_kernel<false>, dim3(blocks_c), dim3(GS_BIN_THREADS), smem_p, st, P,
+              (const uint32_t*)s.dval[0], (const uint32_t*)s.dval[1], (const uint32_t*)s.hist, (const uint32_t*)g.tiles_touched,
+              (const uint32_t*)g.rect, gx, tiles, blockcount, s.tile_total, (unsigned long long)cap, list, im.ranges, g.hdr,
+              s.counters + 16);
+  } else {
+    // 2. chained scan + pair emission in depth order
+    int bits = (int)higher_msb((uint32_t)tiles);
+    int tile_passes = (bits + 7) / 8;
+    if (tile_passes < 1) tile_passes = 1;
+    if (tile_passes > 4) tile_passes = 4;
+    uint32_t* vbuf[2] = {s.tval[0], s.tval[1]};
+    const int blocks_e = (P + GS_EMIT_THREADS - 1) / GS_EMIT_THREADS;
+    gs_launch(emit_kernel, dim3(blocks_e), dim3(GS_EMIT_THREADS), 0, st, P, (const uint32_t*)s.dval[0],
+              (const uint32_t*)s.dval[1], (const uint32_t*)s.hist, (const uint32_t*)g.tiles_touched, (const uint32_t*)g.rect, gx,
+              (unsigned long long)cap, s.tkey[0], vbuf[0], s.hist + 4 * 256, tile_passes, s.scan_status, s.counters + 8, g.hdr);
+    // 3. stable sort of the pairs by tile id; the last pass writes into `list`
+    const int blocks_t = (int)gs_sort_blocks((unsigned long long)cap);
+    const bool small_t = gs_sort_items((unsigned long long)cap) == GS_SORT_ITEMS_SMALL;
+    for (int p = 0; p < tile_passes; p++) {
+      uint32_t* vout = (p == tile_passes - 1) ? list : vbuf[(p + 1) & 1];
+      auto kern = small_t ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL> : onesweep_pass_kernel<GS_SORT_ITEMS>;
+      gs_launch(kern, dim3(blocks_t), dim3(GS_SORT_THREADS), 0, st,
+          (const uint32_t*)s.tkey[p & 1], s.tkey[(p + 1) & 1], (const uint32_t*)vbuf[p & 1], vout,
+          (const unsigned long long*)&g.hdr->num_rendered, (unsigned long long)cap, 8 * p,
+          (const uint32_t*)(s.hist + (4 + p) * 256), s.status_t + (size_t)p * s.blocks_t * 256, s.counters + 4 + p,
+          &g.hdr->error, -1, (const uint32_t*)nullptr);
+    }
+    // 4. tile ranges
+    int rb = (int)((cap + 255) / 256);
+    if (rb > 148 * 16) rb = 148 * 16;
+    if (rb < 1) rb = 1;
+    gs_launch(tile_ranges_kernel, dim3(rb), dim3(256), 0, st, (const uint32_t*)s.tkey[tile_passes & 1],
+              (const unsigned long long*)&g.hdr->num_rendered, (unsigned long long)cap, im.ranges);
   }
-  // 4. tile ranges
-  int rb = (int)((cap + 255) / 256);
-  if (rb > 148 * 16) rb = 148 * 16;
-  if (rb < 1) rb = 1;
-  gs_launch(tile_ranges_kernel, dim3(rb), dim3(256), 0, st, s.tkey[tile_passes & 1], &g.hdr->num_rendered, (unsigned long long)cap, im.ranges);
   // 5. backward work plan (segments of GS_SEG entries per tile)
   gs_launch(plan_kernel, dim3(1), dim3(1024), 0, st, tiles, im.ranges, im.seg_off, l.items, (uint32_t)l.max_items, im.order);
   return gs_check(cudaGetLastError());

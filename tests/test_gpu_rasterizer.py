@@ -136,6 +136,15 @@ def test_bench_config_50k_512(built_lib):
         assert rel_err(g[k], bw[v]) <= 1e-4, k
 
 
+def test_many_gaussians_small_grid_unfused_placement(built_lib):
+    """130k Gaussians on a 128x128 image: more than GS_BIN_FUSED_MAX_BLOCKS blocks of 1024, so direct placement runs as
+    two kernels (count, place) instead of the co-resident fused grid; integer artefacts and image bit-exact."""
+    sc = scenes.avatar_scene(P=130000, W=128, H=128)
+    fw = scenes.oracle_forward(sc)
+    assert fw["N"] > 100000
+    check_forward_exact(fw, run_cuda(sc))
+
+
 def test_trained_like_opaque_scene(built_lib):
     """High-opacity Gaussians: pixels terminate early (T < 1e-4), exercising the done / early-exit paths of the pipelined
     forward and the checkpoint restarts of the segmented backward."""
