@@ -127,6 +127,7 @@ static inline __host__ size_t gs_carve_list(char* base, int64_t cap, int W, int 
 #define GS_SORT_THREADS 256
 #define GS_SORT_TILE (GS_SORT_ITEMS * GS_SORT_THREADS)   // 4096 keys per CTA
 #define GS_EMIT_THREADS 256
+#define GS_L1_MAX_BLOCKS 592                               // fused L1 loss: 4 CTAs per SM
 #define GS_BIN_THREADS 1024                                // direct placement: Gaussians per block
 #define GS_BIN_FUSED_MAX_BLOCKS 120                        // count+place in one co-resident grid up to this many blocks
 #define GS_BIN_TILE_BITS 11                                // log2(GS_BIN_MAX_TILES)

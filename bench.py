@@ -113,7 +113,9 @@ class HotPath:
         from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
         from avatar_pose import fused_pose
         self.dev, self.W, self.H = dev, W, H
+        from avatar_pose.loss import l1_loss
         self.Settings, self.Rasterizer, self.fused_pose = GaussianRasterizationSettings, GaussianRasterizer, fused_pose
+        self.l1_loss = l1_loss
         t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
         self.params = {k: t(g[k]).requires_grad_(True) for k in ("xyz", "rotation", "scaling", "opacity", "features_dc", "features_rest")}
         self.weights = t(wts)
@@ -171,7 +173,7 @@ class HotPath:
         for v in self.params.values():
             v.grad = None
         img, _ = self.forward(f)
-        loss = (img - f["target"]).abs().mean()  # l1_loss, train.py:121
+        loss = self.l1_loss(img, f["target"])  # l1_loss, train.py:121 (fused forward + gradient kernel)
         loss.backward()
         return loss
 
@@ -429,7 +431,7 @@ def ours_main(args):
     loss_host = torch.empty(1).pin_memory()
     # e2e input pipeline: two static frames / two graphs in ping-pong; the H2D copy of step k+1's inputs (pose, camera,
     # target image, from pinned host memory) runs on a copy stream while step k computes, and step k+1 waits for it.
-    e2e = {"k": 0, "ready": [None, None]}
+    e2e = {"k": 0, "ready": [None, None], "read": [None, None]}
     copy_stream = torch.cuda.Stream(dev)
     if not eager:
         f_static2 = hp.static_frame(frames[rank])
@@ -437,7 +439,10 @@ def ours_main(args):
         e2e_frames, e2e_graphs = [f_static, f_static2], [g_train, g_train2]
 
         def prefetch(slot):
-            copy_stream.wait_stream(torch.cuda.current_stream(dev))  # the slot's previous reader has been enqueued
+            # overwrite the slot only after its previous reader (the graph of step k-1) has finished -- NOT after the step
+            # just launched, which reads the other slot and is what this copy overlaps
+            if e2e["read"][slot] is not None:
+                copy_stream.wait_event(e2e["read"][slot])
             with torch.cuda.stream(copy_stream):
                 hp.load_static(e2e_frames[slot], f_pin)
                 ev = torch.cuda.Event()
@@ -453,7 +458,9 @@ def ours_main(args):
                 prefetch(slot)  # very first step: nothing was prefetched yet
             torch.cuda.current_stream(dev).wait_event(e2e["ready"][slot])
             loss = e2e_graphs[slot].replay()
-            prefetch(slot ^ 1)  # inputs of the NEXT step, overlapping this step's kernels
+            e2e["read"][slot] = torch.cuda.Event()
+            e2e["read"][slot].record(torch.cuda.current_stream(dev))
+            prefetch(slot ^ 1)  # inputs of the NEXT step: the copy runs while this step's kernels do
             e2e["k"] += 1
         loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
         torch.cuda.current_stream(dev).synchronize()  # the caller reads the loss
@@ -563,9 +570,15 @@ def ours_main(args):
                         "what": "reference CUDA rasterizer rebuilt for sm_100 + the reference's PyTorch posing chain on the same GPU"}
         except Exception as ex:
             ref_cuda = {"unavailable": str(ex)[:200]}
-    tile_passes = (max((((W + 15) // 16) * ((H + 15) // 16)).bit_length(), 1) + 7) // 8
-    # pose_fwd | preprocess, 4 depth passes, emit, tile passes, ranges, plan, blend_fwd | blend_bwd, preprocess_bwd | pose_bwd
-    launches = args.steps * (1 + (1 + 4 + 1 + tile_passes + 1 + 1 + 1) + 2 + 1)
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    blocks_c = (P + 1023) // 1024
+    if tiles <= 2048:  # direct placement (gs_sort.cu): count+place fused into one grid up to 120 blocks, else two kernels
+        binning = 4 + (1 if blocks_c <= 120 else 2) + 1            # depth passes, placement, plan
+    else:
+        tile_passes = (max(tiles.bit_length(), 1) + 7) // 8
+        binning = 4 + 1 + tile_passes + 1 + 1                       # depth passes, emit, tile passes, ranges, plan
+    # pose_fwd | preprocess, binning, blend_fwd | l1 loss fwd + bwd | blend_bwd, preprocess_bwd | pose_bwd
+    launches = args.steps * (1 + (1 + binning + 1) + 2 + 2 + 1)
     h2d = int(f_pin["small"].numel() * 4 + f_pin["target"].numel() * 4)
     line = {"metric": METRIC, "value": world * 1e3 / ms_train, "unit": "iter/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_train, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -243,6 +243,17 @@ typedef struct SkinArgs {
 size_t skinning_workspace_bytes(const SkinArgs* args);
 int skinning_forward(const SkinArgs* args, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- photometric L1 loss of the training step, forward + per-pixel gradient in one pass ----
+ * Replaces l1_loss (utils/loss_utils.py:19-20: torch.abs(network_output - gt).mean(), called at train.py:121) and its
+ * autograd backward.  `loss` [1] = mean |image - target|; `dL_dimage` [n] = sign(image - target) / n (sign(0) = 0), i.e.
+ * the gradient for dL/dloss = 1; l1_loss_backward scales it by the device scalar dL_dloss.  Deterministic summation.
+ * `workspace`: l1_loss_workspace_bytes() bytes, zero-filled once by the caller before the first use.  Pointers 16-byte
+ * aligned. */
+size_t l1_loss_workspace_bytes(void);
+int l1_loss_forward(const float* image, const float* target, int64_t n, float* loss, float* dL_dimage, void* workspace,
+                    size_t workspace_bytes, void* stream);
+int l1_loss_backward(const float* dL_dimage_unit, const float* dL_dloss, int64_t n, float* dL_dimage, void* stream);
+
 /* Bench support (no reference counterpart): per-stage CUDA-event timing of the last forward/backward call, and an
  * FP32 FMA throughput probe (8 independent FMA chains per thread, `iters` rounds: 16*iters flop per thread). */
 void gs_profile_enable(int on);
