@@ -250,6 +250,10 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           }
         }
       }
+      for (int kk = k; kk & (kChunk - 1); kk++) {  // the consumer reads whole chunks, branch-free: pad rows must be 0 * finite
+        ws.alpha[kk][lane] = 0.0f;
+        if (lane == 0) ws.row[kk] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
       if (lane == 0) ws.cnt = (uint32_t)k;
       __syncwarp();
       if (lane == 0) mbar_arrive(&ctl.full[p]);
@@ -263,9 +267,15 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   // -------------------------------------------------- consumer --------------------------------------------------
   // checkpoint slots of this tile: one per segment start + one final (backward work items restart from them)
   float4* const ck = ckpt + ((size_t)seg_off[tile] + tile) * 256 + blk * 32 + lane;
-  float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
+  // Front-to-back blending of one pixel, forward.cu:335-361, without carried control state.  Tr is the running product
+  // of (1 - alpha) over ALL rows; it never increases (0 < 1 - alpha <= 1; a row the pixel skips has alpha = 0 and
+  // multiplies by exactly 1), so "the pixel has terminated" (the reference's done flag, set by the first row with
+  // T * (1 - alpha) < 1e-4) is simply Tr < 1e-4, and the reference's T is the last Tr that was still >= 1e-4.  A live row
+  // with alpha = 0 adds Tr * (0 * c) = 0 to C, leaving its bits unchanged (finite colours), so only n_contrib needs the
+  // alpha != 0 test.
+  // Same values in the same order as the reference; 12 instructions per row on the consumer's chain instead of 24.
+  float T = 1.0f, Tr = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
   uint32_t last = 0;
-  bool done = !inside;
   for (int b = 0; b < nb; b++) {
     const int p = b % kProducers;
     FwdBuf& ws = bufs[p];
@@ -273,40 +283,29 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     mbar_wait(&ctl.full[p], (uint32_t)(b / kProducers) & 1u);
     TRACE(b, 3);
     if ((b & (GS_SEG / 32 - 1)) == 0) ck[(size_t)(b / (GS_SEG / 32)) * 256] = make_float4(T, C0, C1, C2);
-    const int cnt = (int)ws.cnt;
-    // The transmittance runs on unconditionally (one FMUL per row on the critical chain: a skipped entry multiplies by
-    // exactly 1.0f); the first entry that would push it below 1e-4 freezes a copy.  Same values, same order as
-    // forward.cu:335-361, but the compare no longer sits between two multiplies.
-    float Tr = T;
+    const int cnt = (int)ws.cnt;  // rows up to the next multiple of kChunk are zero-padded by the producer
     for (int k0 = 0; k0 < cnt; k0 += kChunk) {
       float al[kChunk];
       float4 rw[kChunk];
 #pragma unroll
       for (int u = 0; u < kChunk; u++) {
-        const int k = k0 + u;  // <= 31 because cnt <= 32 and k0 is a multiple of kChunk
-        const float a_ = ws.alpha[k][lane];
-        al[u] = (k < cnt) ? a_ : 0.0f;
-        rw[u] = ws.row[k];
+        al[u] = ws.alpha[k0 + u][lane];
+        rw[u] = ws.row[k0 + u];
       }
 #pragma unroll
       for (int u = 0; u < kChunk; u++) {
-        const bool nz = al[u] != 0.0f;
-        const float m = nz ? __fsub_rn(1.0f, al[u]) : 1.0f;
-        const float test_T = __fmul_rn(Tr, m);
-        const bool term = nz && !done && (test_T < 0.0001f);
-        const bool ok = nz && !done && !term;
-        if (term) { T = Tr; done = true; }
-        if (ok) {
-          C0 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].x), C0);
-          C1 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].y), C1);
-          C2 = __fmaf_rn(Tr, __fmul_rn(al[u], rw[u].z), C2);
-          last = (uint32_t)__float_as_int(rw[u].w);  // 1-based position in the tile list (contributor, forward.cu:328)
-        }
+        const float test_T = __fmul_rn(Tr, __fsub_rn(1.0f, al[u]));
+        const bool ok = !(test_T < 0.0001f);
+        const float Tw = ok ? Tr : 0.0f;  // branch-free: a terminated pixel adds 0 * (alpha * c) = 0, C keeps its bits
+        C0 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].x), C0);
+        C1 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].y), C1);
+        C2 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].z), C2);
+        T = ok ? test_T : T;
+        last = (ok && al[u] != 0.0f) ? (uint32_t)__float_as_int(rw[u].w) : last;  // contributor, forward.cu:328 (1-based)
         Tr = test_T;
       }
     }
-    if (!done) T = Tr;
-    const bool all_done = __all_sync(0xFFFFFFFFu, done);
+    const bool all_done = __all_sync(0xFFFFFFFFu, !inside || Tr < 0.0001f);
     if (lane == 0) {
       if (all_done) {  // stop the producers: whoever waits on an empty barrier wakes and sees the flag
         st_release_cta(&ctl.done, 1u);
@@ -525,7 +524,10 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 
 int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st) {
   dim3 grid((a.width + GS_TILE - 1) / GS_TILE, (a.height + GS_TILE - 1) / GS_TILE);
-  const size_t smem = sizeof(FwdCtl) + kProducers * sizeof(FwdBuf);
+#ifndef GS_FWD_SMEM_PAD
+#define GS_FWD_SMEM_PAD 0
+#endif
+  const size_t smem = sizeof(FwdCtl) + kProducers * sizeof(FwdBuf) + GS_FWD_SMEM_PAD;
   const int gx = (int)grid.x;
   grid = dim3(grid.x * grid.y * kWarps);  // one CTA per 8x4 pixel block of a tile, tiles in im.order
   static bool configured = false;
