@@ -284,6 +284,9 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     TRACE(b, 3);
     if ((b & (GS_SEG / 32 - 1)) == 0) ck[(size_t)(b / (GS_SEG / 32)) * 256] = make_float4(T, C0, C1, C2);
     const int cnt = (int)ws.cnt;  // rows up to the next multiple of kChunk are zero-padded by the producer
+#ifdef GS_FWD_TRACE
+    if (trace_on && lane == 0 && b < 512) s_trace[b * 8 + 5] = cnt;
+#endif
     for (int k0 = 0; k0 < cnt; k0 += kChunk) {
       float al[kChunk];
       float4 rw[kChunk];
