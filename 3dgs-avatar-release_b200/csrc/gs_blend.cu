@@ -157,12 +157,16 @@ __device__ long long g_fwd_trace[512 * 8];
 #define TRACE(b, i) do { } while (0)
 #endif
 
+// OP: the fused opacity pass (gaussian_renderer/__init__.py:131-142: a second rasterisation of the same geometry with
+// colours = 1, channel 0 kept).  The consumer carries one more accumulator, C3 += T * alpha -- what forward.cu:349
+// computes for a feature of exactly 1.0 -- so out_opacity is bit-identical to the second call's channel 0.
+template <bool OP>
 __global__ void __launch_bounds__(kFwdWarps * 32)
 blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H,
                  const GsRec* __restrict__ rec, const float* __restrict__ bg, float* __restrict__ final_T,
                  uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                  const uint32_t* __restrict__ seg_off, float4* __restrict__ ckpt, const uint32_t* __restrict__ order,
-                 int grid_x) {
+                 int grid_x, float* __restrict__ out_opacity, float* __restrict__ ckpt_op) {
   GS_PDL_PROLOGUE();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FwdCtl& ctl = *reinterpret_cast<FwdCtl*>(smem_raw);
@@ -266,7 +270,9 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 
   // -------------------------------------------------- consumer --------------------------------------------------
   // checkpoint slots of this tile: one per segment start + one final (backward work items restart from them)
-  float4* const ck = ckpt + ((size_t)seg_off[tile] + tile) * 256 + blk * 32 + lane;
+  const size_t ck_base = ((size_t)seg_off[tile] + tile) * 256 + blk * 32 + lane;
+  float4* const ck = ckpt + ck_base;
+  float* const ck3 = OP ? ckpt_op + ck_base : nullptr;
   // Front-to-back blending of one pixel, forward.cu:335-361, without carried control state.  Tr is the running product
   // of (1 - alpha) over ALL rows; it never increases (0 < 1 - alpha <= 1; a row the pixel skips has alpha = 0 and
   // multiplies by exactly 1), so "the pixel has terminated" (the reference's done flag, set by the first row with
@@ -274,7 +280,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   // with alpha = 0 adds Tr * (0 * c) = 0 to C, leaving its bits unchanged (finite colours), so only n_contrib needs the
   // alpha != 0 test.
   // Same values in the same order as the reference; 12 instructions per row on the consumer's chain instead of 24.
-  float T = 1.0f, Tr = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
+  float T = 1.0f, Tr = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, C3 = 0.f;
   uint32_t last = 0;
   for (int b = 0; b < nb; b++) {
     const int p = b % kProducers;
@@ -282,7 +288,10 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     TRACE(b, 2);
     mbar_wait(&ctl.full[p], (uint32_t)(b / kProducers) & 1u);
     TRACE(b, 3);
-    if ((b & (GS_SEG / 32 - 1)) == 0) ck[(size_t)(b / (GS_SEG / 32)) * 256] = make_float4(T, C0, C1, C2);
+    if ((b & (GS_SEG / 32 - 1)) == 0) {
+      ck[(size_t)(b / (GS_SEG / 32)) * 256] = make_float4(T, C0, C1, C2);
+      if (OP) ck3[(size_t)(b / (GS_SEG / 32)) * 256] = C3;
+    }
     const int cnt = (int)ws.cnt;  // rows up to the next multiple of kChunk are zero-padded by the producer
 #ifdef GS_FWD_TRACE
     if (trace_on && lane == 0 && b < 512) s_trace[b * 8 + 5] = cnt;
@@ -303,6 +312,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         C0 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].x), C0);
         C1 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].y), C1);
         C2 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].z), C2);
+        if (OP) C3 = __fmaf_rn(Tw, al[u], C3);  // colour 1.0: (1 * alpha) * T
         T = ok ? test_T : T;
         last = (ok && al[u] != 0.0f) ? (uint32_t)__float_as_int(rw[u].w) : last;  // contributor, forward.cu:328 (1-based)
         Tr = test_T;
@@ -325,6 +335,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   if (trace_on) for (int i = lane; i < 512 * 8; i += 32) g_fwd_trace[i] = s_trace[i];
 #endif
   ck[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256] = make_float4(T, C0, C1, C2);
+  if (OP) ck3[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256] = C3;
   if (inside) {
     const size_t pix = (size_t)py * W + px, hw = (size_t)H * W;
     final_T[pix] = T;
@@ -332,6 +343,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     out_color[pix] = __fmaf_rn(T, bg[0], C0);
     out_color[hw + pix] = __fmaf_rn(T, bg[1], C1);
     out_color[2 * hw + pix] = __fmaf_rn(T, bg[2], C2);
+    if (OP) out_opacity[pix] = __fmaf_rn(T, bg[0], C3);  // channel 0 of the second call: same background
   }
 }
 
@@ -355,6 +367,10 @@ __device__ __forceinline__ void xpose_step(float* v, int lane) {
 #ifndef GS_BWD_MINBLOCKS
 #define GS_BWD_MINBLOCKS 2
 #endif
+// OP: upstream gradient of the fused opacity image too.  dL/dalpha is linear in the per-channel terms, so the opacity
+// channel (colour 1, no colour gradient) is one more term of the same sum and every geometry gradient comes out as the
+// sum of the reference's two backward calls.
+template <bool OP>
 __global__ void __launch_bounds__(kWarps * 32, GS_BWD_MINBLOCKS)
 blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H, int grid_x,
                  const uint32_t* __restrict__ seg_off, int tiles, const uint2* __restrict__ items,
@@ -362,7 +378,8 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  const float* __restrict__ bg, const GsRec* __restrict__ rec, const float* __restrict__ final_Ts,
                  const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
                  float* __restrict__ dL_dmean2D /*[P,3]*/, float* __restrict__ dL_dconic /*[P,4]*/,
-                 float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors) {
+                 float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors,
+                 const float* __restrict__ ckpt_op, const float* __restrict__ dL_dop_pix) {
   GS_PDL_PROLOGUE();
   __shared__ Slab s_slab[kWarps];
   if (blockIdx.x >= seg_off[tiles]) return;
@@ -390,17 +407,25 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   const float T_final = inside ? final_Ts[pix] : 0.f;
   float T = T_final;
   float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_alpha = 0.f;
+  float acc3 = 0.f, lc3 = 0.f;  // opacity channel: its colour is 1 once a contributor has been seen
   if (last_contributor > seg_end) {  // restart from the checkpoint at the segment end
-    const float4* ck = ckpt + ((size_t)seg_off[tile] + tile) * 256 + threadIdx.x;
+    const size_t ck_base = ((size_t)seg_off[tile] + tile) * 256 + threadIdx.x;
+    const float4* ck = ckpt + ck_base;
     const float4 c = ck[(size_t)(item.y + 1) * 256];
     const float4 cf = ck[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256];
     T = c.x;
     const float rT = 1.f / T;
     acc0 = (cf.y - c.y) * rT; acc1 = (cf.z - c.z) * rT; acc2 = (cf.w - c.w) * rT;
+    if (OP) {
+      const float* ck3 = ckpt_op + ck_base;
+      acc3 = (ck3[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256] - ck3[(size_t)(item.y + 1) * 256]) * rT;
+    }
   }
-  float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f;
+  float dp0 = 0.f, dp1 = 0.f, dp2 = 0.f, dp3 = 0.f;
   if (inside) { dp0 = dL_dpixels[pix]; dp1 = dL_dpixels[hw + pix]; dp2 = dL_dpixels[2 * hw + pix]; }
-  const float bg_dot_dpixel = bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2;
+  if (OP && inside) dp3 = dL_dop_pix[pix];
+  // the second call's image has the same background; only its channel 0 carries an upstream gradient (`[:1]`)
+  const float bg_dot_dpixel = bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2 + (OP ? bg[0] * dp3 : 0.f);
   const float nTfbg = -T_final * bg_dot_dpixel;
   const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;  // backward.cu:460-461
   // which accumulator this lane feeds after the transposing reduction: entry (lane >> 3) of the chunk, component lane & 7
@@ -478,7 +503,13 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         const float a0 = last_alpha * lc0 + (1.f - last_alpha) * acc0;
         const float a1 = last_alpha * lc1 + (1.f - last_alpha) * acc1;
         const float a2 = last_alpha * lc2 + (1.f - last_alpha) * acc2;
-        float dL_dalpha = ((c0 - a0) * dp0 + (c1 - a1) * dp1 + (c2 - a2) * dp2) * Tn + nTfbg * rinv[k];
+        float dsum = (c0 - a0) * dp0 + (c1 - a1) * dp1 + (c2 - a2) * dp2;
+        float a3 = 0.f;
+        if (OP) {
+          a3 = last_alpha * lc3 + (1.f - last_alpha) * acc3;
+          dsum += (1.f - a3) * dp3;
+        }
+        float dL_dalpha = dsum * Tn + nTfbg * rinv[k];
         const float dchannel_dcolor = al[k] * Tn;
         const float dL_dG = o * dL_dalpha;
         const float gdx = G_[k] * dx_[k], gdy = G_[k] * dy_[k];
@@ -495,6 +526,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         v8[k] = ok ? dchannel_dcolor * dp2 : 0.f;
         if (ok) {
           T = Tn; acc0 = a0; acc1 = a1; acc2 = a2; lc0 = c0; lc1 = c1; lc2 = c2; last_alpha = al[k];
+          if (OP) { acc3 = a3; lc3 = 1.f; }
         }
       }
       // warp reduction BEFORE the atomics: lane L ends with the total of v[L] (entry L>>3, component L&7)
@@ -535,20 +567,23 @@ int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& 
   grid = dim3(grid.x * grid.y * kWarps);  // one CTA per 8x4 pixel block of a tile, tiles in im.order
   static bool configured = false;
   if (!configured) {
-    if (gs_check(cudaFuncSetAttribute(blend_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != GS_OK)
+    if (gs_check(cudaFuncSetAttribute(blend_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != GS_OK ||
+        gs_check(cudaFuncSetAttribute(blend_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != GS_OK)
       return GS_ERR_CUDA;
     configured = true;
   }
-  gs_launch(blend_fwd_kernel, grid, dim3(kFwdWarps * 32), smem, st, im.ranges, l.point_list, a.width, a.height, g.rec, a.background,
-                                                       im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt, im.order, gx);
+  gs_launch(a.out_opacity ? blend_fwd_kernel<true> : blend_fwd_kernel<false>, grid, dim3(kFwdWarps * 32), smem, st, im.ranges,
+            l.point_list, a.width, a.height, g.rec, a.background, im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt,
+            im.order, gx, a.out_opacity, l.ckpt_op);
   return gs_check(cudaGetLastError());
 }
 
 int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st) {
   const int gx = (a.width + GS_TILE - 1) / GS_TILE, gy = (a.height + GS_TILE - 1) / GS_TILE;
-  gs_launch(blend_bwd_kernel, dim3((unsigned)l.max_items), dim3(kWarps * 32), 0, st,
+  gs_launch(a.dL_dopacity_pix ? blend_bwd_kernel<true> : blend_bwd_kernel<false>, dim3((unsigned)l.max_items), dim3(kWarps * 32), 0, st,
       im.ranges, l.point_list, a.width, a.height, gx, im.seg_off, gx * gy, l.items, l.ckpt, a.background, g.rec,
-      im.final_T, im.n_contrib, a.dL_dpix, a.dL_dmean2D, a.dL_dconic, a.dL_dopacity, a.dL_dcolor);
+      im.final_T, im.n_contrib, a.dL_dpix, a.dL_dmean2D, a.dL_dconic, a.dL_dopacity, a.dL_dcolor,
+      (const float*)l.ckpt_op, a.dL_dopacity_pix);
   return gs_check(cudaGetLastError());
 }
 

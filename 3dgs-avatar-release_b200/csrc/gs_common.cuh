@@ -55,6 +55,7 @@ struct GsList {
   uint32_t* point_list;     // [cap] Gaussian index per (tile, depth)-sorted pair
   uint2* items;             // [max_items] (tile, segment) work items of the backward blend
   float4* ckpt;             // [(max_items + tiles) * 256] per-pixel (T, C.rgb) at every segment start + final state
+  float* ckpt_op;           // same slots: accumulated opacity channel (written only by the fused opacity pass)
   size_t max_items;
 };
 
@@ -117,6 +118,7 @@ static inline __host__ size_t gs_carve_list(char* base, int64_t cap, int W, int 
   gs_carve(p, t.point_list, (size_t)cap);
   gs_carve(p, t.items, t.max_items);
   gs_carve(p, t.ckpt, (t.max_items + tiles) * 256);
+  gs_carve(p, t.ckpt_op, (t.max_items + tiles) * 256);
   if (l) *l = t;
   return (size_t)(p - base);
 }

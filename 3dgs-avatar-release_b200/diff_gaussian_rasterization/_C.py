@@ -35,7 +35,7 @@ class GsForwardArgs(ctypes.Structure):
                 ("background", c_float_p), ("means3D", c_float_p), ("shs", c_float_p), ("colors_precomp", c_float_p),
                 ("opacities", c_float_p), ("scales", c_float_p), ("rotations", c_float_p),
                 ("cov3D_precomp", c_float_p), ("viewmatrix", c_float_p), ("projmatrix", c_float_p),
-                ("campos", c_float_p), ("out_color", c_float_p), ("radii", c_float_p)]
+                ("campos", c_float_p), ("out_color", c_float_p), ("radii", c_float_p), ("out_opacity", c_float_p)]
 
 
 class GsBackwardArgs(ctypes.Structure):
@@ -47,7 +47,8 @@ class GsBackwardArgs(ctypes.Structure):
                 ("viewmatrix", c_float_p), ("projmatrix", c_float_p), ("campos", c_float_p), ("radii", c_float_p),
                 ("dL_dpix", c_float_p), ("dL_dmean2D", c_float_p), ("dL_dconic", c_float_p),
                 ("dL_dopacity", c_float_p), ("dL_dcolor", c_float_p), ("dL_dmean3D", c_float_p),
-                ("dL_dcov3D", c_float_p), ("dL_dsh", c_float_p), ("dL_dscale", c_float_p), ("dL_drot", c_float_p)]
+                ("dL_dcov3D", c_float_p), ("dL_dsh", c_float_p), ("dL_dscale", c_float_p), ("dL_drot", c_float_p),
+                ("dL_dopacity_pix", c_float_p)]
 
 
 _lib = None
@@ -149,6 +150,27 @@ def _dev_state(device):
 def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
                         projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
                         debug):
+    return _forward(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                    projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, debug, None)
+
+
+def rasterize_gaussians_opacity(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                                viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree,
+                                campos, prefiltered, debug):
+    """rasterize_gaussians + the opacity image of the reference's second rasterizer call (colours = 1, channel 0 kept:
+    gaussian_renderer/__init__.py:131-142) from the same forward blend.
+    -> (num_rendered, color, opacity_image [1,H,W], radii, geomBuffer, binningBuffer, imgBuffer)"""
+    H, W = int(image_height), int(image_width)
+    op_img = torch.zeros(1, H, W, dtype=torch.float32, device=means3D.device)
+    n, color, radii, geom, lst, img = _forward(bg, means3D, colors, opacity, scales, rotations, scale_modifier,
+                                               cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh,
+                                               degree, campos, prefiltered, debug, op_img)
+    return n, color, op_img, radii, geom, lst, img
+
+
+def _forward(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+             projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, debug,
+             out_opacity):
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise GsError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:57-59
     if not means3D.is_cuda:
@@ -171,7 +193,8 @@ def rasterize_gaussians(bg, means3D, colors, opacity, scales, rotations, scale_m
                           _ptr(sh, "sh"), _ptr(colors, "colors_precomp"), _ptr(opacity, "opacities"),
                           _ptr(scales, "scales"), _ptr(rotations, "rotations"), _ptr(cov3D_precomp, "cov3D_precomp"),
                           _ptr(viewmatrix, "viewmatrix"), _ptr(projmatrix, "projmatrix"), _ptr(campos, "campos"),
-                          out_color.data_ptr(), radii.data_ptr())
+                          out_color.data_ptr(), radii.data_ptr(),
+                          out_opacity.data_ptr() if out_opacity is not None else None)
         st = _dev_state(dev)
         stream = torch.cuda.current_stream(dev).cuda_stream
         geom = torch.empty(L.gs_geom_bytes(P), **u8)
@@ -237,7 +260,9 @@ def graph_overflow(device=None):
 
 def rasterize_gaussians_backward(bg, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
-                                 geomBuffer, R, binningBuffer, imageBuffer, debug):
+                                 geomBuffer, R, binningBuffer, imageBuffer, debug, dL_dout_opacity=None):
+    """dL_dout_opacity ([1,H,W], only after rasterize_gaussians_opacity): upstream gradient of the fused opacity image;
+    the returned geometry gradients are then the sum of the reference's two backward calls."""
     L = lib()
     P = int(means3D.size(0))
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
@@ -259,6 +284,7 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, scales, rotations, 
             return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot
         means3D, colors, scales, rotations, cov3D_precomp, sh = map(_c, (means3D, colors, scales, rotations, cov3D_precomp, sh))
         bg, viewmatrix, projmatrix, campos, dL = map(_c, (bg, viewmatrix, projmatrix, campos, dL_dout_color))
+        dLo = _c(dL_dout_opacity)
         a = GsBackwardArgs(P, int(degree), M, W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier),
                            int(bool(debug)), _ptr(bg, "bg"), _ptr(means3D, "means3D"), _ptr(sh, "sh"),
                            _ptr(colors, "colors_precomp"), _ptr(scales, "scales"), _ptr(rotations, "rotations"),
@@ -266,7 +292,8 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, scales, rotations, 
                            _ptr(projmatrix, "projmatrix"), _ptr(campos, "campos"), _ptr(radii, "radii", torch.int32),
                            _ptr(dL, "dL_dout_color"), dmeans2D.data_ptr(), dconic.data_ptr(), dopacity.data_ptr(),
                            dcolors.data_ptr(), dmeans3D.data_ptr(), dcov3D.data_ptr(),
-                           dsh.data_ptr() if M else None, dscales.data_ptr(), drot.data_ptr())
+                           dsh.data_ptr() if M else None, dscales.data_ptr(), drot.data_ptr(),
+                           _ptr(dLo, "dL_dout_opacity"))
         stream = torch.cuda.current_stream(dev).cuda_stream
         cap = L.gs_list_capacity(binningBuffer.numel(), W, H)
         status = L.gs_backward(ctypes.byref(a), geomBuffer.data_ptr(), geomBuffer.numel(), imageBuffer.data_ptr(),

@@ -65,6 +65,52 @@ class _RasterizeGaussians(torch.autograd.Function):
                 grad_cov3Ds_precomp, None)
 
 
+class _RasterizeGaussiansOpacity(torch.autograd.Function):
+    """Colour image + opacity image from ONE rasterisation: what gaussian_renderer/__init__.py:121-142 obtains with two
+    calls (the second with colors_precomp = ones, `[:1]` kept).  The backward is one call too; the geometry gradients are
+    the sum autograd forms over the reference's two calls."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                raster_settings):
+        rs = raster_settings
+        args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+                rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh,
+                rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
+        num_rendered, color, opacity_image, radii, geomBuffer, binningBuffer, imgBuffer = _run_with_snapshot(
+            _C.rasterize_gaussians_opacity, args, rs.debug, "snapshot_fw.dump", "forward")
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
+                              binningBuffer, imgBuffer)
+        ctx.mark_non_differentiable(radii)
+        return color, radii, opacity_image
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _grad_radii, grad_out_opacity):
+        rs = ctx.raster_settings
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer, binningBuffer,
+         imgBuffer) = ctx.saved_tensors
+        if grad_out_color is None:
+            grad_out_color = torch.zeros(3, rs.image_height, rs.image_width, dtype=torch.float32, device=means3D.device)
+        if grad_out_opacity is None:
+            grad_out_opacity = torch.zeros(1, rs.image_height, rs.image_width, dtype=torch.float32, device=means3D.device)
+        args = (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+                rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, sh, rs.sh_degree, rs.campos,
+                geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, rs.debug, grad_out_opacity)
+        (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
+         grad_rotations) = _run_with_snapshot(_C.rasterize_gaussians_backward, args, rs.debug, "snapshot_bw.dump",
+                                              "backward")
+        return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales, grad_rotations,
+                grad_cov3Ds_precomp, None)
+
+
+def rasterize_gaussians_opacity(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                                raster_settings):
+    return _RasterizeGaussiansOpacity.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                            cov3Ds_precomp, raster_settings)
+
+
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
@@ -98,7 +144,10 @@ class GaussianRasterizer(nn.Module):
             return _C.mark_visible(positions, rs.viewmatrix, rs.projmatrix)
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
-                cov3D_precomp=None):
+                cov3D_precomp=None, return_opacity=False):
+        """return_opacity (extension, default off = the reference's signature): also returns the opacity image
+        `[1,H,W]` the reference renders with a second call (gaussian_renderer/__init__.py:131-142), from the same pass:
+        -> (color, radii, opacity_image)."""
         if (shs is None) == (colors_precomp is None):
             raise Exception('Please provide excatly one of either SHs or precomputed colors!')
         has_sr = scales is not None or rotations is not None
@@ -110,5 +159,5 @@ class GaussianRasterizer(nn.Module):
         scales = empty if scales is None else scales
         rotations = empty if rotations is None else rotations
         cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
-        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
-                                   self.raster_settings)
+        fn = rasterize_gaussians_opacity if return_opacity else rasterize_gaussians
+        return fn(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp, self.raster_settings)

@@ -65,6 +65,10 @@ typedef struct GsForwardArgs {
   const float* campos;     /* [3] */
   float* out_color;        /* [3,H,W] */
   int32_t* radii;          /* [P] */
+  /* Fused opacity pass.  gaussian_renderer/__init__.py:131-142 rasterises the same geometry a
+   * second time with colors_precomp = ones and keeps channel 0 (`opacity_image[:1]`).  Non-NULL: the one forward blend
+   * carries that channel too and writes it here, bit-identical to the second call.  NULL: plain forward. */
+  float* out_opacity;      /* [H,W] or NULL */
 } GsForwardArgs;
 
 typedef struct GsBackwardArgs {
@@ -95,6 +99,9 @@ typedef struct GsBackwardArgs {
   float* dL_dsh;         /* [P,M,3] or NULL when M == 0 */
   float* dL_dscale;      /* [P,3] */
   float* dL_drot;        /* [P,4] */
+  /* upstream gradient of the fused opacity image (forward must have been run with out_opacity); the geometry
+   * gradients come out as the SUM of the two backward calls of the reference, in one backward blend */
+  const float* dL_dopacity_pix; /* [H,W] or NULL */
 } GsBackwardArgs;
 
 /* Workspace sizes.  geom and image are kept for backward (like geomBuffer / imgBuffer); `list` holds the

@@ -42,9 +42,9 @@ def test_workspace_sizes(built_lib):
 def test_struct_layout_matches_header(built_lib):
     from diff_gaussian_rasterization import _C
     import avatar_pose
-    # 10 x 4-byte scalars + 13 pointers / 9 scalars (+pad) + 21 pointers / 5 scalars (+pad) + 15 pointers
-    assert ctypes.sizeof(_C.GsForwardArgs) == 40 + 13 * 8
-    assert ctypes.sizeof(_C.GsBackwardArgs) == 40 + 21 * 8
+    # 10 x 4-byte scalars + 14 pointers / 9 scalars (+pad) + 22 pointers / 5 scalars (+pad) + 15 pointers
+    assert ctypes.sizeof(_C.GsForwardArgs) == 40 + 14 * 8
+    assert ctypes.sizeof(_C.GsBackwardArgs) == 40 + 22 * 8
     assert ctypes.sizeof(avatar_pose.PoseArgs) == 24 + 15 * 8
     assert ctypes.sizeof(avatar_pose.PoseBackwardArgs) == ctypes.sizeof(avatar_pose.PoseArgs) + 11 * 8
     # and against the library itself
