@@ -99,3 +99,43 @@ def hierarchical_softmax(x):
 def skinning_weights(xyz, Ws, bs, aabb_min, aabb_max):
     h = mlp(2.0 * ((xyz - aabb_min) / (aabb_max - aabb_min)) - 1.0, Ws, bs)
     return hierarchical_softmax(h) if h.shape[1] == 25 else torch.softmax(h, -1)
+
+
+_SH_C1 = 0.4886025119029199
+_SH_C2 = (1.0925484305920792, -1.0925484305920792, 0.31539156525252005, -1.0925484305920792, 0.5462742152960396)
+_SH_C3 = (-0.5900435899266435, 2.890611442640554, -0.4570457994644658, 0.3731763325901154, -0.4570457994644658,
+          1.445305721320277, -0.5900435899266435)
+
+
+def sh_bases_1(deg, d):
+    """eval_sh_bases(deg, d)[..., 1:] (utils/sh_utils.py:115-149), autograd friendly."""
+    x, y, z = d.unbind(-1)
+    out = []
+    if deg > 0:
+        out += [-_SH_C1 * y, _SH_C1 * z, -_SH_C1 * x]
+    if deg > 1:
+        xx, yy, zz, xy, yz, xz = x * x, y * y, z * z, x * y, y * z, x * z
+        out += [_SH_C2[0] * xy, _SH_C2[1] * yz, _SH_C2[2] * (2.0 * zz - xx - yy), _SH_C2[3] * xz, _SH_C2[4] * (xx - yy)]
+    if deg > 2:
+        out += [_SH_C3[0] * y * (3 * xx - yy), _SH_C3[1] * xy * z, _SH_C3[2] * y * (4 * zz - xx - yy),
+                _SH_C3[3] * z * (2 * zz - 3 * xx - 3 * yy), _SH_C3[4] * x * (4 * zz - xx - yy), _SH_C3[5] * z * (xx - yy),
+                _SH_C3[6] * x * (xx - 3 * yy)]
+    return torch.stack(out, -1)
+
+
+def color_mlp(features, xyz, T_fwd, camera_center, non_rigid_feature, latent, Ws, bs, sh_degree, cano_view_dir, view_noise):
+    """ColorMLP.forward (texture.py:74-125) for the backward re-evaluation of avatar_pose.texture."""
+    n = features.shape[0]
+    parts = [features]
+    if sh_degree > 0:
+        d = xyz - camera_center.reshape(1, 3)
+        if cano_view_dir:
+            d = torch.matmul(T_fwd.reshape(n, 4, 4)[:, :3, :3].transpose(1, 2), d.unsqueeze(-1)).squeeze(-1)
+            if view_noise is not None:
+                d = torch.matmul(d, view_noise)
+        parts.append(sh_bases_1(sh_degree, d / (d.norm(dim=1, keepdim=True) + 1e-12)))
+    if non_rigid_feature is not None:
+        parts.append(non_rigid_feature)
+    if latent is not None:
+        parts.append(latent.reshape(1, -1).expand(n, -1))
+    return torch.sigmoid(mlp(torch.cat(parts, 1), Ws, bs))

@@ -155,7 +155,7 @@ int gs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, co
   return gs_launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream);
 }
 
-/* sizeof of the ABI structs (0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs):
+/* sizeof of the ABI structs (0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs, 6 ColorArgs):
  * lets a binding check its own struct declarations against the library it loaded */
 size_t gs_sizeof(int32_t which) {
   switch (which) {
@@ -165,6 +165,7 @@ size_t gs_sizeof(int32_t which) {
     case 3: return sizeof(PoseBackwardArgs);
     case 4: return sizeof(NonRigidArgs);
     case 5: return sizeof(SkinArgs);
+    case 6: return sizeof(ColorArgs);
     default: return 0;
   }
 }

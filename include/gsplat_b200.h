@@ -250,6 +250,41 @@ typedef struct SkinArgs {
 size_t skinning_workspace_bytes(const SkinArgs* args);
 int skinning_forward(const SkinArgs* args, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- colour MLP texture (forward) ----
+ * Replaces ColorMLP.forward, models/texture/texture.py:40-125 (registry key "mlp", the repository's default texture,
+ * configs/texture/shallow_mlp.yaml): compose_input = [ per-Gaussian feature (feature_dim) | eval_sh_bases(sh_degree,
+ * view dir)[1:] (utils/sh_utils.py:115-161) | non_rigid_feature (non_rigid.py:87,119-120) | per-frame latent code ],
+ * view dir = (xyz - camera_center), rotated into the canonical frame by T_fwd[:, :3, :3]^T when cano_view_dir
+ * (texture.py:90-93), times the optional training-time view-noise rotation (:94-99), divided by (norm + 1e-12) (:100);
+ * VanillaCondMLP(d_in -> H -> H -> 3) with LeakyReLU(0.01) (models/network_utils.py:182-249) and a sigmoid (:121-123).
+ * The latent code is the same for every Gaussian of a frame and is folded into the first bias; the three linear layers
+ * run on tcgen05 tensor cores (64-wide layers, accumulators in TMEM, 2-way BF16 split as in nonrigid_forward) in a
+ * persistent kernel whose weights stay resident in shared memory. */
+typedef struct ColorArgs {
+  int32_t P;
+  int32_t feature_dim;     /* F (32) */
+  int32_t sh_degree;       /* 0..3; contributes (sh_degree+1)^2 - 1 inputs */
+  int32_t non_rigid_dim;   /* R (16), 0 = none */
+  int32_t latent_dim;      /* Z (16), 0 = none */
+  int32_t hidden;          /* H: must be 64 */
+  int32_t cano_view_dir;   /* texture.py:90 */
+  int32_t pad_;
+  const float* features;   /* [P,F] gaussians.get_features.squeeze(-1) */
+  const float* xyz;        /* [P,3] deformed means (gaussians.get_xyz of the posed set) */
+  const float* T_fwd;      /* [P,16] row-major forward transforms (needed when cano_view_dir), else NULL */
+  const float* camera_center; /* [3] */
+  const float* view_noise; /* [9] row-major 3x3, dir <- dir @ view_noise (training augmentation), or NULL */
+  const float* non_rigid_feature; /* [P,R] or NULL when R == 0 */
+  const float* latent;     /* [Z] latent code of the frame, or NULL when Z == 0 */
+  const float* W0; const float* b0;  /* [H, F + S + R + Z], [H]   (S = (sh_degree+1)^2 - 1; F + S + R <= 64) */
+  const float* W1; const float* b1;  /* [H, H], [H] */
+  const float* W2; const float* b2;  /* [3, H], [3] */
+  float* colors;           /* [P,3] sigmoid(MLP) = colors_precomp of the rasterizer */
+  float* inputs;           /* [P, F + S + R] composed per-Gaussian input (debug / tests), or NULL */
+} ColorArgs;
+size_t color_workspace_bytes(const ColorArgs* args);
+int color_forward(const ColorArgs* args, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- photometric L1 loss of the training step, forward + per-pixel gradient in one pass ----
  * Replaces l1_loss (utils/loss_utils.py:19-20: torch.abs(network_output - gt).mean(), called at train.py:121) and its
  * autograd backward.  `loss` [1] = mean |image - target|; `dL_dimage` [n] = sign(image - target) / n (sign(0) = 0), i.e.
@@ -267,7 +302,8 @@ void gs_profile_enable(int on);
 int gs_profile_read(float* ms_host /* [7]: preprocess, binning, blend fwd, blend bwd, preprocess bwd, pose fwd, pose bwd */);
 int gs_fma_probe(int blocks, int threads, int iters, float* out_dev, void* stream);
 
-/* sizeof of the ABI structs: 0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs */
+/* sizeof of the ABI structs: 0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs,
+ * 6 ColorArgs */
 size_t gs_sizeof(int32_t which);
 int gs_last_cuda_error(void);
 const char* gs_version(void);
