@@ -57,16 +57,20 @@ class SMPLNNFused(nn.Module):
 
 
 class FusedGaussianConverter(nn.Module):
-    def __init__(self, rigid, non_rigid=None, pose_encoder=None, cano_view_dir=True):
+    def __init__(self, rigid, non_rigid=None, pose_encoder=None, cano_view_dir=True, texture=None):
         """rigid: SMPLNNFused | SkinningFieldFused (anything with query_weights(xyz) -> [P,24]);
-        non_rigid: HashGridMLPFused or None; pose_encoder(rots, Jtrs) -> [1,C] (HierarchicalPoseEncoder) for its condition."""
+        non_rigid: HashGridMLPFused or None; pose_encoder(rots, Jtrs) -> [1,C] (HierarchicalPoseEncoder) for its condition;
+        texture: None = `sh2rgb` (SH colour inside the fused posing kernel) or a ColorMLPFused = `mlp` (texture.py:128-134),
+        in which case the Gaussians carry feature vectors (`use_sh: false`, gaussian_model.py:45-46,182) instead of SH."""
         super().__init__()
         self.rigid, self.non_rigid, self.pose_encoder, self.cano_view_dir = rigid, non_rigid, pose_encoder, cano_view_dir
+        self.texture = texture
 
     def forward(self, gaussians, camera, iteration, compute_loss=True):
         g = gaussians
         xyz, scaling, rotation = g._xyz, g._scaling, g._rotation
         loss_reg = {}
+        deltas = None
         if self.non_rigid is not None and iteration >= self.non_rigid.delay:  # non_rigid.py:227-232
             cond = self.pose_encoder(camera.rots, camera.Jtrs) if self.pose_encoder is not None else \
                 torch.zeros(self.non_rigid.n_cond, device=xyz.device)
@@ -77,10 +81,20 @@ class FusedGaussianConverter(nn.Module):
                             "nr_rot": deltas[:, 7:10].norm(p=1, dim=1).mean()}
         query = getattr(self.rigid, "query_weights_autograd", None) if torch.is_grad_enabled() else None
         weights = (query or self.rigid.query_weights)(xyz)  # at the non-rigidly displaced position (rigid.py:217-220)
-        means, cov, colors, opacity, T_fwd, Rbar = fused_pose(
-            xyz, rotation, scaling, g._opacity, g._features_dc, g._features_rest, weights, camera.bone_transforms,
-            camera.camera_center, g.active_sh_degree, 1.0, self.cano_view_dir, return_aux=True)
         feats = torch.cat([g._features_dc, g._features_rest], 1)
+        if self.texture is None:
+            f_dc, f_rest, deg = g._features_dc, g._features_rest, g.active_sh_degree
+        else:  # colours come from the texture MLP: the posing kernel gets a constant degree-0 stand-in
+            f_dc, f_rest, deg = xyz.new_zeros(xyz.shape[0], 1, 3), xyz.new_zeros(xyz.shape[0], 0, 3), 0
+        means, cov, colors, opacity, T_fwd, Rbar = fused_pose(
+            xyz, rotation, scaling, g._opacity, f_dc, f_rest, weights, camera.bone_transforms,
+            camera.camera_center, deg, 1.0, self.cano_view_dir, return_aux=True)
         deformed = PosedGaussians(means, cov, opacity, scaling, rotation, feats, T_fwd, Rbar, g.active_sh_degree,
                                   getattr(g, "max_sh_degree", 3))
+        if self.texture is not None:
+            tex = self.texture
+            if tex.non_rigid_dim > 0:  # non_rigid.py:59-60 (zeros before the delay), :87,119-120
+                deformed.non_rigid_feature = deltas[:, 10:10 + tex.non_rigid_dim] if deltas is not None else \
+                    xyz.new_zeros(xyz.shape[0], tex.non_rigid_dim)
+            colors = tex(deformed, camera)  # ColorMLP.forward(deformed_gaussians, camera), gaussian_converter.py:57
         return deformed, loss_reg, colors

@@ -166,6 +166,7 @@ size_t gs_sizeof(int32_t which) {
     case 4: return sizeof(NonRigidArgs);
     case 5: return sizeof(SkinArgs);
     case 6: return sizeof(ColorArgs);
+    case 7: return sizeof(AdamArgs);
     default: return 0;
   }
 }

@@ -121,7 +121,10 @@ __device__ __forceinline__ void cl_publish() {
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 }
 
-__global__ void __launch_bounds__(NR_TILE, 2) color_fwd_kernel(ColorArgs a, ClWs w, int n_tiles) {
+// FAST: the default configuration (feature 32 | SH deg 3 -> 15 | non-rigid 16): every index of the input row is a
+// compile-time constant, so the row lives in registers (the generic variant keeps it in local memory).
+template <bool FAST>
+__global__ void __launch_bounds__(NR_TILE, 3) color_fwd_kernel(ColorArgs a, ClWs w, int n_tiles) {
   extern __shared__ __align__(1024) unsigned char cl_smem_raw[];
   ClSmem& sm = *reinterpret_cast<ClSmem*>(cl_smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5, row = tid;
@@ -143,7 +146,8 @@ __global__ void __launch_bounds__(NR_TILE, 2) color_fwd_kernel(ColorArgs a, ClWs
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = sm.tmem_base;
   const uint32_t tmem_row = tmem + ((uint32_t)(warp * 32) << 16);  // this warp's 32-lane quadrant
-  const int F = a.feature_dim, S = cl_n_sh(a.sh_degree), R = a.non_rigid_dim, n_in = F + S + R;
+  const int F = FAST ? 32 : a.feature_dim, S = FAST ? 15 : cl_n_sh(a.sh_degree), R = FAST ? 16 : a.non_rigid_dim, n_in = F + S + R;
+  const int deg = FAST ? 3 : a.sh_degree;
   float cam[3] = {0.f, 0.f, 0.f};
   if (S > 0) { cam[0] = a.camera_center[0]; cam[1] = a.camera_center[1]; cam[2] = a.camera_center[2]; }
   uint32_t phase = 0;
@@ -159,7 +163,15 @@ __global__ void __launch_bounds__(NR_TILE, 2) color_fwd_kernel(ColorArgs a, ClWs
       for (int k = 0; k < CL_K0; k++) in[k] = 0.f;
       if (live) {
         const float* f = a.features + (size_t)i * F;
-        for (int k = 0; k < F; k++) in[k] = f[k];
+        if (FAST) {  // 128-byte rows: 8 x LDG.128
+#pragma unroll
+          for (int k = 0; k < 32; k += 4) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(f + k));
+            in[k] = v.x; in[k + 1] = v.y; in[k + 2] = v.z; in[k + 3] = v.w;
+          }
+        } else {
+          for (int k = 0; k < F; k++) in[k] = f[k];
+        }
         if (S > 0) {
           float dx = a.xyz[3 * (size_t)i] - cam[0], dy = a.xyz[3 * (size_t)i + 1] - cam[1], dz = a.xyz[3 * (size_t)i + 2] - cam[2];
           if (a.cano_view_dir) {  // R_bwd = T_fwd[:3,:3]^T; dir <- R_bwd . dir
@@ -178,15 +190,34 @@ __global__ void __launch_bounds__(NR_TILE, 2) color_fwd_kernel(ColorArgs a, ClWs
           }
           const float inv = 1.0f / (sqrtf(dx * dx + dy * dy + dz * dz) + 1e-12f);
           float sh[15];
-          sh_bases_1(a.sh_degree, dx * inv, dy * inv, dz * inv, sh);
-          for (int k = 0; k < S; k++) in[F + k] = sh[k];
+          sh_bases_1(deg, dx * inv, dy * inv, dz * inv, sh);
+          if (FAST) {
+#pragma unroll
+            for (int k = 0; k < 15; k++) in[32 + k] = sh[k];
+          } else {
+            for (int k = 0; k < S; k++) in[F + k] = sh[k];
+          }
         }
         if (R > 0) {
           const float* nr = a.non_rigid_feature + (size_t)i * R;
-          for (int k = 0; k < R; k++) in[F + S + k] = nr[k];
+          if (FAST) {
+#pragma unroll
+            for (int k = 0; k < 16; k += 4) {
+              const float4 v = __ldg(reinterpret_cast<const float4*>(nr + k));
+              in[47 + k] = v.x; in[48 + k] = v.y; in[49 + k] = v.z; in[50 + k] = v.w;
+            }
+          } else {
+            for (int k = 0; k < R; k++) in[F + S + k] = nr[k];
+          }
         }
-        if (a.inputs)
-          for (int k = 0; k < n_in; k++) a.inputs[(size_t)i * n_in + k] = in[k];
+        if (a.inputs) {
+          if (FAST) {
+#pragma unroll
+            for (int k = 0; k < 63; k++) a.inputs[(size_t)i * 63 + k] = in[k];
+          } else {
+            for (int k = 0; k < n_in; k++) a.inputs[(size_t)i * n_in + k] = in[k];
+          }
+        }
       }
 #pragma unroll
       for (int k = 0; k < CL_K0; k += 8) store_act8(sm.A_hi, sm.A_lo, row, k, in + k);
@@ -245,14 +276,19 @@ extern "C" int color_forward(const ColorArgs* args, void* workspace, size_t work
   color_prep_kernel<<<16, 256, 0, st>>>(a, w);
   static int sms = 0;
   if (!sms) {
-    if (gs_check(cudaFuncSetAttribute(color_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ClSmem) + 1024)) != GS_OK)
+    if (gs_check(cudaFuncSetAttribute(color_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ClSmem) + 1024)) != GS_OK ||
+        gs_check(cudaFuncSetAttribute(color_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ClSmem) + 1024)) != GS_OK)
       return GS_ERR_CUDA;
     int dev = 0;
     if (gs_check(cudaGetDevice(&dev)) != GS_OK || gs_check(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)) != GS_OK)
       return GS_ERR_CUDA;
   }
   const int n_tiles = (a.P + NR_TILE - 1) / NR_TILE;
-  const int grid = n_tiles < 2 * sms ? n_tiles : 2 * sms;  // persistent: two CTAs per SM (70 KB of shared memory each)
-  color_fwd_kernel<<<grid, NR_TILE, sizeof(ClSmem) + 1024, st>>>(a, w, n_tiles);
+  const int grid = n_tiles < 3 * sms ? n_tiles : 3 * sms;  // persistent: three CTAs per SM (70 KB of shared memory, 64 TMEM columns each)
+  const bool aligned = ((uintptr_t)a.features % 16 == 0) && (!a.non_rigid_feature || (uintptr_t)a.non_rigid_feature % 16 == 0);
+  if (a.feature_dim == 32 && a.sh_degree == 3 && a.non_rigid_dim == 16 && aligned)
+    color_fwd_kernel<true><<<grid, NR_TILE, sizeof(ClSmem) + 1024, st>>>(a, w, n_tiles);
+  else
+    color_fwd_kernel<false><<<grid, NR_TILE, sizeof(ClSmem) + 1024, st>>>(a, w, n_tiles);
   return gs_check(cudaGetLastError());
 }

@@ -285,6 +285,38 @@ typedef struct ColorArgs {
 size_t color_workspace_bytes(const ColorArgs* args);
 int color_forward(const ColorArgs* args, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- optimiser-side per-Gaussian work of a training iteration ----
+ * adam_step: torch.optim.Adam as configured by GaussianModel.training_setup (scene/gaussian_model.py:201-221: six
+ * parameter groups with their own learning rates, betas (0.9, 0.999), eps 1e-15, no weight decay / amsgrad), applied by
+ * scene.optimize at train.py:231-232, as ONE launch over a flat parameter slab.  The slab layout is the flat gradient
+ * slab of pose_backward (xyz 3P | rotation 4P | scaling 3P | opacity P | f_dc 3P | f_rest 3(M-1)P), which is also the
+ * buffer the data-parallel all-reduce runs over; `group_end` are the exclusive end offsets of the groups, `lrs` a
+ * DEVICE array (the xyz learning rate is rescheduled every iteration, gaussian_model.py:223-229; the launch can sit in a
+ * CUDA graph).  `state` = adam_state_bytes() zero-initialised device bytes holding the step counter.  Operation order is
+ * torch's _single_tensor_adam. */
+#define ADAM_MAX_GROUPS 8
+typedef struct AdamArgs {
+  int64_t n;                 /* scalars in the slab */
+  int32_t n_groups;
+  int32_t pad_;
+  int64_t group_end[ADAM_MAX_GROUPS];
+  const float* lrs;          /* device [n_groups] */
+  float beta1, beta2, eps;
+  float pad2_;
+  float* params;             /* [n] updated in place */
+  const float* grads;        /* [n] */
+  float* exp_avg;            /* [n] */
+  float* exp_avg_sq;         /* [n] */
+  void* state;               /* device, adam_state_bytes() */
+} AdamArgs;
+size_t adam_state_bytes(void);
+int adam_step(const AdamArgs* args, void* stream);
+
+/* densify_stats: for every visible Gaussian (radii > 0): max_radii2D = max(max_radii2D, radii) (train.py:219),
+ * xyz_gradient_accum += ||viewspace_grad[:, :2]||, denom += 1 (scene/gaussian_model.py:464-466), one pass. */
+int densify_stats(int32_t P, const int32_t* radii, const float* viewspace_grad /*[P,3]*/, float* max_radii2D /*[P]*/,
+                  float* xyz_gradient_accum /*[P]*/, float* denom /*[P]*/, void* stream);
+
 /* ---- photometric L1 loss of the training step, forward + per-pixel gradient in one pass ----
  * Replaces l1_loss (utils/loss_utils.py:19-20: torch.abs(network_output - gt).mean(), called at train.py:121) and its
  * autograd backward.  `loss` [1] = mean |image - target|; `dL_dimage` [n] = sign(image - target) / n (sign(0) = 0), i.e.
@@ -303,7 +335,7 @@ int gs_profile_read(float* ms_host /* [7]: preprocess, binning, blend fwd, blend
 int gs_fma_probe(int blocks, int threads, int iters, float* out_dev, void* stream);
 
 /* sizeof of the ABI structs: 0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs,
- * 6 ColorArgs */
+ * 6 ColorArgs, 7 AdamArgs */
 size_t gs_sizeof(int32_t which);
 int gs_last_cuda_error(void);
 const char* gs_version(void);

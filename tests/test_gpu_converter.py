@@ -111,3 +111,69 @@ def test_converter_full_chain_trains_every_parameter(built_lib):
             p -= p.grad * (1e-4 / float(p.grad.abs().max()))
         loss1 = ((render(100)[0] - target) ** 2).mean()
     assert float(loss1) < float(loss0.detach()), (float(loss0.detach()), float(loss1))
+
+
+def test_converter_default_config_mlp_texture_and_mask(built_lib):
+    """The repository's default configuration end to end: non-rigid (hash grid + MLP with 16 extra feature outputs) ->
+    skinning field -> fused posing -> colour-MLP texture (`mlp`, 32-d per-Gaussian features, use_sh false) -> ONE
+    rasterisation returning colour + opacity (return_opacity) -> L1 + mask loss.  The colours equal the oracle's ColorMLP
+    on the module's own intermediate tensors; every trainable tensor of the chain receives a finite, non-zero gradient."""
+    from avatar_pose.modules import FusedGaussianConverter
+    from avatar_pose.nonrigid import HashGridMLPFused
+    from avatar_pose.skinning import SkinningFieldFused
+    from avatar_pose.texture import ColorMLPFused
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    from oracle import color_oracle
+    dev = torch.device("cuda:0")
+    torch.manual_seed(1)
+    P = 4000
+    g = synth.canonical_gaussians(P, seed=3)
+    gm = types.SimpleNamespace(active_sh_degree=0, max_sh_degree=0)
+    for k in ("xyz", "rotation", "scaling", "opacity"):
+        setattr(gm, "_" + k, torch.from_numpy(g[k]).to(dev).requires_grad_(True))
+    gm._features_dc = (0.5 * torch.randn(P, 1, 1, device=dev)).requires_grad_(True)     # gaussian_model.py:182: [P, feature_dim, 1]
+    gm._features_rest = (0.5 * torch.randn(P, 31, 1, device=dev)).requires_grad_(True)
+    lo, hi = (g["xyz"].min(0) - 0.05).tolist(), (g["xyz"].max(0) + 0.05).tolist()
+    nr = HashGridMLPFused(n_cond=144, feature_dim=16, aabb_min=lo, aabb_max=hi, delay=10)
+    sk = SkinningFieldFused(aabb_min=lo, aabb_max=hi)
+    tex = ColorMLPFused(n_frames=8)
+    with torch.no_grad():
+        nr.table.mul_(300.0)
+        nr.lin3.weight.mul_(0.05)
+        nr.lin3.weight[10:].mul_(100.0)  # visible non-rigid features
+        sk.lin4.weight.mul_(4.0)
+        for l in range(3):
+            getattr(tex, f"lin{l}").weight.mul_(3.0)
+    enc = lambda rots, Jtrs: torch.full((1, 144), 0.1, device=dev)
+    conv = FusedGaussianConverter(sk, nr, enc, texture=tex).to(dev).eval()
+    ps, cam = synth.pose(2), synth.camera(W=128, H=128, fx=134.0, fy=134.0)
+    camera = types.SimpleNamespace(bone_transforms=torch.from_numpy(ps["bone_transforms"]).to(dev),
+                                   camera_center=torch.from_numpy(cam["camera_center"]).to(dev), rots=None, Jtrs=None, latent_idx=5)
+    d = lambda a: torch.as_tensor(np.ascontiguousarray(a)).to(dev)
+    rs = GaussianRasterizationSettings(128, 128, cam["tanfovx"], cam["tanfovy"], torch.zeros(3, device=dev), 1.0,
+                                       d(cam["world_view_transform"]), d(cam["full_proj_transform"]), 0, d(cam["camera_center"]), False, False)
+    deformed, loss_reg, colors = conv(gm, camera, 100)
+    assert colors.shape == (P, 3) and deformed.non_rigid_feature.shape == (P, 16)
+    assert float(deformed.non_rigid_feature.abs().max()) > 1e-3
+    # oracle ColorMLP on the chain's own intermediates (fp64)
+    D = lambda t: t.detach().double().cpu()
+    truth = color_oracle.color_forward(D(deformed.get_features).squeeze(-1), D(deformed.get_xyz), D(deformed.fwd_transform).reshape(P, 16),
+                                       D(camera.camera_center), D(deformed.non_rigid_feature), D(tex.latent.weight[5]),
+                                       [D(getattr(tex, f"lin{l}").weight) for l in range(3)],
+                                       [D(getattr(tex, f"lin{l}").bias) for l in range(3)], 3, True, None)
+    assert float((D(colors) - truth).abs().max()) <= 3e-5
+    assert float(D(colors).std()) > 0.01
+    screenspace = torch.zeros_like(deformed.get_xyz, requires_grad=True)
+    img, radii, opim = GaussianRasterizer(rs)(means3D=deformed.get_xyz, means2D=screenspace, opacities=deformed.get_opacity,
+                                              colors_precomp=colors, cov3D_precomp=deformed.get_covariance(1.0), return_opacity=True)
+    target = torch.rand(3, 128, 128, device=dev)
+    mask = (torch.rand(1, 128, 128, device=dev) > 0.5).float()
+    loss = (img - target).abs().mean() + 0.1 * (opim - mask).abs().mean() + 0.01 * sum(loss_reg.values())
+    loss.backward()
+    named = list(conv.named_parameters()) + [(k, getattr(gm, "_" + k)) for k in ("xyz", "rotation", "scaling", "opacity", "features_dc", "features_rest")]
+    for name, p in named:
+        if name == "texture.latent.weight":
+            assert p.grad is not None and float(p.grad[5].abs().max()) > 0 and float(p.grad[:5].abs().max()) == 0
+            continue
+        assert p.grad is not None and torch.isfinite(p.grad).all() and float(p.grad.abs().max()) > 0, name
+    assert float(screenspace.grad.abs().max()) > 0
