@@ -2,10 +2,20 @@
 // interfaces they replace).  Orchestration only: carve the caller's workspaces, launch the stage kernels on the
 // caller's stream, never allocate, never synchronise (except in debug mode, like CHECK_CUDA auxiliary.h:166-173).
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "gs_common.cuh"
 
 static thread_local int g_last_cuda_error = 0;
+
+bool gs_fwd_two_kernel_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GS_FWD_TWO_KERNEL");
+    v = (e && e[0] == '1') ? 1 : 0;
+  }
+  return v != 0;
+}
 
 int gs_check(cudaError_t e) {
   if (e == cudaSuccess) return GS_OK;
@@ -103,7 +113,7 @@ int gs_forward(const GsForwardArgs* args, void* geom, size_t geom_bytes, void* i
     GS_TRY(gs_check(cudaMemcpyAsync(num_rendered_pinned_host, &g.hdr->num_rendered, 2 * sizeof(int64_t),
                                     cudaMemcpyDeviceToHost, st)));
   gs_prof_mark(ST_BLEND_F, 0, st);
-  GS_TRY(gs_launch_blend_fwd(a, g, im, l, st));
+  GS_TRY(gs_launch_blend_fwd(a, g, im, l, s, st));
   gs_prof_mark(ST_BLEND_F, 1, st);
   GS_TRY(debug_sync(a.debug, st));
   return GS_OK;

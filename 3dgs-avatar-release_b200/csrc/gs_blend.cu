@@ -17,6 +17,8 @@
 // Backward: same traversal back-to-front; the nine per-Gaussian gradient terms are reduced over the warp's 32 pixels
 // with a transposing butterfly (14 shuffles instead of 45) BEFORE any atomic: 9 atomics per (warp, entry) instead
 // of 9 per (pixel, entry).
+#include <stdlib.h>
+
 #include "gs_common.cuh"
 
 namespace {
@@ -347,6 +349,206 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   }
 }
 
+// ---- forward, two-kernel variant -------------------------------------------------------------------------------------
+// The trace of the one-kernel blend (profiles/tools/fwd_trace.py) shows the deepest tile's consumer spending ~70 % of its
+// time on producer/consumer hand-overs, not on the transmittance chain.  Here the two halves are separate grids:
+//   blend_rows_kernel   fully parallel over (tile, 128-entry segment) x 8 pixel blocks: cull + the reference's alpha tests,
+//                       surviving rows written to fixed (tile, block, batch) slots (L2-resident between the two grids);
+//   blend_chain_kernel  ONE warp per (tile, pixel block), longest lists first: streams its rows through a cp.async ring
+//                       (no cross-warp synchronisation at all) and runs only the serial part -- the same operations in the
+//                       same order as the consumer above, so final_T / n_contrib / image stay bit-identical.
+__device__ __forceinline__ size_t rows_batch_index(uint32_t seg_base, uint32_t nseg, int blk, int b) {
+  return ((size_t)seg_base * 8 + (size_t)blk * nseg) * (GS_SEG / 32) + (size_t)b;  // [tile][pixel block][batch]
+}
+
+__global__ void __launch_bounds__(kWarps * 32)
+blend_rows_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int grid_x,
+                  const uint32_t* __restrict__ seg_off, int tiles, const uint2* __restrict__ items,
+                  const GsRec* __restrict__ rec, float* __restrict__ rows_alpha, float4* __restrict__ rows_data,
+                  uint8_t* __restrict__ rows_cnt) {
+  GS_PDL_PROLOGUE();
+  __shared__ Slab s_slab[kWarps];
+  if (blockIdx.x >= seg_off[tiles]) return;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  Slab& sl = s_slab[w];
+  const uint2 item = items[blockIdx.x];
+  const int tile = (int)item.x, seg = (int)item.y;
+  const uint2 range = ranges[tile];
+  const int len = (int)(range.y - range.x);
+  const int seg_begin = seg * GS_SEG, seg_end = min(len, seg_begin + GS_SEG);
+  const uint32_t seg_base = seg_off[tile], nseg = (uint32_t)((len + GS_SEG - 1) / GS_SEG);
+  const int tx = tile % grid_x, ty = tile / grid_x;
+  const int bx = tx * GS_TILE + (w & 1) * 8, by = ty * GS_TILE + (w >> 1) * 4;
+  const float pfx = (float)(bx + (lane & 7)), pfy = (float)(by + (lane >> 3));
+  const float X0 = (float)bx, X1 = (float)(bx + 7), Y0 = (float)by, Y1 = (float)(by + 3);
+  const uint32_t* const sl_list = list + range.x + seg_begin;
+  constexpr int NB = GS_SEG / 32;
+  Rec3 r[NB];  // all gathers of the segment in flight at once
+#pragma unroll
+  for (int bb = 0; bb < NB; bb++) {
+    r[bb].a = r[bb].b = r[bb].c = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (seg_begin + bb * 32 + lane < seg_end) r[bb] = load_rec(rec, sl_list[bb * 32 + lane]);
+  }
+#pragma unroll
+  for (int bb = 0; bb < NB; bb++) {
+    const bool valid_e = seg_begin + bb * 32 + lane < seg_end;
+    const int b = seg * NB + bb;  // batch index inside the tile list
+    const size_t q = rows_batch_index(seg_base, nseg, w, b);
+    const Rec3 cur = r[bb];
+    const bool keep = valid_e && may_contribute(cur.a.x, cur.a.y, cur.b.x, cur.b.y, cur.b.z, cur.a.z, X0, X1, Y0, Y1);
+    if (valid_e) {
+      sl.q0[lane] = make_float4(cur.a.x, cur.a.y, cur.b.x, cur.b.y);
+      sl.q1[lane] = make_float4(cur.b.z, cur.b.w, cur.c.x, cur.c.y);
+      sl.q2[lane] = cur.c.z;
+    }
+    __syncwarp();
+    uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
+    float* const arow = rows_alpha + q * 1024 + lane;
+    float4* const drow = rows_data + q * 32;
+    int k = 0;
+    while (m) {
+#pragma unroll
+      for (int u = 0; u < kPChunk; u++) {
+        const bool valid = m != 0;
+        const int j = valid ? (__ffs(m) - 1) : 0;
+        m &= m - 1;
+        const float4 q0 = sl.q0[j], q1 = sl.q1[j];
+        const float dx = __fsub_rn(q0.x, pfx), dy = __fsub_rn(q0.y, pfy);
+        const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x))), -0.5f,
+                                      -__fmul_rn(dy, __fmul_rn(dx, q0.w)));
+        const float alpha = fminf(0.99f, __fmul_rn(q1.y, gs_exp(power)));
+        const bool ok = valid && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+        if (__any_sync(0xFFFFFFFFu, ok)) {  // rows no pixel of the block blends never reach the chain
+          arow[k * 32] = ok ? alpha : 0.0f;
+          if (lane == 0) drow[k] = make_float4(q1.z, q1.w, sl.q2[j], __int_as_float(b * 32 + j + 1));
+          k++;
+        }
+      }
+    }
+    for (int kk = k; kk & (kChunk - 1); kk++) {  // the chain reads whole chunks, branch-free: pad rows are 0 * finite
+      arow[kk * 32] = 0.0f;
+      if (lane == 0) drow[kk] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (lane == 0) rows_cnt[q] = (uint8_t)k;
+    __syncwarp();  // the slab is reused by the next batch
+  }
+}
+
+constexpr int kRowDepth = 4;  // batches in flight per chain warp
+struct RowBuf {
+  float alpha[32][32];
+  float4 row[32];
+};
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <bool OP>
+__global__ void __launch_bounds__(32)
+blend_chain_kernel(const uint2* __restrict__ ranges, int W, int H, const float* __restrict__ bg, float* __restrict__ final_T,
+                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, const uint32_t* __restrict__ seg_off,
+                   float4* __restrict__ ckpt, const uint32_t* __restrict__ order, int grid_x, float* __restrict__ out_opacity,
+                   float* __restrict__ ckpt_op, const float* __restrict__ rows_alpha, const float4* __restrict__ rows_data,
+                   const uint8_t* __restrict__ rows_cnt, uint32_t max_items) {
+  GS_PDL_PROLOGUE();
+  __shared__ __align__(16) RowBuf ring[kRowDepth];
+  const int lane = threadIdx.x;
+  const int blk = blockIdx.x & 7;
+  const int tile = (int)order[blockIdx.x >> 3];  // longest lists first
+  const int tile_x = tile % grid_x, tile_y = tile / grid_x;
+  const uint2 range = ranges[tile];
+  const int len = (int)(range.y - range.x);
+  const uint32_t seg_base = seg_off[tile], nseg = (uint32_t)((len + GS_SEG - 1) / GS_SEG);
+  int nb = (len + 31) >> 5;
+  if (seg_base + nseg > max_items) nb = 0;  // overflowed frame (invalid anyway, rerun by the caller): stay in bounds
+  const int bx = tile_x * GS_TILE + (blk & 1) * 8, by = tile_y * GS_TILE + (blk >> 1) * 4;
+  const int px = bx + (lane & 7), py = by + (lane >> 3);
+  const bool inside = px < W && py < H;
+  const size_t q0 = rows_batch_index(seg_base, nseg, blk, 0);
+  // row counts of 64 batches in two registers per lane (lane j: batch chunk_base + j and chunk_base + 32 + j)
+  int chunk_base = 0;
+  uint32_t cA = lane < nb ? rows_cnt[q0 + lane] : 0u, cB = 32 + lane < nb ? rows_cnt[q0 + 32 + lane] : 0u;
+  auto count_of = [&](int b) -> int {
+    const int rel = b - chunk_base;
+    return (int)__shfl_sync(0xFFFFFFFFu, rel < 32 ? cA : cB, rel & 31);
+  };
+  auto issue = [&](int b) {  // copies of batch b into its ring slot (one commit group per batch, possibly empty)
+    if (b < nb) {
+      const int cp = (count_of(b) + kChunk - 1) & ~(kChunk - 1);
+      RowBuf& buf = ring[b % kRowDepth];
+      const float* const srcA = rows_alpha + (q0 + b) * 1024;
+      for (int r0 = 0; r0 < cp; r0 += 4)  // 4 rows x 128 B per warp instruction
+        cp_async16(&buf.alpha[r0 + (lane >> 3)][(lane & 7) * 4], srcA + (r0 + (lane >> 3)) * 32 + (lane & 7) * 4);
+      if (lane < cp) cp_async16(&buf.row[lane], rows_data + (q0 + b) * 32 + lane);
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int d = 0; d < kRowDepth; d++) issue(d);
+
+  const size_t ck_base = ((size_t)seg_base + tile) * 256 + blk * 32 + lane;
+  float4* const ck = ckpt + ck_base;
+  float* const ck3 = OP ? ckpt_op + ck_base : nullptr;
+  float T = 1.0f, Tr = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, C3 = 0.f;  // see the consumer of blend_fwd_kernel
+  uint32_t last = 0;
+  for (int b = 0; b < nb; b++) {
+    if (b - chunk_base == 32) {
+      chunk_base += 32;
+      cA = cB;
+      cB = chunk_base + 32 + lane < nb ? rows_cnt[q0 + chunk_base + 32 + lane] : 0u;
+    }
+    cp_async_wait<kRowDepth - 1>();
+    __syncwarp();
+    if ((b & (GS_SEG / 32 - 1)) == 0) {
+      ck[(size_t)(b / (GS_SEG / 32)) * 256] = make_float4(T, C0, C1, C2);
+      if (OP) ck3[(size_t)(b / (GS_SEG / 32)) * 256] = C3;
+    }
+    const int cnt = count_of(b);
+    const RowBuf& ws = ring[b % kRowDepth];
+    for (int k0 = 0; k0 < cnt; k0 += kChunk) {
+      float al[kChunk];
+      float4 rw[kChunk];
+#pragma unroll
+      for (int u = 0; u < kChunk; u++) {
+        al[u] = ws.alpha[k0 + u][lane];
+        rw[u] = ws.row[k0 + u];
+      }
+#pragma unroll
+      for (int u = 0; u < kChunk; u++) {
+        const float test_T = __fmul_rn(Tr, __fsub_rn(1.0f, al[u]));
+        const bool ok = !(test_T < 0.0001f);
+        const float Tw = ok ? Tr : 0.0f;
+        C0 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].x), C0);
+        C1 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].y), C1);
+        C2 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].z), C2);
+        if (OP) C3 = __fmaf_rn(Tw, al[u], C3);
+        T = ok ? test_T : T;
+        last = (ok && al[u] != 0.0f) ? (uint32_t)__float_as_int(rw[u].w) : last;
+        Tr = test_T;
+      }
+    }
+    if (__all_sync(0xFFFFFFFFu, !inside || Tr < 0.0001f)) break;  // every pixel of the block has terminated
+    __syncwarp();  // every lane has finished reading the slot that is refilled now
+    issue(b + kRowDepth);
+  }
+  cp_async_wait<0>();
+  ck[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256] = make_float4(T, C0, C1, C2);
+  if (OP) ck3[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256] = C3;
+  if (inside) {
+    const size_t pix = (size_t)py * W + px, hw = (size_t)H * W;
+    final_T[pix] = T;
+    n_contrib[pix] = last;
+    out_color[pix] = __fmaf_rn(T, bg[0], C0);
+    out_color[hw + pix] = __fmaf_rn(T, bg[1], C1);
+    out_color[2 * hw + pix] = __fmaf_rn(T, bg[2], C2);
+    if (OP) out_opacity[pix] = __fmaf_rn(T, bg[0], C3);
+  }
+}
+
 // Transposing butterfly step: N values per lane -> N/2, exchanging with lane ^ XOR.  After the steps for XOR = 16, 8, 4, 2, 1
 // on 32 values, lane L holds the warp total of value L: 31 shuffles for 32 sums instead of 160.
 template <int N, int XOR>
@@ -557,8 +759,19 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 
 }  // namespace
 
-int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st) {
+int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, const GsScratch& s,
+                        cudaStream_t st) {
   dim3 grid((a.width + GS_TILE - 1) / GS_TILE, (a.height + GS_TILE - 1) / GS_TILE);
+  if (s.rows_alpha) {  // GS_FWD_TWO_KERNEL=1: rows + chain variant (the scratch carries its row storage only then)
+    const int gx2 = (int)grid.x, tiles = (int)(grid.x * grid.y);
+    gs_launch(blend_rows_kernel, dim3((unsigned)l.max_items), dim3(kWarps * 32), 0, st, im.ranges, l.point_list, gx2, im.seg_off,
+              tiles, l.items, g.rec, s.rows_alpha, s.rows_data, s.rows_cnt);
+    gs_launch(a.out_opacity ? blend_chain_kernel<true> : blend_chain_kernel<false>, dim3((unsigned)tiles * kWarps), dim3(32), 0, st,
+              im.ranges, a.width, a.height, a.background, im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt, im.order, gx2,
+              a.out_opacity, l.ckpt_op, (const float*)s.rows_alpha, (const float4*)s.rows_data, (const uint8_t*)s.rows_cnt,
+              (uint32_t)l.max_items);
+    return gs_check(cudaGetLastError());
+  }
 #ifndef GS_FWD_SMEM_PAD
 #define GS_FWD_SMEM_PAD 0
 #endif

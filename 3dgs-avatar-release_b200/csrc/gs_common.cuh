@@ -74,6 +74,10 @@ struct GsScratch {
   uint32_t* tile_total;     // [tiles] pairs per tile (direct placement)
   uint32_t* zero_end;
   size_t blocks_d, blocks_t, blocks_e;
+  // ---- alpha rows of the two-kernel forward blend (not zeroed; NULL when over GS_ROWS_BUDGET) ----
+  float* rows_alpha;        // [batches][32 rows][32 pixels]
+  float4* rows_data;        // [batches][32 rows] r, g, b, 1-based list position
+  uint8_t* rows_cnt;        // [batches] rows of the batch; batches = max_items * 8 blocks * (GS_SEG / 32)
 };
 
 static inline __host__ __device__ size_t gs_align_up(size_t v) { return (v + GS_ALIGN - 1) / GS_ALIGN * GS_ALIGN; }
@@ -141,6 +145,18 @@ static inline __host__ size_t gs_sort_blocks(unsigned long long n) {
   return ((size_t)n + tile - 1) / tile;
 }
 
+// Two-kernel forward blend (opt-in experiment, measured slower than the one-kernel producer/consumer blend: DESIGN.md 4.3):
+// (tile, 32-entry batch, pixel block) row slots at fixed offsets, carved only when enabled and while the worst-case row
+// storage stays under the budget.
+#define GS_ROWS_BUDGET ((size_t)1 << 30)
+bool gs_fwd_two_kernel_enabled();  // gs_api.cu: GS_FWD_TWO_KERNEL=1 in the environment (read once); default off, see DESIGN.md 4.3
+static inline __host__ size_t gs_rows_batches(int64_t cap, int W, int H) {
+  if (!gs_fwd_two_kernel_enabled()) return 0;
+  const size_t tiles = (size_t)((W + GS_TILE - 1) / GS_TILE) * ((H + GS_TILE - 1) / GS_TILE);
+  const size_t batches = ((size_t)cap / GS_SEG + tiles) * 8 * (GS_SEG / 32);
+  return batches * 32 * 144 <= GS_ROWS_BUDGET ? batches : 0;
+}
+
 // Direct placement needs the [blocks][tiles] count matrix to fit the pair-sized scratch it borrows.
 static inline __host__ bool gs_direct_binning(int P, int tiles, int64_t cap) {
   const int64_t blocks = ((int64_t)P + GS_BIN_THREADS - 1) / GS_BIN_THREADS;
@@ -165,6 +181,13 @@ static inline __host__ size_t gs_carve_scratch(char* base, int P, int W, int H, 
   gs_carve(p, t.scan_status, t.blocks_e);
   gs_carve(p, t.tile_total, (size_t)((W + GS_TILE - 1) / GS_TILE) * ((H + GS_TILE - 1) / GS_TILE));
   t.zero_end = reinterpret_cast<uint32_t*>(p);
+  const size_t rb = gs_rows_batches(cap, W, H);
+  t.rows_alpha = nullptr; t.rows_data = nullptr; t.rows_cnt = nullptr;
+  if (rb) {
+    gs_carve(p, t.rows_alpha, rb * 32 * 32);
+    gs_carve(p, t.rows_data, rb * 32);
+    gs_carve(p, t.rows_cnt, rb);
+  }
   if (s) *s = t;
   return (size_t)(p - base);
 }
@@ -227,7 +250,8 @@ static inline cudaError_t gs_launch(void (*kern)(KArgs...), dim3 grid, dim3 bloc
 int gs_launch_preprocess(const GsForwardArgs& a, const GsGeom& g, const GsScratch& s, cudaStream_t st);
 int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsScratch& s, const GsList& l,
                       int64_t cap, cudaStream_t st);
-int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st);
+int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, const GsScratch& s,
+                        cudaStream_t st);
 int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st);
 int gs_launch_preprocess_bwd(const GsBackwardArgs& a, const GsGeom& g, cudaStream_t st);
 int gs_launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);

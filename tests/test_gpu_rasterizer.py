@@ -243,3 +243,22 @@ def test_graph_capture_and_capacity_overflow_recapture(built_lib):
     assert _C.stats["capacity_regrows"] > regrows and st.capacity >= fw["N"]
     assert np.array_equal(img2.detach().cpu().numpy().view(np.uint32), fw["color"].view(np.uint32))
     assert torch.allclose(means.grad, grad, rtol=1e-4, atol=1e-9)
+
+
+def test_two_kernel_forward_blend_variant(built_lib):
+    """The forward blend has a second implementation, opt-in with GS_FWD_TWO_KERNEL=1: a fully parallel rows kernel (cull +
+    the reference's alpha tests, rows written to fixed (tile, block, batch) slots) followed by a chain kernel (one warp per
+    (tile, pixel block) streaming its rows through a cp.async ring).  Same operations in the same order, so it must be
+    bit-identical too; the choice is read once per process, so the parity tests are re-run in a child process."""
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, GS_FWD_TWO_KERNEL="1")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", os.path.join(here, "test_gpu_rasterizer.py"),
+                        os.path.join(here, "test_gpu_opacity_pass.py"), "-k",
+                        "test_avatar_forward_backward or test_sh_scale_rot_path or test_trained_like_opaque_scene or "
+                        "test_bench_config_50k_512 or test_fused_opacity_vs_oracle_two_calls"], env=env,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout
