@@ -168,7 +168,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  const GsRec* __restrict__ rec, const float* __restrict__ bg, float* __restrict__ final_T,
                  uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                  const uint32_t* __restrict__ seg_off, float4* __restrict__ ckpt, const uint32_t* __restrict__ order,
-                 int grid_x, float* __restrict__ out_opacity, float* __restrict__ ckpt_op) {
+                 int grid_x, float* __restrict__ out_opacity, float* __restrict__ ckpt_op, uint32_t* __restrict__ rowmask) {
   GS_PDL_PROLOGUE();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FwdCtl& ctl = *reinterpret_cast<FwdCtl*>(smem_raw);
@@ -201,6 +201,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     const float pfx = (float)px, pfy = (float)py;
     const float X0 = (float)bx, X1 = (float)(bx + 7), Y0 = (float)by, Y1 = (float)(by + 3);
     const uint32_t* const tl = list + range.x;
+    uint32_t* const rm = rowmask + ((size_t)seg_off[tile] * 8 + blk) * (GS_SEG / 32);  // + segment * 32 + batch in segment
     Rec3 cur;
     cur.a = cur.b = cur.c = make_float4(0.f, 0.f, 0.f, 0.f);
     uint32_t id_next = 0;
@@ -235,7 +236,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
       }
       __syncwarp();
       const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
-      uint32_t m = mask;
+      uint32_t m = mask, kept = 0;
       int k = 0;
       while (m) {
 #pragma unroll
@@ -252,6 +253,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
           if (__any_sync(0xFFFFFFFFu, ok)) {  // rows no pixel of the block blends are dropped here, off the serial chain
             ws.alpha[k][lane] = ok ? alpha : 0.0f;
             if (lane == 0) ws.row[k] = make_float4(q1.z, q1.w, ws.q2[j], __int_as_float(b * 32 + j + 1));
+            kept |= 1u << j;
             k++;
           }
         }
@@ -260,7 +262,10 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         ws.alpha[kk][lane] = 0.0f;
         if (lane == 0) ws.row[kk] = make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      if (lane == 0) ws.cnt = (uint32_t)k;
+      if (lane == 0) {
+        ws.cnt = (uint32_t)k;
+        rm[(size_t)(b >> 2) * 32 + (b & 3)] = kept;  // the backward blend visits exactly these entries
+      }
       __syncwarp();
       if (lane == 0) mbar_arrive(&ctl.full[p]);
       TRACE(b, 1);
@@ -365,7 +370,7 @@ __global__ void __launch_bounds__(kWarps * 32)
 blend_rows_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int grid_x,
                   const uint32_t* __restrict__ seg_off, int tiles, const uint2* __restrict__ items,
                   const GsRec* __restrict__ rec, float* __restrict__ rows_alpha, float4* __restrict__ rows_data,
-                  uint8_t* __restrict__ rows_cnt) {
+                  uint8_t* __restrict__ rows_cnt, uint32_t* __restrict__ rowmask) {
   GS_PDL_PROLOGUE();
   __shared__ Slab s_slab[kWarps];
   if (blockIdx.x >= seg_off[tiles]) return;
@@ -402,7 +407,7 @@ blend_rows_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       sl.q2[lane] = cur.c.z;
     }
     __syncwarp();
-    uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
+    uint32_t m = __ballot_sync(0xFFFFFFFFu, keep), kept = 0;
     float* const arow = rows_alpha + q * 1024 + lane;
     float4* const drow = rows_data + q * 32;
     int k = 0;
@@ -421,6 +426,7 @@ blend_rows_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         if (__any_sync(0xFFFFFFFFu, ok)) {  // rows no pixel of the block blends never reach the chain
           arow[k * 32] = ok ? alpha : 0.0f;
           if (lane == 0) drow[k] = make_float4(q1.z, q1.w, sl.q2[j], __int_as_float(b * 32 + j + 1));
+          kept |= 1u << j;
           k++;
         }
       }
@@ -429,7 +435,10 @@ blend_rows_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
       arow[kk * 32] = 0.0f;
       if (lane == 0) drow[kk] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    if (lane == 0) rows_cnt[q] = (uint8_t)k;
+    if (lane == 0) {
+      rows_cnt[q] = (uint8_t)k;
+      rowmask[(((size_t)seg_base + seg) * 8 + w) * NB + bb] = kept;
+    }
     __syncwarp();  // the slab is reused by the next batch
   }
 }
@@ -581,7 +590,8 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
                  float* __restrict__ dL_dmean2D /*[P,3]*/, float* __restrict__ dL_dconic /*[P,4]*/,
                  float* __restrict__ dL_dopacity, float* __restrict__ dL_dcolors,
-                 const float* __restrict__ ckpt_op, const float* __restrict__ dL_dop_pix) {
+                 const float* __restrict__ ckpt_op, const float* __restrict__ dL_dop_pix,
+                 const uint32_t* __restrict__ rowmask) {
   GS_PDL_PROLOGUE();
   __shared__ Slab s_slab[kWarps];
   if (blockIdx.x >= seg_off[tiles]) return;
@@ -597,7 +607,6 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   const int px = bx + (lane & 7), py = by + (lane >> 3);
   const bool inside = px < W && py < H;
   const float pfx = (float)px, pfy = (float)py;
-  const float X0 = (float)bx, X1 = (float)(bx + 7), Y0 = (float)by, Y1 = (float)(by + 3);
   const size_t pix = (size_t)py * W + px, hw = (size_t)H * W;
   const int last_contributor = inside ? (int)n_contrib[pix] : 0;
   const int hi = min(last_contributor, seg_end);  // this pixel owns list positions [seg_begin, hi)
@@ -606,6 +615,10 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xFFFFFFFFu, wmax, o));
   if (wmax <= seg_begin) return;
+  // entries of this segment that at least one pixel of this block blended in the forward pass (written by the forward's
+  // producers for every batch its consumer reached, i.e. every batch below wmax): the only ones worth visiting
+  const uint4 mk = *reinterpret_cast<const uint4*>(rowmask + (((size_t)seg_off[tile] + item.y) * 8 + w) * (GS_SEG / 32));
+  auto mask_of = [&](int bq) -> uint32_t { return bq == 0 ? mk.x : bq == 1 ? mk.y : bq == 2 ? mk.z : mk.w; };
   const float T_final = inside ? final_Ts[pix] : 0.f;
   float T = T_final;
   float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_alpha = 0.f;
@@ -647,21 +660,21 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   uint32_t id_cur = 0, id_next = 0;
   {
     const int pos = b * 32 + lane;
-    if (pos < wmax) { id_cur = seg_list[pos]; cur = load_rec(rec, id_cur); }
+    if (pos < wmax) { id_cur = seg_list[pos]; if ((mask_of(b) >> lane) & 1u) cur = load_rec(rec, id_cur); }
     if (b > 0) id_next = seg_list[pos - 32];
   }
   for (; b >= 0; b--) {
     const int pos = b * 32 + lane;
     bool keep = false;
-    if (pos < wmax) {
-      keep = may_contribute(cur.a.x, cur.a.y, cur.b.x, cur.b.y, cur.b.z, cur.a.z, X0, X1, Y0, Y1);
+    if (pos < wmax && ((mask_of(b) >> lane) & 1u)) {
+      keep = true;
       sl.q0[lane] = make_float4(cur.a.x, cur.a.y, cur.b.x, cur.b.y);
       sl.q1[lane] = make_float4(cur.b.z, cur.b.w, cur.c.x, cur.c.y);
       sl.q2[lane] = cur.c.z;
       sl.id[lane] = id_cur;
     }
     Rec3 nxt = cur;
-    if (b > 0) nxt = load_rec(rec, id_next);
+    if (b > 0 && ((mask_of(b - 1) >> lane) & 1u)) nxt = load_rec(rec, id_next);
     uint32_t id_nn = 0;
     if (b > 1) id_nn = seg_list[pos - 64];
     __syncwarp();
@@ -765,7 +778,7 @@ int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& 
   if (s.rows_alpha) {  // GS_FWD_TWO_KERNEL=1: rows + chain variant (the scratch carries its row storage only then)
     const int gx2 = (int)grid.x, tiles = (int)(grid.x * grid.y);
     gs_launch(blend_rows_kernel, dim3((unsigned)l.max_items), dim3(kWarps * 32), 0, st, im.ranges, l.point_list, gx2, im.seg_off,
-              tiles, l.items, g.rec, s.rows_alpha, s.rows_data, s.rows_cnt);
+              tiles, l.items, g.rec, s.rows_alpha, s.rows_data, s.rows_cnt, l.rowmask);
     gs_launch(a.out_opacity ? blend_chain_kernel<true> : blend_chain_kernel<false>, dim3((unsigned)tiles * kWarps), dim3(32), 0, st,
               im.ranges, a.width, a.height, a.background, im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt, im.order, gx2,
               a.out_opacity, l.ckpt_op, (const float*)s.rows_alpha, (const float4*)s.rows_data, (const uint8_t*)s.rows_cnt,
@@ -787,7 +800,7 @@ int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& 
   }
   gs_launch(a.out_opacity ? blend_fwd_kernel<true> : blend_fwd_kernel<false>, grid, dim3(kFwdWarps * 32), smem, st, im.ranges,
             l.point_list, a.width, a.height, g.rec, a.background, im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt,
-            im.order, gx, a.out_opacity, l.ckpt_op);
+            im.order, gx, a.out_opacity, l.ckpt_op, l.rowmask);
   return gs_check(cudaGetLastError());
 }
 
@@ -796,7 +809,7 @@ int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage&
   gs_launch(a.dL_dopacity_pix ? blend_bwd_kernel<true> : blend_bwd_kernel<false>, dim3((unsigned)l.max_items), dim3(kWarps * 32), 0, st,
       im.ranges, l.point_list, a.width, a.height, gx, im.seg_off, gx * gy, l.items, l.ckpt, a.background, g.rec,
       im.final_T, im.n_contrib, a.dL_dpix, a.dL_dmean2D, a.dL_dconic, a.dL_dopacity, a.dL_dcolor,
-      (const float*)l.ckpt_op, a.dL_dopacity_pix);
+      (const float*)l.ckpt_op, a.dL_dopacity_pix, (const uint32_t*)l.rowmask);
   return gs_check(cudaGetLastError());
 }
 

@@ -56,6 +56,8 @@ struct GsList {
   uint2* items;             // [max_items] (tile, segment) work items of the backward blend
   float4* ckpt;             // [(max_items + tiles) * 256] per-pixel (T, C.rgb) at every segment start + final state
   float* ckpt_op;           // same slots: accumulated opacity channel (written only by the fused opacity pass)
+  uint32_t* rowmask;        // [max_items][8 pixel blocks][GS_SEG / 32] per 32-entry batch: entries at least one pixel of
+                            // the block blended in the forward pass (what the backward blend visits)
   size_t max_items;
 };
 
@@ -123,6 +125,7 @@ static inline __host__ size_t gs_carve_list(char* base, int64_t cap, int W, int 
   gs_carve(p, t.items, t.max_items);
   gs_carve(p, t.ckpt, (t.max_items + tiles) * 256);
   gs_carve(p, t.ckpt_op, (t.max_items + tiles) * 256);
+  gs_carve(p, t.rowmask, t.max_items * 8 * (GS_SEG / 32));
   if (l) *l = t;
   return (size_t)(p - base);
 }
