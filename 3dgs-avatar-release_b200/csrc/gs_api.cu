@@ -177,6 +177,7 @@ size_t gs_sizeof(int32_t which) {
     case 5: return sizeof(SkinArgs);
     case 6: return sizeof(ColorArgs);
     case 7: return sizeof(AdamArgs);
+    case 8: return sizeof(PoseEncoderArgs);
     default: return 0;
   }
 }

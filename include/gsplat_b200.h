@@ -317,6 +317,26 @@ int adam_step(const AdamArgs* args, void* stream);
 int densify_stats(int32_t P, const int32_t* radii, const float* viewspace_grad /*[P,3]*/, float* max_radii2D /*[P]*/,
                   float* xyz_gradient_accum /*[P]*/, float* denom /*[P]*/, void* stream);
 
+/* ---- hierarchical pose encoder (forward): the per-frame condition of the non-rigid MLP ----
+ * Replaces HierarchicalPoseEncoder.forward, models/network_utils.py:152-178 (constructed from cfg.pose_encoder at
+ * models/deformer/non_rigid.py:33,137,206; num_joints 24, dim_per_joint 6, out_dim -1 -> identity output layer):
+ * global feature = layer_0([rots | Jtrs]); per joint, in kinematic-tree order, out[j] = Linear(ReLU(Linear([rot_j | Jtr_j |
+ * bone length | out[parent] (global feature for the root)]))); result = concatenation [24*6].  One launch. */
+typedef struct PoseEncoderArgs {
+  int32_t num_joints;      /* must be 24 */
+  int32_t dim_per_joint;   /* must be 6 */
+  int32_t rel_joints;      /* network_utils.py:155-159 */
+  int32_t pad_;
+  int32_t parents[24];     /* ktree_parents (:128-129), parents[j] < j, -1 for the root */
+  const float* rots;       /* [24,9] */
+  const float* Jtrs;       /* [24,3] */
+  const float* W0; const float* b0;  /* layer_0: [6, 288], [6] */
+  const float* Wa; const float* ba;  /* layers[j][0]: [24,19,19], [24,19] */
+  const float* Wb; const float* bb;  /* layers[j][2]: [24,6,19], [24,6] */
+  float* out;              /* [144] */
+} PoseEncoderArgs;
+int pose_encoder_forward(const PoseEncoderArgs* args, void* stream);
+
 /* ---- photometric L1 loss of the training step, forward + per-pixel gradient in one pass ----
  * Replaces l1_loss (utils/loss_utils.py:19-20: torch.abs(network_output - gt).mean(), called at train.py:121) and its
  * autograd backward.  `loss` [1] = mean |image - target|; `dL_dimage` [n] = sign(image - target) / n (sign(0) = 0), i.e.
@@ -335,7 +355,7 @@ int gs_profile_read(float* ms_host /* [7]: preprocess, binning, blend fwd, blend
 int gs_fma_probe(int blocks, int threads, int iters, float* out_dev, void* stream);
 
 /* sizeof of the ABI structs: 0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs,
- * 6 ColorArgs, 7 AdamArgs */
+ * 6 ColorArgs, 7 AdamArgs, 8 PoseEncoderArgs */
 size_t gs_sizeof(int32_t which);
 int gs_last_cuda_error(void);
 const char* gs_version(void);
