@@ -32,6 +32,14 @@ class PoseBackwardArgs(ctypes.Structure):
 
 _configured = False
 _last_slab = [None]
+_slab_buffer = [None]
+
+
+def set_grad_slab_buffer(buf):
+    """Makes every following pose backward write its flat gradient slab into `buf[:n]` (a fixed FP32 CUDA buffer, e.g. the
+    symmetric-memory buffer of avatar_pose.dist.SymmetricGradSlab, so that the all-reduce kernel finds the gradients in place)
+    instead of a fresh allocation.  None restores the default."""
+    _slab_buffer[0] = buf
 
 
 def last_grad_slab():
@@ -118,7 +126,9 @@ class _FusedPose(torch.autograd.Function):
             # one flat gradient slab (the buffer a data-parallel all-reduce runs over): xyz 3 | rot 4 | scale 3 |
             # opacity 1 | dc 3 | rest 3*nrest
             widths = [3, 4, 3, 1, 3, 3 * nrest]
-            flat = torch.empty(P * sum(widths), **f32)
+            total = P * sum(widths)
+            buf = _slab_buffer[0]
+            flat = buf[:total] if (buf is not None and buf.numel() >= total and buf.device == dev) else torch.empty(total, **f32)
             parts, off = [], 0
             for wd in widths:
                 parts.append(flat[off:off + P * wd])

@@ -40,6 +40,70 @@ def allreduce_gradients(slab, average=False, group=None):
     return slab
 
 
+class SymmetricGradSlab:
+    """The flat gradient slab in symmetric memory + the hand-written NVLink all-reduce over it (`slab_allreduce`,
+    include/gsplat_b200.h; gs_allreduce.cu).  Collective constructor (every rank of `group`, same `n`):
+
+        slab = SymmetricGradSlab(59 * P)              # once, after init_process_group("nccl")
+        avatar_pose.set_grad_slab_buffer(slab.buf)    # pose backward now writes its gradients straight into it
+        loss.backward(); slab.all_reduce()            # one kernel; capturable in the step's CUDA graph
+
+    `buf` is padded to a multiple of 4 * world floats (pad stays zero).  Falls back to nothing: construction raises where
+    symmetric memory is unavailable and the caller keeps using allreduce_gradients (NCCL)."""
+
+    def __init__(self, n, group=None, blocks=64):
+        import ctypes
+        import torch.distributed._symmetric_memory as symm
+        from diff_gaussian_rasterization import _C as _gs
+        group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        dev = torch.device("cuda", torch.cuda.current_device())
+        q = 4 * self.world
+        self.n = (int(n) + q - 1) // q * q
+        try:
+            symm.enable_symm_mem_for_group(group.group_name)
+        except Exception:
+            pass
+        self.buf = symm.empty(self.n, dtype=torch.float32, device=dev)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, group)
+        self.multicast = int(self.hdl.multicast_ptr) if getattr(self.hdl, "has_multicast_support", False) else 0
+        self.byte_offset = int(self.buf.data_ptr()) - int(self.hdl.buffer_ptrs[self.rank])
+        self.blocks = max(1, min(int(blocks), int(self.hdl.signal_pad_size) // (4 * self.world)))
+        self.error_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+
+        class Args(ctypes.Structure):
+            _fields_ = [("n", ctypes.c_int64), ("rank", ctypes.c_int32), ("world", ctypes.c_int32), ("peer_ptrs", ctypes.c_void_p),
+                        ("signal_pads", ctypes.c_void_p), ("multicast_ptr", ctypes.c_void_p), ("byte_offset", ctypes.c_int64),
+                        ("blocks", ctypes.c_int32), ("pad_", ctypes.c_int32), ("error_flag", ctypes.c_void_p)]
+        self._Args, self._gs, self._ctypes = Args, _gs, ctypes
+        L = _gs.lib()
+        L.slab_allreduce.restype = ctypes.c_int
+        L.slab_allreduce.argtypes = [ctypes.POINTER(Args), ctypes.c_void_p]
+        self._L = L
+        torch.cuda.synchronize(dev)
+        dist.barrier(group)
+
+    def all_reduce(self, n=None):
+        """In-place sum over the ranks of buf[:n] (default: the whole buffer), on the current stream."""
+        a = self._Args()
+        n = self.n if n is None else (int(n) + 3) // 4 * 4
+        a.n, a.rank, a.world = n, self.rank, self.world
+        a.peer_ptrs, a.signal_pads = int(self.hdl.buffer_ptrs_dev), int(self.hdl.signal_pad_ptrs_dev)
+        a.multicast_ptr = self.multicast if self.multicast else None
+        a.byte_offset, a.blocks, a.error_flag = self.byte_offset, self.blocks, self.error_flag.data_ptr()
+        dev = self.buf.device
+        with torch.cuda.device(dev):
+            self._gs._check(self._L.slab_allreduce(self._ctypes.byref(a), torch.cuda.current_stream(dev).cuda_stream), "slab_allreduce")
+        return self.buf
+
+    def check(self):
+        """After a synchronisation: raises if an in-kernel barrier gave up (a peer never arrived)."""
+        e = int(self.error_flag.item())
+        if e:
+            raise RuntimeError(f"slab_allreduce: cross-rank barrier timed out (code {e})")
+
+
 def allreduce_densification_stats(grad_accum, denom, max_radii2D, group=None):
     """Keeps replicas identical: sums of the view-space gradient accumulators (scene/gaussian_model.py:464-466) and the
     max of the screen radii (train.py:219-220)."""

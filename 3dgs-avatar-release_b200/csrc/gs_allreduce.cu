@@ -1,0 +1,103 @@
+// gs_allreduce.cu -- the one collective of data-parallel training: sum of the per-rank flat gradient slabs
+// that pose_bwd_kernel writes, in place, as ONE hand-written kernel over NVLink / NVSwitch peer memory (the slab lives in
+// symmetric memory: every rank holds the peers' addresses and, with NVLS, a multicast address of the same buffer).
+// Two-shot: rank r owns the r-th slice.
+//   multicast (NVLS) variant: `multimem.ld_reduce` pulls the slice already summed by the switch, `multimem.st` writes the
+//     result into every replica: each GPU moves 2/N of the slab instead of NCCL's ring traffic, and there is no staging copy;
+//   peer-to-peer variant (no multicast object): reduce-scatter with P2P loads in fixed rank order, then all-gather.
+// Ranks meet at in-kernel barriers over the symmetric signal pads (one flag per (block, peer)), so the launch sits inside the
+// step's CUDA graph right behind pose_bwd_kernel and overlaps its tail through programmatic dependent launch.  Sums are
+// identical on every rank (each slice is reduced once, then broadcast).
+#include "gs_common.cuh"
+
+namespace {
+
+#define AR_THREADS 512
+#define AR_SPIN_LIMIT (1u << 28)
+
+__device__ __forceinline__ uint32_t cas_sys_acq_rel(uint32_t* addr, uint32_t cmp, uint32_t val) {
+  uint32_t old;
+  asm volatile("atom.global.acq_rel.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
+  return old;
+}
+
+// Barrier among the blocks with this blockIdx on all ranks: thread t < world raises flag [block][rank] on peer t's pad and
+// waits for flag [block][t] on its own pad; every flag returns to 0 (same protocol as the signal pads' other users).
+__device__ __forceinline__ void barrier_remote_blocks(uint32_t* const* pads, int rank, int world, uint32_t* error_flag) {
+  __syncthreads();
+  if ((int)threadIdx.x < world) {
+    __threadfence_system();
+    const int peer = (int)threadIdx.x;
+    uint32_t* put = pads[peer] + (size_t)blockIdx.x * world + rank;
+    uint32_t* wait = pads[rank] + (size_t)blockIdx.x * world + peer;
+    uint32_t spins = 0;
+    while (cas_sys_acq_rel(put, 0u, 1u) != 0u)
+      if (++spins > AR_SPIN_LIMIT) { *error_flag = 1u; break; }
+    spins = 0;
+    while (cas_sys_acq_rel(wait, 1u, 0u) != 1u)
+      if (++spins > AR_SPIN_LIMIT) { *error_flag = 2u; break; }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float4 mm_ld_reduce(const float4* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mm_st(float4* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 ld_sys(const float4* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(AR_THREADS)
+slab_allreduce_kernel(long long n4, int rank, int world, void* const* peers, uint32_t* const* pads, float4* mc, long long byte_off,
+                      uint32_t* error_flag) {
+  GS_PDL_PROLOGUE();  // the local slab is complete (pose_bwd_kernel has finished)
+  const long long per = (n4 + world - 1) / world;
+  const long long begin = min(n4, per * rank), end = min(n4, begin + per);
+  const long long stride = (long long)gridDim.x * AR_THREADS, t0 = (long long)blockIdx.x * AR_THREADS + threadIdx.x;
+  barrier_remote_blocks(pads, rank, world, error_flag);  // every rank's slab is complete
+  if (mc) {
+    float4* const m = reinterpret_cast<float4*>(reinterpret_cast<char*>(mc) + byte_off);
+    for (long long i = begin + t0; i < end; i += stride) mm_st(m + i, mm_ld_reduce(m + i));
+    barrier_remote_blocks(pads, rank, world, error_flag);  // every slice has reached every replica
+    return;
+  }
+  float4* const mine = reinterpret_cast<float4*>(reinterpret_cast<char*>(peers[rank]) + byte_off);
+  for (long long i = begin + t0; i < end; i += stride) {  // reduce-scatter: my slice, peers in rank order
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < world; r++) {
+      const float4 v = ld_sys(reinterpret_cast<const float4*>(reinterpret_cast<const char*>(peers[r]) + byte_off) + i);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    mine[i] = acc;
+  }
+  barrier_remote_blocks(pads, rank, world, error_flag);  // every slice is final on its owner
+  for (int r = 0; r < world; r++) {                      // all-gather
+    if (r == rank) continue;
+    const long long b = min(n4, per * r), e = min(n4, b + per);
+    const float4* src = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(peers[r]) + byte_off);
+    for (long long i = b + t0; i < e; i += stride) mine[i] = ld_sys(src + i);
+  }
+  barrier_remote_blocks(pads, rank, world, error_flag);  // nobody overwrites a slab a peer is still reading
+}
+
+}  // namespace
+
+extern "C" int slab_allreduce(const SlabAllReduceArgs* args, void* stream) {
+  if (!args) return GS_ERR_BAD_ARG;
+  const SlabAllReduceArgs& a = *args;
+  if (a.n < 0 || (a.n & 3) || a.world < 1 || a.world > 64 || a.rank < 0 || a.rank >= a.world || !a.peer_ptrs || !a.signal_pads ||
+      !a.error_flag || a.blocks < 1 || (a.byte_offset & 15))
+    return GS_ERR_BAD_ARG;
+  if (a.n == 0 || a.world == 1) return GS_OK;
+  gs_launch(slab_allreduce_kernel, dim3((unsigned)a.blocks), dim3(AR_THREADS), 0, (cudaStream_t)stream, (long long)(a.n >> 2), (int)a.rank,
+            (int)a.world, a.peer_ptrs, a.signal_pads, (float4*)a.multicast_ptr, (long long)a.byte_offset, a.error_flag);
+  return gs_check(cudaGetLastError());
+}

@@ -178,6 +178,7 @@ size_t gs_sizeof(int32_t which) {
     case 6: return sizeof(ColorArgs);
     case 7: return sizeof(AdamArgs);
     case 8: return sizeof(PoseEncoderArgs);
+    case 9: return sizeof(SlabAllReduceArgs);
     default: return 0;
   }
 }

@@ -114,7 +114,13 @@ __device__ __forceinline__ void pose_core(const PoseArgs& a, int i, const float*
   const float x = a.xyz[3 * (size_t)i], y = a.xyz[3 * (size_t)i + 1], z = a.xyz[3 * (size_t)i + 2];
 #pragma unroll
   for (int r = 0; r < 3; r++) c.xb[r] = c.A[r][0] * x + c.A[r][1] * y + c.A[r][2] * z + c.t[r];
-  const float4 q = *reinterpret_cast<const float4*>(a.rotation + 4 * (size_t)i);
+  float4 q;
+  if ((reinterpret_cast<uintptr_t>(a.rotation) & 15) == 0) {
+    q = *reinterpret_cast<const float4*>(a.rotation + 4 * (size_t)i);
+  } else {  // a view into a flat parameter slab (avatar_pose.optim) starts at float 3P: aligned only when P % 4 == 0
+    const float* qp = a.rotation + 4 * (size_t)i;
+    q = make_float4(qp[0], qp[1], qp[2], qp[3]);
+  }
   const float norm = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
   c.inv_norm = 1.0f / norm;
   const float qr = q.x * c.inv_norm, qx = q.y * c.inv_norm, qy = q.z * c.inv_norm, qz = q.w * c.inv_norm;
@@ -309,7 +315,12 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
       float4 out;
       out.x = (gq[0] - qr * dotq) * c.inv_norm; out.y = (gq[1] - qx * dotq) * c.inv_norm;
       out.z = (gq[2] - qy * dotq) * c.inv_norm; out.w = (gq[3] - qz * dotq) * c.inv_norm;
-      *reinterpret_cast<float4*>(ba.dL_drotation + 4 * (size_t)i) = out;
+      float* const gq_out = ba.dL_drotation + 4 * (size_t)i;
+      if ((reinterpret_cast<uintptr_t>(ba.dL_drotation) & 15) == 0) {
+        *reinterpret_cast<float4*>(gq_out) = out;
+      } else {  // the rotation part of the flat gradient slab starts at float 3P: 16-byte aligned only when P % 4 == 0
+        gq_out[0] = out.x; gq_out[1] = out.y; gq_out[2] = out.z; gq_out[3] = out.w;
+      }
     }
     // mean: x_bar = A x + t
     const float x = a.xyz[3 * (size_t)i], y = a.xyz[3 * (size_t)i + 1], z = a.xyz[3 * (size_t)i + 2];

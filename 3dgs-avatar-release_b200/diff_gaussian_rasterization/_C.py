@@ -271,11 +271,12 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, scales, rotations, 
     with torch.cuda.device(dev):
         # one zero-filled slab carved into the 9 gradient tensors of rasterize_points.cu:151-159
         sizes = [3, 3, 3, 4, 1, 6, 3 * M, 3, 4]  # means3D, means2D, colors, conic, opacity, cov3D, sh, scales, rot
-        flat = torch.zeros(P * sum(sizes), dtype=torch.float32, device=dev)
+        pad4 = lambda n: (n + 3) // 4 * 4  # every part 16-byte aligned (the kernels read dL_dconic as float4) for any P
+        flat = torch.zeros(sum(pad4(P * s) for s in sizes), dtype=torch.float32, device=dev)
         parts, off = [], 0
         for s in sizes:
             parts.append(flat[off:off + P * s])
-            off += P * s
+            off += pad4(P * s)
         dmeans3D, dmeans2D, dcolors, dconic, dopacity, dcov3D, dsh, dscales, drot = parts
         dmeans3D, dmeans2D, dcolors = dmeans3D.view(P, 3), dmeans2D.view(P, 3), dcolors.view(P, 3)
         dconic, dopacity, dcov3D = dconic.view(P, 2, 2), dopacity.view(P, 1), dcov3D.view(P, 6)

@@ -337,6 +337,26 @@ typedef struct PoseEncoderArgs {
 } PoseEncoderArgs;
 int pose_encoder_forward(const PoseEncoderArgs* args, void* stream);
 
+/* ---- data-parallel training: in-place sum of the per-rank gradient slabs over NVLink / NVSwitch peer memory ----
+ * The reference has no multi-GPU path; this is the one collective the data-parallel step needs, as one kernel
+ * behind pose_backward instead of an NCCL call.  The slab must live in symmetric memory (same allocation on every rank,
+ * peers' addresses exchanged once): `peer_ptrs[world]` / `signal_pads[world]` are DEVICE arrays of the peers' buffer and
+ * signal-pad addresses (zero-initialised pads, >= blocks * world * 4 bytes), `multicast_ptr` the NVLS multicast address of
+ * the buffer or NULL (then peer-to-peer loads are used).  Every rank must call it with the same n / blocks; ranks meet at
+ * in-kernel barriers.  `error_flag` (device u32) is set if a barrier gives up (a peer never arrived). */
+typedef struct SlabAllReduceArgs {
+  int64_t n;               /* floats, multiple of 4 */
+  int32_t rank, world;
+  void* const* peer_ptrs;
+  uint32_t* const* signal_pads;
+  void* multicast_ptr;
+  int64_t byte_offset;     /* of the slab inside the symmetric buffer (multiple of 16) */
+  int32_t blocks;
+  int32_t pad_;
+  uint32_t* error_flag;
+} SlabAllReduceArgs;
+int slab_allreduce(const SlabAllReduceArgs* args, void* stream);
+
 /* ---- photometric L1 loss of the training step, forward + per-pixel gradient in one pass ----
  * Replaces l1_loss (utils/loss_utils.py:19-20: torch.abs(network_output - gt).mean(), called at train.py:121) and its
  * autograd backward.  `loss` [1] = mean |image - target|; `dL_dimage` [n] = sign(image - target) / n (sign(0) = 0), i.e.
@@ -355,7 +375,7 @@ int gs_profile_read(float* ms_host /* [7]: preprocess, binning, blend fwd, blend
 int gs_fma_probe(int blocks, int threads, int iters, float* out_dev, void* stream);
 
 /* sizeof of the ABI structs: 0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs,
- * 6 ColorArgs, 7 AdamArgs, 8 PoseEncoderArgs */
+ * 6 ColorArgs, 7 AdamArgs, 8 PoseEncoderArgs, 9 SlabAllReduceArgs */
 size_t gs_sizeof(int32_t which);
 int gs_last_cuda_error(void);
 const char* gs_version(void);

@@ -163,3 +163,28 @@ def test_fused_opacity_only_one_upstream(built_lib):
     assert rel_err(g["means3D"], bw2["dL_dmeans3D"]) <= 1e-4
     assert rel_err(g["opacities"], bw2["dL_dopacity"]) <= 1e-4
     assert float(np.abs(g["colors_precomp"]).max()) == 0.0
+
+
+def test_fused_opacity_empty_and_invisible(built_lib):
+    """P == 0 short-circuits to zeros like the plain path (rasterize_points.cu:81); a scene entirely behind the camera gives
+    opacity == bg[0] * 1 everywhere (T stays 1) and zero gradients."""
+    from diff_gaussian_rasterization import GaussianRasterizer
+    dev = _dev()
+    sc = scenes.avatar_scene(P=500, W=64, H=48)
+    rs = _settings(sc, dev)
+    z = lambda *s: torch.zeros(*s, device=dev)
+    img, radii, op = GaussianRasterizer(rs)(means3D=z(0, 3), means2D=z(0, 3), opacities=z(0, 1), colors_precomp=z(0, 3),
+                                            cov3D_precomp=z(0, 6), return_opacity=True)
+    assert img.shape == (3, 48, 64) and op.shape == (1, 48, 64) and radii.numel() == 0
+    assert float(img.abs().max()) == 0.0 and float(op.abs().max()) == 0.0
+    sc["bg"] = np.asarray((0.25, 0.5, 0.75), np.float32)
+    sc["means3D"] = sc["means3D"] + np.asarray([0, 0, 100.0], np.float32)  # far behind the camera
+    t = _leaves(sc, dev)
+    img, radii, op = GaussianRasterizer(_settings(sc, dev))(means3D=t["means3D"], means2D=t["means2D"], opacities=t["opacities"],
+                                                            colors_precomp=t["colors_precomp"], cov3D_precomp=t["cov3D_precomp"],
+                                                            return_opacity=True)
+    (img.sum() + op.sum()).backward()
+    torch.cuda.synchronize()
+    assert int((radii > 0).sum()) == 0
+    assert torch.all(op == 0.25) and torch.all(img[2] == 0.75)
+    assert float(t["means3D"].grad.abs().max()) == 0.0

@@ -70,7 +70,7 @@ def rel_err(a, b):
     return float(np.abs(a.astype(np.float64) - b.astype(np.float64)).max()) / scale
 
 
-@pytest.mark.parametrize("P,W,H", [(3000, 128, 128), (20000, 256, 256), (1500, 200, 120)])
+@pytest.mark.parametrize("P,W,H", [(3000, 128, 128), (20000, 256, 256), (1500, 200, 120), (3001, 128, 96)])
 def test_avatar_forward_backward(built_lib, P, W, H):
     from oracle import gs_oracle
     sc = scenes.avatar_scene(P=P, W=W, H=H)
