@@ -48,10 +48,11 @@ class SymmetricGradSlab:
         avatar_pose.set_grad_slab_buffer(slab.buf)    # pose backward now writes its gradients straight into it
         loss.backward(); slab.all_reduce()            # one kernel; capturable in the step's CUDA graph
 
-    `buf` is padded to a multiple of 4 * world floats (pad stays zero).  Falls back to nothing: construction raises where
-    symmetric memory is unavailable and the caller keeps using allreduce_gradients (NCCL)."""
+    `buf` is padded to a multiple of 4 * world floats (pad stays zero).  Construction raises where symmetric memory or the
+    NVLS multicast object is unavailable (the caller then keeps using allreduce_gradients = NCCL); the peer-to-peer variant of
+    the kernel is opt-in (`allow_p2p=True`): it has not been exercised on hardware without multicast support."""
 
-    def __init__(self, n, group=None, blocks=64):
+    def __init__(self, n, group=None, blocks=144, use_multicast=True, allow_p2p=False):
         import ctypes
         import torch.distributed._symmetric_memory as symm
         from diff_gaussian_rasterization import _C as _gs
@@ -67,10 +68,14 @@ class SymmetricGradSlab:
         self.buf = symm.empty(self.n, dtype=torch.float32, device=dev)
         self.buf.zero_()
         self.hdl = symm.rendezvous(self.buf, group)
-        self.multicast = int(self.hdl.multicast_ptr) if getattr(self.hdl, "has_multicast_support", False) else 0
+        self.multicast = int(self.hdl.multicast_ptr) if (use_multicast and getattr(self.hdl, "has_multicast_support", False)) else 0
+        if not self.multicast:
+            if not allow_p2p:
+                raise RuntimeError("SymmetricGradSlab: no NVLS multicast support for this group (peer-to-peer variant is opt-in)")
+            blocks = min(int(blocks), 128)
         self.byte_offset = int(self.buf.data_ptr()) - int(self.hdl.buffer_ptrs[self.rank])
-        self.blocks = max(1, min(int(blocks), int(self.hdl.signal_pad_size) // (4 * self.world)))
-        self.error_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.blocks = max(1, int(blocks))
+        self.error_flag = torch.zeros(16, dtype=torch.int32, device=dev)  # [0] error code, [2:10] phase timestamps of block 0
 
         class Args(ctypes.Structure):
             _fields_ = [("n", ctypes.c_int64), ("rank", ctypes.c_int32), ("world", ctypes.c_int32), ("peer_ptrs", ctypes.c_void_p),
@@ -99,7 +104,7 @@ class SymmetricGradSlab:
 
     def check(self):
         """After a synchronisation: raises if an in-kernel barrier gave up (a peer never arrived)."""
-        e = int(self.error_flag.item())
+        e = int(self.error_flag[0].item())
         if e:
             raise RuntimeError(f"slab_allreduce: cross-rank barrier timed out (code {e})")
 

@@ -13,7 +13,8 @@
 namespace {
 
 #define AR_THREADS 512
-#define AR_SPIN_LIMIT (1u << 28)
+#define AR_SPIN_LIMIT (1u << 21)  // a stuck barrier gives up after about two seconds (error word set) instead of hanging the GPU
+#define AR_UNROLL 8
 
 __device__ __forceinline__ uint32_t cas_sys_acq_rel(uint32_t* addr, uint32_t cmp, uint32_t val) {
   uint32_t old;
@@ -21,21 +22,37 @@ __device__ __forceinline__ uint32_t cas_sys_acq_rel(uint32_t* addr, uint32_t cmp
   return old;
 }
 
-// Barrier among the blocks with this blockIdx on all ranks: thread t < world raises flag [block][rank] on peer t's pad and
-// waits for flag [block][t] on its own pad; every flag returns to 0 (same protocol as the signal pads' other users).
-__device__ __forceinline__ void barrier_remote_blocks(uint32_t* const* pads, int rank, int world, uint32_t* error_flag) {
-  __syncthreads();
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Cross-rank barrier executed by ONE block per rank: thread t < world raises flag [rank] on peer t's signal pad and waits for
+// flag [t] on its own pad (load-spin, so that the waiting side does not flood its own memory with atomics while the peers'
+// remote atomics are trying to land); every flag returns to 0.
+__device__ __forceinline__ void barrier_ranks(uint32_t* const* pads, int rank, int world, uint32_t* error_flag) {
   if ((int)threadIdx.x < world) {
     __threadfence_system();
     const int peer = (int)threadIdx.x;
-    uint32_t* put = pads[peer] + (size_t)blockIdx.x * world + rank;
-    uint32_t* wait = pads[rank] + (size_t)blockIdx.x * world + peer;
+    uint32_t* put = pads[peer] + rank;
+    uint32_t* wait = pads[rank] + peer;
     uint32_t spins = 0;
     while (cas_sys_acq_rel(put, 0u, 1u) != 0u)
       if (++spins > AR_SPIN_LIMIT) { *error_flag = 1u; break; }
     spins = 0;
-    while (cas_sys_acq_rel(wait, 1u, 0u) != 1u)
+    while (ld_acquire_sys(wait) != 1u)
       if (++spins > AR_SPIN_LIMIT) { *error_flag = 2u; break; }
+    *wait = 0u;
+    __threadfence_system();
   }
   __syncthreads();
 }
@@ -59,14 +76,67 @@ __global__ void __launch_bounds__(AR_THREADS)
 slab_allreduce_kernel(long long n4, int rank, int world, void* const* peers, uint32_t* const* pads, float4* mc, long long byte_off,
                       uint32_t* error_flag) {
   GS_PDL_PROLOGUE();  // the local slab is complete (pose_bwd_kernel has finished)
+  // phase timestamps of block 0 (ns, %globaltimer) behind the error word: [2] start, [4] after barrier 1, [6] after the data
+  // phase, [8] end -- read by profiles/allreduce_bench.py (a multi-rank barrier kernel cannot be replayed under ncu)
+  unsigned long long* const stamps = reinterpret_cast<unsigned long long*>(error_flag + 2);
+  auto stamp = [&](int k) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      stamps[k] = t;
+    }
+  };
+  stamp(0);
   const long long per = (n4 + world - 1) / world;
   const long long begin = min(n4, per * rank), end = min(n4, begin + per);
   const long long stride = (long long)gridDim.x * AR_THREADS, t0 = (long long)blockIdx.x * AR_THREADS + threadIdx.x;
-  barrier_remote_blocks(pads, rank, world, error_flag);  // every rank's slab is complete
+  // local control words behind the stamps: [12] go flag, [13] blocks done
+  uint32_t* const go = error_flag + 12;
+  uint32_t* const done = error_flag + 13;
+  __shared__ bool s_last;
+  auto open_gate = [&]() {   // every rank's slab is complete: block 0 meets the peers, the other blocks wait for block 0
+    if (blockIdx.x == 0) {
+      barrier_ranks(pads, rank, world, error_flag);
+      if (threadIdx.x == 0) st_release_gpu(go, 1u);
+    } else {
+      if (threadIdx.x == 0) {
+        uint32_t spins = 0;
+        while (ld_acquire_gpu(go) == 0u)
+          if (++spins > AR_SPIN_LIMIT) { *error_flag = 3u; break; }
+      }
+      __syncthreads();
+    }
+  };
+  auto last_block = [&]() -> bool {  // true in the block that finishes a phase last (its writes and everybody else's are out)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      s_last = atomicAdd(done, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    return s_last;
+  };
+  open_gate();
+  stamp(1);
   if (mc) {
     float4* const m = reinterpret_cast<float4*>(reinterpret_cast<char*>(mc) + byte_off);
-    for (long long i = begin + t0; i < end; i += stride) mm_st(m + i, mm_ld_reduce(m + i));
-    barrier_remote_blocks(pads, rank, world, error_flag);  // every slice has reached every replica
+    // AR_UNROLL independent switch reductions in flight per thread before the first store: the round trip through the
+    // NVSwitch is microseconds, so the loop is latency-bound unless many are outstanding
+    for (long long i0 = begin + t0; i0 < end; i0 += stride * AR_UNROLL) {
+      float4 v[AR_UNROLL];
+#pragma unroll
+      for (int u = 0; u < AR_UNROLL; u++)
+        if (i0 + u * stride < end) v[u] = mm_ld_reduce(m + i0 + u * stride);
+#pragma unroll
+      for (int u = 0; u < AR_UNROLL; u++)
+        if (i0 + u * stride < end) mm_st(m + i0 + u * stride, v[u]);
+    }
+    stamp(2);
+    if (last_block()) {  // every block's stores are out: meet the peers, then leave the control words clean
+      barrier_ranks(pads, rank, world, error_flag);  // every slice has reached every replica
+      if (threadIdx.x == 0) { *go = 0u; *done = 0u; }
+      if (threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); stamps[3] = t; }
+    }
     return;
   }
   float4* const mine = reinterpret_cast<float4*>(reinterpret_cast<char*>(peers[rank]) + byte_off);
@@ -78,14 +148,29 @@ slab_allreduce_kernel(long long n4, int rank, int world, void* const* peers, uin
     }
     mine[i] = acc;
   }
-  barrier_remote_blocks(pads, rank, world, error_flag);  // every slice is final on its owner
+  // every slice is final on its owner: the last block meets the peers and re-opens the gate for the gather phase
+  uint32_t* const go2 = error_flag + 14;
+  if (last_block()) {
+    barrier_ranks(pads, rank, world, error_flag);
+    if (threadIdx.x == 0) { *done = 0u; st_release_gpu(go2, 1u); }
+  } else {
+    if (threadIdx.x == 0) {
+      uint32_t spins = 0;
+      while (ld_acquire_gpu(go2) == 0u)
+        if (++spins > AR_SPIN_LIMIT) { *error_flag = 4u; break; }
+    }
+    __syncthreads();
+  }
   for (int r = 0; r < world; r++) {                      // all-gather
     if (r == rank) continue;
     const long long b = min(n4, per * r), e = min(n4, b + per);
     const float4* src = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(peers[r]) + byte_off);
     for (long long i = b + t0; i < e; i += stride) mine[i] = ld_sys(src + i);
   }
-  barrier_remote_blocks(pads, rank, world, error_flag);  // nobody overwrites a slab a peer is still reading
+  if (last_block()) {  // nobody overwrites a slab a peer is still reading
+    barrier_ranks(pads, rank, world, error_flag);
+    if (threadIdx.x == 0) { *go = 0u; *go2 = 0u; *done = 0u; }
+  }
 }
 
 }  // namespace
@@ -97,6 +182,8 @@ extern "C" int slab_allreduce(const SlabAllReduceArgs* args, void* stream) {
       !a.error_flag || a.blocks < 1 || (a.byte_offset & 15))
     return GS_ERR_BAD_ARG;
   if (a.n == 0 || a.world == 1) return GS_OK;
+  // the peer-to-peer variant has grid-wide gates in the middle of the kernel: every block must be resident at once
+  if (!a.multicast_ptr && a.blocks > 128) return GS_ERR_BAD_ARG;
   gs_launch(slab_allreduce_kernel, dim3((unsigned)a.blocks), dim3(AR_THREADS), 0, (cudaStream_t)stream, (long long)(a.n >> 2), (int)a.rank,
             (int)a.world, a.peer_ptrs, a.signal_pads, (float4*)a.multicast_ptr, (long long)a.byte_offset, a.error_flag);
   return gs_check(cudaGetLastError());

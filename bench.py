@@ -469,11 +469,38 @@ def ours_main(args):
     eager = args.eager
     from avatar_pose import dist as apd
 
+    # the one collective of the data-parallel step: the hand-written NVLink all-reduce over the symmetric gradient slab
+    # (gs_allreduce.cu: NVLS multimem two-shot, P2P fallback); NCCL only where symmetric memory cannot be set up
+    symm_slab, collective = None, "none (single GPU)"
+    if world > 1:
+        collective = "nccl all_reduce of the flat gradient slab"
+        # measured on this pool (profiles/r1_v12_allreduce_n*.json): 11.8 MB slab, N = 2: kernel 69 us vs NCCL 67 us; N = 8: kernel
+        # 66 us vs NCCL 110 us -> the kernel from four ranks up, NCCL for two (GS_NCCL_ALLREDUCE=1 / =0 force either)
+        want_native = os.environ.get("GS_NCCL_ALLREDUCE", "1" if world < 4 else "0") != "1"
+        if want_native:
+            try:
+                symm_slab = apd.SymmetricGradSlab(59 * P)
+                avatar_pose.set_grad_slab_buffer(symm_slab.buf)
+                collective = ("slab_allreduce kernel over symmetric memory (" +
+                              ("NVLS multimem.ld_reduce / multimem.st two-shot" if symm_slab.multicast else "peer-to-peer two-shot") + ")")
+            except Exception as ex:
+                symm_slab = None
+                print(f"[bench] symmetric-memory all-reduce unavailable, using NCCL: {str(ex)[:200]}", file=sys.stderr)
+        ok = torch.tensor([1.0 if symm_slab is not None else 0.0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)  # all ranks must take the same path
+        if float(ok.item()) == 0.0 and symm_slab is not None:
+            symm_slab = None
+            avatar_pose.set_grad_slab_buffer(None)
+            collective = "nccl all_reduce of the flat gradient slab"
+
     def step_with_allreduce(f):
         """One data-parallel training step: fwd + bwd, then ONE all-reduce of the flat per-Gaussian gradient slab."""
         loss = hp.train_step(f)
         if world > 1:
-            apd.allreduce_gradients(avatar_pose.last_grad_slab())
+            if symm_slab is not None:
+                symm_slab.all_reduce(avatar_pose.last_grad_slab().numel())
+            else:
+                apd.allreduce_gradients(avatar_pose.last_grad_slab())
         return loss
 
     # the NCCL all-reduce is captured inside the graph too (one launch per step for everything)
@@ -670,6 +697,9 @@ def ours_main(args):
                                  "vs torch.optim.Adam(capturable) + the reference's torch statements, both around this library's hot path"}
         except Exception as ex:  # informational leg
             full_iter = {"unavailable": str(ex)[:300]}
+    if symm_slab is not None:
+        torch.cuda.synchronize(dev)
+        symm_slab.check()  # raises if an in-kernel cross-rank barrier gave up
     if rank != 0:
         finish(world, dev)
         return
@@ -743,7 +773,8 @@ def ours_main(args):
                                    "rasterizer (BASELINE.json configs[2]); one camera/pose per rank", "N_pairs": N, "E_fwd": E_fwd,
                        "E_bwd": E_bwd, "l2": "flushed between timed steps (256 MiB write, outside the per-step events)",
                        "launch": "eager Python calls" if eager else "one CUDA-graph replay per step (avatar_pose.graphs.GraphedStep); eager_ms_per_step is the same step launched op by op",
-                       "parallelism": f"dp{world} (frame-sharded; NCCL all-reduce of the flat gradient slab)" if world > 1 else "single GPU"},
+                       "parallelism": f"dp{world} (frame-sharded; one all-reduce of the flat gradient slab per step)" if world > 1 else "single GPU",
+                       "collective": collective},
             "e2e": {"value": world * 1e3 / ms_train_e2e, "unit": "iter/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": ms_train_e2e,
                     "pipeline": "per step: H2D of the NEXT step's pose+camera+target from pinned memory on a copy stream (double-buffered "

@@ -343,7 +343,8 @@ int pose_encoder_forward(const PoseEncoderArgs* args, void* stream);
  * peers' addresses exchanged once): `peer_ptrs[world]` / `signal_pads[world]` are DEVICE arrays of the peers' buffer and
  * signal-pad addresses (zero-initialised pads, >= blocks * world * 4 bytes), `multicast_ptr` the NVLS multicast address of
  * the buffer or NULL (then peer-to-peer loads are used).  Every rank must call it with the same n / blocks; ranks meet at
- * in-kernel barriers.  `error_flag` (device u32) is set if a barrier gives up (a peer never arrived). */
+ * in-kernel barriers.  `error_flag`: 16 device u32; [0] is set if a barrier gives up (a peer never arrived), [2:10] receive
+ * four 64-bit %globaltimer stamps of block 0 (start, after the first barrier, after the data phase, end). */
 typedef struct SlabAllReduceArgs {
   int64_t n;               /* floats, multiple of 4 */
   int32_t rank, world;
