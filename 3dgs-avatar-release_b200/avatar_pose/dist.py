@@ -52,7 +52,7 @@ class SymmetricGradSlab:
     NVLS multicast object is unavailable (the caller then keeps using allreduce_gradients = NCCL); the peer-to-peer variant of
     the kernel is opt-in (`allow_p2p=True`): it has not been exercised on hardware without multicast support."""
 
-    def __init__(self, n, group=None, blocks=144, use_multicast=True, allow_p2p=False):
+    def __init__(self, n, group=None, blocks=32, use_multicast=True, allow_p2p=False):
         import ctypes
         import torch.distributed._symmetric_memory as symm
         from diff_gaussian_rasterization import _C as _gs

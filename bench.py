@@ -764,7 +764,7 @@ def ours_main(args):
         tile_passes = (max(tiles.bit_length(), 1) + 7) // 8
         binning = 4 + 1 + tile_passes + 1 + 1                       # depth passes, emit, tile passes, ranges, plan
     # pose_fwd | preprocess, binning, blend_fwd | l1 loss fwd + bwd | blend_bwd, preprocess_bwd | pose_bwd
-    launches = args.steps * (1 + (1 + binning + 1) + 2 + 2 + 1)
+    launches = args.steps * (1 + (1 + binning + 1) + 2 + 2 + 1 + (1 if symm_slab is not None else 0))  # + slab_allreduce
     h2d = int(f_pin["small"].numel() * 4 + f_pin["target"].numel() * 4)
     line = {"metric": METRIC, "value": world * 1e3 / ms_train, "unit": "iter/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_train, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
