@@ -68,3 +68,17 @@ def test_color_range_and_dtype_agreement():
     a, b = co.color_forward(*args(c32)), co.color_forward(*args(c64))
     assert a.shape == (500, 3) and float(a.min()) > 0 and float(a.max()) < 1
     assert float((a.double() - b).abs().max()) < 5e-6
+
+
+def test_color_oracle_matches_reference_colormlp():
+    """The whole colour-MLP oracle against the reference's OWN ColorMLP + VanillaCondMLP classes (lifted out of their files
+    with `ast` and executed unmodified: tests/golden/make_color_mlp_golden.py -> tests/golden/ref_color_mlp.npz)."""
+    z = np.load(os.path.join(HERE, "golden", "ref_color_mlp.npz"))
+    T = lambda k: torch.from_numpy(z[k])
+    Ws, bs = [T(f"W{l}") for l in range(3)], [T(f"b{l}") for l in range(3)]
+    x = co.compose_input(T("features"), T("xyz"), T("T_fwd"), T("camera_center"), T("non_rigid_feature"), T("latent"), 3, True)
+    assert x.shape == (400, 79)
+    assert float((x - T("inputs")).abs().max()) <= 1e-6
+    col = co.color_forward(T("features"), T("xyz"), T("T_fwd"), T("camera_center"), T("non_rigid_feature"), T("latent"), Ws, bs, 3, True)
+    assert float((col - T("colors")).abs().max()) <= 1e-6
+    assert float(T("colors").std()) > 0.05

@@ -82,3 +82,24 @@ def test_bone_transforms_rest_pose_is_identity():
     assert np.allclose(B, np.eye(4)[None].repeat(24, 0), atol=1e-6)
     seq = synth.pose_sequence(n_frames=8)
     assert len(seq) == 8 and seq[0]["bone_transforms"].shape == (24, 4, 4)
+
+
+def test_pose_chain_matches_reference_code():
+    """The posing oracle against outputs of the reference's OWN code (SMPLNN.forward, build_rotation,
+    build_covariance_from_scaling_rotation, SH2RGB.forward -- lifted out of their files with `ast` and executed unmodified:
+    tests/golden/make_pose_chain_golden.py -> tests/golden/ref_pose_chain.npz).  fp64 oracle vs the fp32 reference run:
+    <= 2e-6 relative (fp32 rounding of the reference's matmuls); fp32 oracle: same bound."""
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_pose_chain.npz"))
+    for dt in (torch.float64, torch.float32):
+        T = lambda k: torch.from_numpy(z[k]).to(dt)
+        feat = torch.cat([T("features_dc"), T("features_rest")], 1)
+        o = po.pose_forward(T("xyz"), T("rotation"), T("scaling"), T("opacity"), feat, T("weights"), T("bone_transforms"),
+                            T("camera_center"), 3, 1.0, True)
+        for k, tol in (("means3D", 2e-6), ("T_fwd", 2e-6), ("rotation_bar", 2e-6), ("cov3D", 5e-6), ("colors", 5e-6)):
+            ref = torch.from_numpy(z[k]).double()
+            err = float((o[k].double().reshape(ref.shape) - ref).abs().max() / ref.abs().max())
+            assert err <= tol, (str(dt), k, err)
+        o07 = po.pose_forward(T("xyz"), T("rotation"), T("scaling"), T("opacity"), feat, T("weights"), T("bone_transforms"),
+                              T("camera_center"), 3, 0.7, True)
+        ref = torch.from_numpy(z["cov3D_mod07"]).double()
+        assert float((o07["cov3D"].double() - ref).abs().max() / ref.abs().max()) <= 5e-6
