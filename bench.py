@@ -274,21 +274,22 @@ def fp32_peak_tflops(dev):
 
 def ncu_traffic(stage):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernel, from the newest committed
-    `ncu --set full` summary under profiles/ (profiles/summarize.py); None when there is none."""
+    `ncu --set full` summary under profiles/ that lists it (profiles/summarize.py); None when there is none."""
     import glob
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_kernels.json")))
-    if not files:
-        return None
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_kernels.json")), reverse=True)
     mult = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0}
-    try:
-        with open(files[-1]) as f:
-            ks = json.load(f)
-        for k in ks:
-            if k["kernel"].startswith(stage + "_kernel") or k["kernel"].startswith(stage.replace("_fwd", "") + "_kernel"):
-                return (k.get("dram_read", 0.0) * mult.get(k.get("dram_read_unit", "byte"), 1.0) +
-                        k.get("dram_write", 0.0) * mult.get(k.get("dram_write_unit", "byte"), 1.0))
-    except Exception:
-        return None
+    names = (stage + "_kernel", stage.replace("_fwd", "") + "_kernel")
+    for path in files:
+        try:
+            with open(path) as f:
+                ks = json.load(f)
+            for k in ks:
+                name = k["kernel"].replace("void ", "").strip()  # templated kernels are listed as "void name<...>"
+                if name.startswith(names):
+                    return (k.get("dram_read", 0.0) * mult.get(k.get("dram_read_unit", "byte"), 1.0) +
+                            k.get("dram_write", 0.0) * mult.get(k.get("dram_write_unit", "byte"), 1.0))
+        except Exception:
+            continue
     return None
 
 
