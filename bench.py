@@ -276,7 +276,9 @@ def ncu_traffic(stage):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernel, from the newest committed
     `ncu --set full` summary under profiles/ that lists it (profiles/summarize.py); None when there is none."""
     import glob
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_kernels.json")), reverse=True)
+    import re
+    natural = lambda p: [int(t) if t.isdigit() else t for t in re.split(r"(\d+)", os.path.basename(p))]  # r1_v13 after r1_v7
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_kernels.json")), key=natural, reverse=True)
     mult = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0}
     names = (stage + "_kernel", stage.replace("_fwd", "") + "_kernel")
     for path in files:
