@@ -102,6 +102,13 @@ class SymmetricGradSlab:
             self._gs._check(self._L.slab_allreduce(self._ctypes.byref(a), torch.cuda.current_stream(dev).cuda_stream), "slab_allreduce")
         return self.buf
 
+    def close(self):
+        """Releases the symmetric buffer and its rendezvous handle (collective in effect: call on every rank, after the graphs
+        that captured all_reduce() have been released and before destroy_process_group)."""
+        self.hdl = None
+        self.buf = None
+        self.error_flag = None
+
     def check(self):
         """After a synchronisation: raises if an in-kernel barrier gave up (a peer never arrived)."""
         e = int(self.error_flag[0].item())

@@ -45,3 +45,11 @@ class GraphedStep:
                 self.graph.replay()
                 torch.cuda.current_stream().synchronize()
         return self.out
+
+    def release(self):
+        """Frees the captured graph and its static outputs (call before tearing a process group / the CUDA context down:
+        a live graph keeps kernels of the communicator and pointers into pool memory)."""
+        self.out = None
+        if self.graph is not None:
+            self.graph.reset()
+            self.graph = None

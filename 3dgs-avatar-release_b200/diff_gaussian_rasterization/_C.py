@@ -242,6 +242,15 @@ def _forward(bg, means3D, colors, opacity, scales, rotations, scale_modifier, co
         return N, out_color, radii, geom, lst, img
 
 
+def release_cached():
+    """Drops the per-device scratch caches (sort scratch, graph keep-alives, pinned words).  For an orderly shutdown: call
+    after the CUDA graphs that captured rasterize_gaussians have been released."""
+    for st in _state.values():
+        st.scratch = None
+        st.graph_keepalive.clear()
+    _state.clear()
+
+
 def graph_overflow(device=None):
     """After replaying a CUDA graph that contains rasterize_gaussians (and synchronising): returns (N, overflowed).
     overflowed means the captured pair capacity was too small, the frame is invalid, and the graph must be re-captured

@@ -34,6 +34,16 @@ P_DEFAULT, W_DEFAULT, H_DEFAULT = 50_000, 512, 512
 METRIC = "fwd+bwd training iterations/s @512x512, 50k Gaussians (posing + rasterizer)"
 
 
+def workload_config(args, info):
+    """The `config` object of the JSON line: identical text in both arms (ours / --impl reference) for the same flags."""
+    W, H, P, world = args.width, args.height, args.P, args.gpus
+    return {"workload": f"training step fwd+bwd, {W}x{H}, {P} random-init Gaussians, SH deg 3, rigid LBS posing + tile "
+                        "rasterizer (BASELINE.json configs[2]); one camera/pose per rank",
+            "N_pairs": info.get("N"), "E_fwd": info.get("E_fwd"), "E_bwd": info.get("E_bwd"),
+            "l2": "GPU arm: flushed between timed steps (256 MiB write, outside the per-step events); CPU arm: host caches, not flushed",
+            "parallelism": f"dp{world} (frame-sharded; one all-reduce of the flat gradient slab per step)" if world > 1 else "single GPU"}
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -361,14 +371,13 @@ def reference_main(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps, warmup = min(args.steps, 20), min(args.warmup, 3)
+    steps, warmup = args.steps, args.warmup  # one step of this arm = one full training step of the workload on the host (~0.15 s)
     sec, cores, info = run_cpu(args, steps, warmup)
     val = 1.0 / sec
     line = {"metric": METRIC, "value": val, "unit": "iter/s", "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
             "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "impl": "reference",
-            "config": {"workload": f"training step fwd+bwd, {args.width}x{args.height}, {args.P} random-init Gaussians, SH deg 3, "
-                                   "rigid LBS posing + tile rasterizer (BASELINE.json configs[2])", "N_pairs": info.get("N")},
+            "config": workload_config(args, info),
             "cpu_baseline": {"value": val, "unit": "iter/s", "cores": cores, "kind": "port",
                              "sample": f"{steps} full training steps of the workload (oracle/: torch-CPU posing + OpenMP C rasterizer)"},
             "e2e": {"value": val, "unit": "iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -467,7 +476,14 @@ def ours_main(args):
     f_pin = hp.frame_to_pinned(frames[rank])
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2, written between timed steps
 
-    from avatar_pose.graphs import GraphedStep
+    from avatar_pose.graphs import GraphedStep as _GraphedStep
+    graphs_alive = []
+
+    def GraphedStep(fn):
+        g_ = _GraphedStep(fn)
+        graphs_alive.append(g_)
+        return g_
+
     f_static = hp.static_frame(frames[rank])
     eager = args.eager
     from avatar_pose import dist as apd
@@ -621,14 +637,15 @@ def ours_main(args):
             dist.all_reduce(tot, op=dist.ReduceOp.MAX)
         return float(tot.item()) / steps, ts
 
+    sampler = ClockSampler(local)
     if args.profile_only:
         for _ in range(args.warmup + args.steps):
             train_resident()
         torch.cuda.synchronize(dev)
         os.dup2(saved_stdout, 1)
         print(json.dumps({"profile_only": True, "steps": args.warmup + args.steps}), flush=True)
+        finish(world, dev, graphs_alive, symm_slab, sampler)
         return
-    sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     ms_train, ts_train = timed(train_resident, args.steps, args.warmup)
@@ -704,7 +721,7 @@ def ours_main(args):
         torch.cuda.synchronize(dev)
         symm_slab.check()  # raises if an in-kernel cross-rank barrier gave up
     if rank != 0:
-        finish(world, dev)
+        finish(world, dev, graphs_alive, symm_slab, sampler)
         return
 
     # ---- rank 0: stage times, roofline, baselines ----
@@ -718,7 +735,7 @@ def ours_main(args):
     E_fwd = int(dbg["n_contrib"].to(torch.int64).sum().item())
     cpu = None
     E_bwd = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:  # N > 1: the other ranks spin in a barrier on the same host cores -- the CPU sample would be garbage
         sec, cores, info = run_cpu(args, args.cpu_steps, 1)
         cpu = {"value": 1.0 / sec, "unit": "iter/s", "cores": cores, "kind": "port",
                "sample": f"{args.cpu_steps} full training steps of this workload on the host (oracle/: torch-CPU posing + OpenMP C rasterizer)"}
@@ -772,12 +789,9 @@ def ours_main(args):
     line = {"metric": METRIC, "value": world * 1e3 / ms_train, "unit": "iter/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_train, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"training step fwd+bwd, {W}x{H}, {P} random-init Gaussians, SH deg 3, rigid LBS posing + tile "
-                                   "rasterizer (BASELINE.json configs[2]); one camera/pose per rank", "N_pairs": N, "E_fwd": E_fwd,
-                       "E_bwd": E_bwd, "l2": "flushed between timed steps (256 MiB write, outside the per-step events)",
-                       "launch": "eager Python calls" if eager else "one CUDA-graph replay per step (avatar_pose.graphs.GraphedStep); eager_ms_per_step is the same step launched op by op",
-                       "parallelism": f"dp{world} (frame-sharded; one all-reduce of the flat gradient slab per step)" if world > 1 else "single GPU",
-                       "collective": collective},
+            "config": workload_config(args, dict(N=N, E_fwd=E_fwd, E_bwd=E_bwd)),
+            "launch": "eager Python calls" if eager else "one CUDA-graph replay per step (avatar_pose.graphs.GraphedStep); eager_ms_per_step is the same step launched op by op",
+            "collective": collective,
             "e2e": {"value": world * 1e3 / ms_train_e2e, "unit": "iter/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": ms_train_e2e,
                     "pipeline": "per step: H2D of the NEXT step's pose+camera+target from pinned memory on a copy stream (double-buffered "
@@ -794,25 +808,38 @@ def ours_main(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         os.dup2(2, 1)
-    finish(world, dev)
-    # leave without interpreter teardown: destroying live CUDA graphs / their pools at exit has aborted the process after
-    # the line was already printed
-    torch.cuda.synchronize(dev)
-    sys.stdout.flush()
-    sys.stderr.flush()
-    os._exit(0)
+    finish(world, dev, graphs_alive, symm_slab, sampler)
 
 
-def finish(world, dev):
-    """End of a multi-rank run: final barrier, then leave WITHOUT tearing the process group down -- destroying an NCCL
-    communicator that live CUDA graphs still reference can hang, and the process is exiting anyway."""
+def finish(world, dev, graphs, symm_slab, sampler):
+    """Orderly end of a run, so that the interpreter exits normally (atexit handlers run): the captured CUDA graphs are
+    released FIRST (they hold kernels of the process group's communicator and pointers into the symmetric slab), then the
+    gradient-slab redirection, then the process group."""
+    import gc
     import torch.distributed as dist
+    import avatar_pose
+    from diff_gaussian_rasterization import _C
+    sampler.stop_flag = True
+    if sampler.is_alive():
+        sampler.join(timeout=10)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()  # nobody tears down while a peer's graph still reads this rank's slab
+        torch.cuda.synchronize(dev)
+    for g_ in graphs:
+        g_.release()
+    graphs.clear()
+    avatar_pose.set_grad_slab_buffer(None)
+    if symm_slab is not None:
+        symm_slab.close()
+    _C.release_cached()
+    gc.collect()
+    torch.cuda.synchronize(dev)
     if world > 1:
         dist.barrier()
-        torch.cuda.synchronize(dev)
-        sys.stdout.flush()
-        sys.stderr.flush()
-        os._exit(0)
+        dist.destroy_process_group()
+    sys.stdout.flush()
+    sys.stderr.flush()
 
 
 if __name__ == "__main__":

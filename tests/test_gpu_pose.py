@@ -40,7 +40,8 @@ def rel(a, b):
 
 
 @pytest.mark.parametrize("deg,cano,mod,P", [(3, True, 1.0, 6000), (2, True, 0.8, 6000), (1, False, 1.0, 6000), (0, True, 1.0, 6000),
-                                             (3, True, 1.0, 3001)])  # 3001: slab parts not 16-byte aligned
+                                             (3, True, 1.0, 3001),   # 3001: slab parts not 16-byte aligned
+                                             (3, True, 1.0, 50000)])  # the bench size (BASELINE.json configs[1]/[2])
 def test_pose_forward_backward(built_lib, deg, cano, mod, P):
     from avatar_pose import fused_pose
     dev = torch.device("cuda:0")

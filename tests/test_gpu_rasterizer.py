@@ -262,3 +262,41 @@ def test_two_kernel_forward_blend_variant(built_lib):
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert " passed" in r.stdout
+
+
+def test_mark_visible(built_lib):
+    """GaussianRasterizer.markVisible (rasterize_points.cu:198-217 -> checkFrustum, rasterizer_impl.cu:54-66: p_view.z > 0.2)
+    against the oracle, bit-exact, on a cloud with points in front of, behind and right at the near plane; and the same mask
+    through the reference build when baseline/_ref is on the box."""
+    import os
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    from oracle import gs_oracle
+    dev = _dev()
+    sc = scenes.generic_scene(P=50001, W=64, H=64, seed=21, spread=2.5)
+    cam = sc["cam"]
+    means = sc["means3D"].copy()
+    # a band of points whose view depth lies within a few ulp of the 0.2 threshold (the decision must be the reference's FMA order)
+    V = cam["world_view_transform"]
+    zaxis = V[:3, 2] / np.linalg.norm(V[:3, 2])
+    depth = means @ V[:3, 2] + V[3, 2]
+    k = 4000
+    means[:k] = means[:k] - (depth[:k, None] - 0.2) * zaxis[None, :] / np.linalg.norm(V[:3, 2])
+    means[:k] += (np.random.default_rng(0).integers(-3, 4, size=(k, 1)) * 1e-8).astype(np.float32)
+    d = lambda a: torch.as_tensor(np.ascontiguousarray(a, dtype=np.float32)).to(dev)
+    rs = GaussianRasterizationSettings(sc["H"], sc["W"], cam["tanfovx"], cam["tanfovy"], d(sc["bg"]), 1.0, d(cam["world_view_transform"]),
+                                       d(cam["full_proj_transform"]), 3, d(cam["camera_center"]), False, False)
+    mask = GaussianRasterizer(rs).markVisible(d(means))
+    assert mask.dtype == torch.bool and mask.shape == (means.shape[0],)
+    want = gs_oracle.mark_visible(means.astype(np.float32), cam["world_view_transform"], cam["full_proj_transform"]).astype(bool)
+    got = mask.cpu().numpy()
+    assert 0 < want.sum() < want.size
+    assert np.array_equal(got, want), f"{int((got != want).sum())} visibility decisions differ from the oracle"
+    assert GaussianRasterizer(rs).markVisible(torch.zeros(0, 3, device=dev)).numel() == 0
+    ref_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "_ref", "diff_gaussian_rasterization")
+    if os.path.isdir(ref_dir) and any(f.endswith(".so") for f in os.listdir(ref_dir)):
+        from test_gpu_vs_reference_cuda import _gen
+        ref = _gen().load_ref()
+        rrs = ref.GaussianRasterizationSettings(sc["H"], sc["W"], cam["tanfovx"], cam["tanfovy"], d(sc["bg"]), 1.0, d(cam["world_view_transform"]),
+                                                d(cam["full_proj_transform"]), 3, d(cam["camera_center"]), False, False)
+        rmask = ref.GaussianRasterizer(rrs).markVisible(d(means)).cpu().numpy()
+        assert np.array_equal(got, rmask), f"{int((got != rmask).sum())} visibility decisions differ from the reference build"

@@ -88,7 +88,14 @@ assert err <= 1e-5, ("dp-sum", err)
 assert params["xyz"].grad.data_ptr() == slab.buf.data_ptr()  # .grad views see the reduced values
 print(f"rank {rank}: ok multicast={bool(slab.multicast)} blocks={slab.blocks}", flush=True)
 dist.barrier(); torch.cuda.synchronize()
-os._exit(0)
+# orderly teardown (no os._exit: the interpreter's exit handlers must run): graph first, then the slab, then the group
+graph.reset(); del graph
+for v in params.values(): v.grad = None
+avatar_pose.set_grad_slab_buffer(None)
+del g_mine, single
+slab.close()
+torch.cuda.synchronize(); dist.barrier()
+dist.destroy_process_group()
 '''
 
 
