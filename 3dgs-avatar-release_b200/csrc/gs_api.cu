@@ -8,13 +8,15 @@
 
 static thread_local int g_last_cuda_error = 0;
 
-bool gs_fwd_two_kernel_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("GS_FWD_TWO_KERNEL");
-    v = (e && e[0] == '1') ? 1 : 0;
+// exp of the blend kernels: 0 = CUDA expf, the reference's instruction sequence (default); 1 = the gs_exp polynomial that the
+// CPU oracle reproduces bit for bit (parity tests against the oracle).  GS_EXP_MODE in the environment sets the initial value.
+static int g_exp_mode = -1;
+int gs_exp_mode() {
+  if (g_exp_mode < 0) {
+    const char* e = getenv("GS_EXP_MODE");
+    g_exp_mode = (e && e[0] == '1') ? 1 : 0;
   }
-  return v != 0;
+  return g_exp_mode;
 }
 
 int gs_check(cudaError_t e) {
@@ -136,7 +138,7 @@ int gs_backward(const GsBackwardArgs* args, const void* geom, size_t geom_bytes,
   const GsBackwardArgs& a = *args;
   cudaStream_t st = (cudaStream_t)stream;
   if (a.P <= 0) return GS_ERR_BAD_ARG;
-  if (!a.dL_dpix || !a.dL_dmean2D || !a.dL_dconic || !a.dL_dopacity || !a.dL_dcolor || !a.dL_dmean3D || !a.dL_dcov3D)
+  if (!a.dL_dpix || !a.dL_dmean2D || !a.dL_dopacity || !a.dL_dcolor || !a.dL_dmean3D || !a.dL_dcov3D)
     return GS_ERR_BAD_ARG;
   if (a.shs && (!a.dL_dsh || !a.campos)) return GS_ERR_BAD_ARG;
   if (a.scales && (!a.rotations || !a.dL_dscale || !a.dL_drot)) return GS_ERR_BAD_ARG;
@@ -184,6 +186,25 @@ size_t gs_sizeof(int32_t which) {
 }
 
 void gs_profile_enable(int on) { g_prof_on = on; }
+
+int gs_set_exp_mode(int mode) {
+  const int prev = gs_exp_mode();
+  g_exp_mode = mode ? 1 : 0;
+  return prev;
+}
+
+/* counters[0] = E_bwd, the (pixel, entry) pairs the last forward over `geom` blended; counters[1] = its forward work items.
+ * Synchronises the stream. */
+int gs_read_counters(const void* geom, uint64_t* counters_host, void* stream) {
+  if (!geom || !counters_host) return GS_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  GsHeader h;
+  GS_TRY(gs_check(cudaMemcpyAsync(&h, geom, sizeof(h), cudaMemcpyDeviceToHost, st)));
+  GS_TRY(gs_check(cudaStreamSynchronize(st)));
+  counters_host[0] = h.evals_blended;
+  counters_host[1] = h.n_fitems;
+  return GS_OK;
+}
 
 /* ms[7] = preprocess, binning (sorts+emit+ranges), blend fwd, blend bwd, preprocess bwd, pose fwd, pose bwd of the LAST call
  * (-1 where no stage was recorded).  Synchronises on the recorded events. */

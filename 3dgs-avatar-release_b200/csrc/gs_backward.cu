@@ -102,7 +102,8 @@ __device__ void cov3d_backward(const float* __restrict__ s3, float mod, const fl
 }
 
 __global__ void __launch_bounds__(256) preprocess_bwd_kernel(GsBackwardArgs a, const float* __restrict__ cov3Ds,
-                                                             const uint8_t* __restrict__ clamped) {
+                                                             const uint8_t* __restrict__ clamped, const GsRec* __restrict__ recs,
+                                                             float* __restrict__ accs) {
   GS_PDL_PROLOGUE();
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   if (threadIdx.x < 16) { s_view[threadIdx.x] = a.viewmatrix[threadIdx.x]; s_proj[threadIdx.x] = a.projmatrix[threadIdx.x]; }
@@ -113,13 +114,47 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(GsBackwardArgs a, c
   const float h_y = a.height / (2.0f * a.tan_fovy), h_x = a.width / (2.0f * a.tan_fovx);
   const float limx = 1.3f * a.tan_fovx, limy = 1.3f * a.tan_fovy;
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < a.P; idx += gridDim.x * blockDim.x) {
-    if (!(a.radii[idx] > 0)) continue;
+    // the blend's accumulators: consumed here and zeroed again (a second backward over the same forward starts clean)
+    float4* const ac = reinterpret_cast<float4*>(accs + (size_t)GS_ACC * idx);
+    const float4 ac0 = ac[0], ac1 = ac[1], ac2 = ac[2];
+    ac[0] = ac[1] = ac[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!(a.radii[idx] > 0)) {  // culled: every gradient is zero (the outputs need no initialisation by the caller)
+      a.dL_dmean2D[3 * (size_t)idx] = a.dL_dmean2D[3 * (size_t)idx + 1] = a.dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
+      a.dL_dopacity[idx] = 0.f;
+      if (a.dL_dconic) *reinterpret_cast<float4*>(a.dL_dconic + 4 * (size_t)idx) = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int k = 0; k < 3; k++) { a.dL_dcolor[3 * (size_t)idx + k] = 0.f; a.dL_dmean3D[3 * (size_t)idx + k] = 0.f; }
+#pragma unroll
+      for (int k = 0; k < 6; k++) a.dL_dcov3D[6 * (size_t)idx + k] = 0.f;
+      if (a.shs) for (int k = 0; k < 3 * a.M; k++) a.dL_dsh[(size_t)idx * a.M * 3 + k] = 0.f;
+      if (a.scales) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) a.dL_dscale[3 * (size_t)idx + k] = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; k++) a.dL_drot[4 * (size_t)idx + k] = 0.f;
+      }
+      continue;
+    }
     const float mx = a.means3D[3 * (size_t)idx], my = a.means3D[3 * (size_t)idx + 1], mz = a.means3D[3 * (size_t)idx + 2];
     float c6[6];
 #pragma unroll
     for (int k = 0; k < 6; k++) c6[k] = cov3Ds[6 * (size_t)idx + k];
-    const float4 dcon4 = *reinterpret_cast<const float4*>(a.dL_dconic + 4 * (size_t)idx);
-    const float dcx = dcon4.x, dcy = dcon4.y, dcz = dcon4.w;
+    // blend_bwd_kernel left RAW MOMENTS of g = G * dL/dalpha over the blended (pixel, Gaussian) pairs: sum g dx, g dy, g dx^2,
+    // g dx dy, g dy^2, g and the colour gradient.  With the Gaussian's conic and opacity they become the sums of
+    // backward.cu:536-549: dL_dmean2D = -ddel * o * (conic * m1), dL_dconic = -0.5 * o * m2, dL_dopacity = sum g.
+    const float4 rb = reinterpret_cast<const float4*>(recs + idx)[1];  // conic a, b, c, opacity
+    const float m1x = ac0.x, m1y = ac0.y;
+    const float g2x = -(0.5f * a.width) * rb.w * (rb.x * m1x + rb.y * m1y);
+    const float g2y = -(0.5f * a.height) * rb.w * (rb.z * m1y + rb.y * m1x);
+    a.dL_dmean2D[3 * (size_t)idx] = g2x;
+    a.dL_dmean2D[3 * (size_t)idx + 1] = g2y;
+    a.dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
+    const float dcx = -0.5f * rb.w * ac0.z, dcy = -0.5f * rb.w * ac0.w, dcz = -0.5f * rb.w * ac1.x;
+    if (a.dL_dconic) *reinterpret_cast<float4*>(a.dL_dconic + 4 * (size_t)idx) = make_float4(dcx, dcy, 0.f, dcz);  // optional output
+    a.dL_dopacity[idx] = ac1.y;
+    const float dcol[3] = {ac1.z, ac1.w, ac2.x};
+#pragma unroll
+    for (int k = 0; k < 3; k++) a.dL_dcolor[3 * (size_t)idx + k] = dcol[k];
     // ---- computeCov2DCUDA ----
     float tx = view[0] * mx + view[4] * my + view[8] * mz + view[12];
     float ty = view[1] * mx + view[5] * my + view[9] * mz + view[13];
@@ -186,13 +221,12 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(GsBackwardArgs a, c
     const float m_w = 1.0f / (m_hw + 0.0000001f);
     const float mul1 = (proj[0] * mx + proj[4] * my + proj[8] * mz + proj[12]) * m_w * m_w;
     const float mul2 = (proj[1] * mx + proj[5] * my + proj[9] * mz + proj[13]) * m_w * m_w;
-    const float g2x = a.dL_dmean2D[3 * (size_t)idx], g2y = a.dL_dmean2D[3 * (size_t)idx + 1];
     dmx += (proj[0] * m_w - proj[3] * mul1) * g2x + (proj[1] * m_w - proj[3] * mul2) * g2y;
     dmy += (proj[4] * m_w - proj[7] * mul1) * g2x + (proj[5] * m_w - proj[7] * mul2) * g2y;
     dmz += (proj[8] * m_w - proj[11] * mul1) * g2x + (proj[9] * m_w - proj[11] * mul2) * g2y;
     if (a.shs) {
       F3 r = sh_backward(a.D, {mx, my, mz}, {s_cam[0], s_cam[1], s_cam[2]}, a.shs + (size_t)idx * a.M * 3,
-                         clamped + 3 * (size_t)idx, a.dL_dcolor + 3 * (size_t)idx, a.dL_dsh + (size_t)idx * a.M * 3);
+                         clamped + 3 * (size_t)idx, dcol, a.dL_dsh + (size_t)idx * a.M * 3);
       dmx += r.x; dmy += r.y; dmz += r.z;
     }
     a.dL_dmean3D[3 * (size_t)idx] = dmx;
@@ -210,6 +244,6 @@ int gs_launch_preprocess_bwd(const GsBackwardArgs& a, const GsGeom& g, cudaStrea
   int blocks = (a.P + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
   const float* cov = a.cov3D_precomp ? a.cov3D_precomp : g.cov3D;
-  gs_launch(preprocess_bwd_kernel, dim3(blocks), dim3(256), 0, st, a, cov, g.clamped);
+  gs_launch(preprocess_bwd_kernel, dim3(blocks), dim3(256), 0, st, a, cov, g.clamped, (const GsRec*)g.rec, g.acc);
   return gs_check(cudaGetLastError());
 }

@@ -4,8 +4,10 @@
 // sort key, radius, tile rectangle, blend skip / termination tests) is written with explicit
 // __fmaf_rn/__fmul_rn/__fadd_rn intrinsics (which the compiler never re-associates or re-contracts) in
 // the order nvcc emits for the reference kernels (cuda_rasterizer/forward.cu, auxiliary.h), so the
-// integer artefacts are bit-identical to the reference build and to the CPU oracle.  exp() in the blend is
-// gs_exp(): a fixed FMA polynomial, bit-reproducible on CPU and GPU.
+// integer artefacts are bit-identical to the reference build and to the CPU oracle.  exp() in the blend is CUDA's expf --
+// the instruction sequence nvcc emits for the reference's `exp(power)` (forward.cu:344, backward.cu:483), so that the
+// alpha >= 1/255 and T < 1e-4 decisions are the reference's bit for bit -- or, in oracle mode (gs_set_exp_mode(1)),
+// gs_exp(): a fixed FMA polynomial that the CPU oracle reproduces bit for bit.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -17,13 +19,22 @@
 #ifndef GS_SEG
 #define GS_SEG 128          // list entries per backward work item = spacing of the forward's per-pixel checkpoints
 #endif
+#ifndef GS_FWD_CHUNK
+#define GS_FWD_CHUNK 256    // list entries per forward work item (tile, pixel block, chunk): a multiple of GS_SEG.  Measured at
+#endif                      // cfg-A: 256 entries / 4 warps / 5 CTAs per SM 78 us, 512 / 8 warps / 3 CTAs 88 us (profiles/r2)
+#define GS_FWD_NCH_BINS 2048  // plan_kernel sorts tiles by chunk count with a counting sort of this many bins
+#define GS_HAND_WORDS (32 * 6)  // hand-off slot of one (tile, pixel block, chunk): 32 lanes x {T, C0, C1, C2} + {last|flags, C3}
 
 // ---- workspace layouts (private; reached from outside only through gs_debug_read) ----
 struct GsHeader {            // first 256 bytes of the geom workspace
   unsigned long long num_rendered;  // N, written by the emit kernel
   unsigned int overflow;            // N > pair_capacity
   unsigned int error;               // look-back spin limit hit etc.
-  unsigned int pad[60];
+  unsigned long long evals_blended; // E_bwd: (pixel, entry) pairs the forward blended (counted by the forward's chain warps)
+  unsigned int n_fitems;            // forward work items (tile, chunk) of the non-empty tiles, written by plan_kernel
+  unsigned int n_empty_tiles;       // ... followed by this many single items of the empty tiles
+  unsigned int fwd_ticket;          // next work unit of the persistent forward blend
+  unsigned int pad[55];
 };
 
 // One packed record per Gaussian, what both blend kernels gather per list entry (3 x LDG.128).
@@ -40,14 +51,17 @@ struct GsGeom {
   uint32_t* tiles_touched;  // [P]
   float* cov3D;             // [P*6]  (only written when computed from scales/rotations)
   uint8_t* clamped;         // [P*3]  (SH path)
+  float* acc;               // [P*12] accumulators of the backward blend, one 48-byte record per Gaussian: raw moments sum g dx,
+                            // g dy, g dx^2, g dx dy, g dy^2, g (g = G * dL/dalpha), colour gradient r, g, b, 3 pad.  Zeroed by
+                            // preprocess_kernel (forward) and again by preprocess_bwd_kernel after it has consumed them
 };
+#define GS_ACC 12
 
 struct GsImage {
   uint2* ranges;            // [tiles]
   uint32_t* n_contrib;      // [H*W]
   float* final_T;           // [H*W]
   uint32_t* seg_off;        // [tiles+1] exclusive prefix of ceil(len/GS_SEG) over tiles; [tiles] = number of work items
-  uint32_t* order;          // [tiles] tile ids, longest lists first (launch order of the forward blend)
 };
 
 // The pair-capacity-sized workspace kept for backward (the reference's binningBuffer).
@@ -56,9 +70,11 @@ struct GsList {
   uint2* items;             // [max_items] (tile, segment) work items of the backward blend
   float4* ckpt;             // [(max_items + tiles) * 256] per-pixel (T, C.rgb) at every segment start + final state
   float* ckpt_op;           // same slots: accumulated opacity channel (written only by the fused opacity pass)
-  uint32_t* rowmask;        // [max_items][8 pixel blocks][GS_SEG / 32] per 32-entry batch: entries at least one pixel of
-                            // the block blended in the forward pass (what the backward blend visits)
-  size_t max_items;
+  uint32_t* rowmask;        // [max_items][8 pixel blocks][GS_SEG / 32][2 strips] per 32-entry batch and 8x2 pixel strip: entries at
+                            // least one pixel of the strip blended in the forward pass (what the backward blend visits)
+  uint4* fitems;            // [max_fitems] forward work items (tile, chunk, index of the successor item or ~0, index of the
+                            // predecessor item or ~0), longest remaining chain first: a predecessor always has a smaller index
+  size_t max_items, max_fitems;
 };
 
 struct GsScratch {
@@ -74,12 +90,10 @@ struct GsScratch {
   uint32_t* status_t;       // [4][blocks_t][256] onesweep look-back status, tile passes
   unsigned long long* scan_status;  // [blocks_e] emit-kernel look-back
   uint32_t* tile_total;     // [tiles] pairs per tile (direct placement)
+  uint32_t* hand;           // [cap / GS_FWD_CHUNK][8 pixel blocks][GS_HAND_WORDS] chain state handed from chunk c to chunk c+1 of
+                            // a tile's forward blend; 0 = not yet published (validity is embedded in the vectors)
   uint32_t* zero_end;
   size_t blocks_d, blocks_t, blocks_e;
-  // ---- alpha rows of the two-kernel forward blend (not zeroed; NULL when over GS_ROWS_BUDGET) ----
-  float* rows_alpha;        // [batches][32 rows][32 pixels]
-  float4* rows_data;        // [batches][32 rows] r, g, b, 1-based list position
-  uint8_t* rows_cnt;        // [batches] rows of the batch; batches = max_items * 8 blocks * (GS_SEG / 32)
 };
 
 static inline __host__ __device__ size_t gs_align_up(size_t v) { return (v + GS_ALIGN - 1) / GS_ALIGN * GS_ALIGN; }
@@ -99,6 +113,7 @@ static inline __host__ size_t gs_carve_geom(char* base, int P, GsGeom* g) {
   gs_carve(p, t.tiles_touched, (size_t)P);
   gs_carve(p, t.cov3D, (size_t)P * 6);
   gs_carve(p, t.clamped, (size_t)P * 3);
+  gs_carve(p, t.acc, (size_t)P * GS_ACC);
   if (g) *g = t;
   return (size_t)(p - base);
 }
@@ -111,7 +126,6 @@ static inline __host__ size_t gs_carve_image(char* base, int W, int H, GsImage* 
   gs_carve(p, t.n_contrib, (size_t)W * H);
   gs_carve(p, t.final_T, (size_t)W * H);
   gs_carve(p, t.seg_off, tiles + 1);
-  gs_carve(p, t.order, tiles);
   if (im) *im = t;
   return (size_t)(p - base);
 }
@@ -121,11 +135,13 @@ static inline __host__ size_t gs_carve_list(char* base, int64_t cap, int W, int 
   GsList t;
   size_t tiles = (size_t)((W + GS_TILE - 1) / GS_TILE) * ((H + GS_TILE - 1) / GS_TILE);
   t.max_items = (size_t)cap / GS_SEG + tiles;  // sum over tiles of ceil(len/GS_SEG) <= N/GS_SEG + tiles
+  t.max_fitems = (size_t)cap / GS_FWD_CHUNK + tiles;  // sum over tiles of max(1, ceil(len/GS_FWD_CHUNK))
   gs_carve(p, t.point_list, (size_t)cap);
   gs_carve(p, t.items, t.max_items);
   gs_carve(p, t.ckpt, (t.max_items + tiles) * 256);
   gs_carve(p, t.ckpt_op, (t.max_items + tiles) * 256);
-  gs_carve(p, t.rowmask, t.max_items * 8 * (GS_SEG / 32));
+  gs_carve(p, t.rowmask, t.max_items * 8 * (2 * GS_SEG / 32));
+  gs_carve(p, t.fitems, t.max_fitems);
   if (l) *l = t;
   return (size_t)(p - base);
 }
@@ -146,18 +162,6 @@ static inline __host__ __device__ int gs_sort_items(unsigned long long n) { retu
 static inline __host__ size_t gs_sort_blocks(unsigned long long n) {
   const size_t tile = (size_t)gs_sort_items(n) * GS_SORT_THREADS;
   return ((size_t)n + tile - 1) / tile;
-}
-
-// Two-kernel forward blend (opt-in experiment, measured slower than the one-kernel producer/consumer blend: DESIGN.md 4.3):
-// (tile, 32-entry batch, pixel block) row slots at fixed offsets, carved only when enabled and while the worst-case row
-// storage stays under the budget.
-#define GS_ROWS_BUDGET ((size_t)1 << 30)
-bool gs_fwd_two_kernel_enabled();  // gs_api.cu: GS_FWD_TWO_KERNEL=1 in the environment (read once); default off, see DESIGN.md 4.3
-static inline __host__ size_t gs_rows_batches(int64_t cap, int W, int H) {
-  if (!gs_fwd_two_kernel_enabled()) return 0;
-  const size_t tiles = (size_t)((W + GS_TILE - 1) / GS_TILE) * ((H + GS_TILE - 1) / GS_TILE);
-  const size_t batches = ((size_t)cap / GS_SEG + tiles) * 8 * (GS_SEG / 32);
-  return batches * 32 * 144 <= GS_ROWS_BUDGET ? batches : 0;
 }
 
 // Direct placement needs the [blocks][tiles] count matrix to fit the pair-sized scratch it borrows.
@@ -183,14 +187,8 @@ static inline __host__ size_t gs_carve_scratch(char* base, int P, int W, int H, 
   gs_carve(p, t.status_t, 4 * t.blocks_t * 256);
   gs_carve(p, t.scan_status, t.blocks_e);
   gs_carve(p, t.tile_total, (size_t)((W + GS_TILE - 1) / GS_TILE) * ((H + GS_TILE - 1) / GS_TILE));
+  gs_carve(p, t.hand, ((size_t)cap / GS_FWD_CHUNK + 1) * 8 * GS_HAND_WORDS);
   t.zero_end = reinterpret_cast<uint32_t*>(p);
-  const size_t rb = gs_rows_batches(cap, W, H);
-  t.rows_alpha = nullptr; t.rows_data = nullptr; t.rows_cnt = nullptr;
-  if (rb) {
-    gs_carve(p, t.rows_alpha, rb * 32 * 32);
-    gs_carve(p, t.rows_data, rb * 32);
-    gs_carve(p, t.rows_cnt, rb);
-  }
   if (s) *s = t;
   return (size_t)(p - base);
 }
@@ -255,8 +253,9 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
                       int64_t cap, cudaStream_t st);
 int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, const GsScratch& s,
                         cudaStream_t st);
+int gs_exp_mode();  // gs_api.cu: 0 = CUDA expf (the reference's instruction sequence, default), 1 = gs_exp polynomial (oracle mode)
 int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, cudaStream_t st);
-int gs_launch_preprocess_bwd(const GsBackwardArgs& a, const GsGeom& g, cudaStream_t st);
+int gs_launch_preprocess_bwd(const GsBackwardArgs& a, const GsGeom& g, cudaStream_t st);  // also finishes the blend's raw moments
 int gs_launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 int gs_check(cudaError_t e);
 void gs_prof_mark(int stage, int end, cudaStream_t st);  // stages: see gs_api.cu (5 = pose fwd, 6 = pose bwd)

@@ -134,6 +134,10 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsForwardArgs a, GsGeom
     uint32_t key = 0xFFFFFFFFu;
     int radius = 0;
     uint32_t touched = 0;
+    {  // accumulators of the backward blend start at zero (no separate fill launch)
+      float4* const ac = reinterpret_cast<float4*>(g.acc + (size_t)GS_ACC * idx);
+      ac[0] = ac[1] = ac[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     const float mx = a.means3D[3 * idx], my = a.means3D[3 * idx + 1], mz = a.means3D[3 * idx + 2];
     const float pvz = gs_dot3p(mx, v[2], my, v[6], mz, v[10], v[14]);
     if (pvz > 0.2f) {  // auxiliary.h:154

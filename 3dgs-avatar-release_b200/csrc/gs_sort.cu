@@ -518,64 +518,109 @@ __global__ void tile_ranges_kernel(const uint32_t* __restrict__ tkey_sorted, con
   }
 }
 
-// Work plan of the backward blend: every tile list is cut into segments of GS_SEG entries; seg_off = exclusive prefix
-// of the segment counts over tiles (seg_off[tiles] = number of items), items[] = (tile, segment).  One CTA.
+// Work plans of the two blend kernels.  One CTA.
+//  * backward: every tile list is cut into segments of GS_SEG entries; seg_off = exclusive prefix of the segment counts over
+//    tiles (seg_off[tiles] = number of items), items[] = (tile, segment);
+//  * forward: every non-empty tile list is cut into chunks of GS_FWD_CHUNK entries; fitems[] = (tile, chunk, index of the
+//    successor item, index of the predecessor item), ordered by the number of chunks that REMAIN in the tile's chain
+//    (this one included), longest first -- "longest remaining path first": the deep tiles, whose chains are the critical path
+//    of avatar frames, start at once, every last chunk comes at the end, and an item's predecessor (one more remaining)
+//    always has a smaller index: CTAs are dispatched in index order, which makes the hand-off wait of blend_fwd_kernel
+//    deadlock-free.  With nch(t) = chunks of tile t, pos(t) = rank of t in descending nch order (counting sort),
+//    ge[k] = #tiles with nch > k and base = exclusive prefix of ge, item (t, c) with r = nch - c remaining sits at
+//    n_fitems - base[r] + pos(t).  The empty tiles follow as one item each (their pixels still get the background).
+__device__ __forceinline__ uint32_t block_scan_incl_1024(uint32_t v, uint32_t* s_w, uint32_t* total) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint32_t incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  __syncthreads();  // s_w may still be read from the previous scan
+  if (lane == 31) s_w[w] = incl;
+  __syncthreads();
+  uint32_t wv = s_w[lane], wincl = wv;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xFFFFFFFFu, wincl, o);
+    if (lane >= o) wincl += t;
+  }
+  *total = __shfl_sync(0xFFFFFFFFu, wincl, 31);
+  return incl + __shfl_sync(0xFFFFFFFFu, wincl - wv, w);
+}
+
 __global__ void __launch_bounds__(1024)
 plan_kernel(int tiles, const uint2* __restrict__ ranges, uint32_t* __restrict__ seg_off, uint2* __restrict__ items,
-            uint32_t max_items, uint32_t* __restrict__ order) {
+            uint32_t max_items, uint4* __restrict__ fitems, uint32_t max_fitems, GsHeader* __restrict__ hdr) {
   GS_PDL_PROLOGUE();
   __shared__ uint32_t s_w[32];
-  __shared__ uint32_t s_carry;
-  __shared__ uint32_t s_bucket[33], s_cursor[33];
-  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  if (tid == 0) s_carry = 0;
-  if (tid < 33) s_bucket[tid] = 0;
+  __shared__ uint32_t s_hist[GS_FWD_NCH_BINS];  // tiles per chunk count -> cursor of the counting sort
+  __shared__ uint32_t s_base[GS_FWD_NCH_BINS];  // base[r] = sum over k < r of ge[k]
+  __shared__ uint32_t s_total, s_nonempty;
+  const int tid = threadIdx.x;
+  for (int k = tid; k < GS_FWD_NCH_BINS; k += 1024) s_hist[k] = 0;
   __syncthreads();
+  uint32_t carry = 0;
   for (int t0 = 0; t0 < tiles; t0 += 1024) {
     const int t = t0 + tid;
     uint32_t nseg = 0;
     if (t < tiles) {
-      uint2 r = ranges[t];
-      nseg = (r.y - r.x + GS_SEG - 1) / GS_SEG;
-      atomicAdd(&s_bucket[32 - __clz(r.y - r.x)], 1u);  // length class = bit length of the list length
+      const uint2 r = ranges[t];
+      const uint32_t len = r.y - r.x;
+      nseg = (len + GS_SEG - 1) / GS_SEG;
+      atomicAdd(&s_hist[min((len + GS_FWD_CHUNK - 1) / GS_FWD_CHUNK, (uint32_t)GS_FWD_NCH_BINS - 1)], 1u);
     }
-    uint32_t incl = nseg;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-      if (lane >= o) incl += v;
-    }
-    if (lane == 31) s_w[w] = incl;
-    __syncthreads();
-    uint32_t wv = s_w[lane], wincl = wv;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      uint32_t v = __shfl_up_sync(0xFFFFFFFFu, wincl, o);
-      if (lane >= o) wincl += v;
-    }
-    const uint32_t wpre = __shfl_sync(0xFFFFFFFFu, wincl - wv, w);
-    const uint32_t total = __shfl_sync(0xFFFFFFFFu, wincl, 31);
-    const uint32_t off = s_carry + wpre + incl - nseg;
+    uint32_t total;
+    const uint32_t off = carry + block_scan_incl_1024(nseg, s_w, &total) - nseg;
     if (t < tiles) {
       seg_off[t] = off;
       for (uint32_t k = 0; k < nseg; k++)
         if (off + k < max_items) items[off + k] = make_uint2((uint32_t)t, k);
     }
-    __syncthreads();
-    if (tid == 0) s_carry += total;
-    __syncthreads();
+    carry += total;
   }
-  if (tid == 0) seg_off[tiles] = s_carry < max_items ? s_carry : max_items;
-  // launch order of the forward blend: longest lists first (bucketed by bit length), so that the deep tiles -- the
-  // critical path of avatar frames -- start in the first wave
-  if (tid == 0) {
-    uint32_t run = 0;
-    for (int bk = 32; bk >= 0; bk--) { s_cursor[bk] = run; run += s_bucket[bk]; }
+  if (tid == 0) seg_off[tiles] = carry < max_items ? carry : max_items;
+  __syncthreads();
+  // ge[k] = #tiles with chunk count > k = tiles - inclusive prefix of hist; base = exclusive prefix of ge.
+  // Two elements per thread (GS_FWD_NCH_BINS = 2 * 1024).
+  static_assert(GS_FWD_NCH_BINS == 2048, "two bins per thread");
+  {
+    const uint32_t h0 = s_hist[2 * tid], h1 = s_hist[2 * tid + 1];
+    uint32_t total;
+    const uint32_t incl = block_scan_incl_1024(h0 + h1, s_w, &total);
+    const uint32_t ge0 = (uint32_t)tiles - (incl - h1), ge1 = (uint32_t)tiles - incl;
+    uint32_t total2;
+    const uint32_t incl2 = block_scan_incl_1024(ge0 + ge1, s_w, &total2);
+    __syncthreads();
+    s_hist[2 * tid] = ge0; s_hist[2 * tid + 1] = ge1;                          // cursor: tiles with a larger chunk count come first
+    s_base[2 * tid] = incl2 - ge0 - ge1; s_base[2 * tid + 1] = incl2 - ge1;
+    if (tid == 0) {
+      s_total = total2;                                                        // items of the non-empty tiles
+      hdr->n_fitems = total2 < max_fitems ? total2 : max_fitems;
+      s_nonempty = ge0;                                                        // ge[0]
+      hdr->n_empty_tiles = h0;                                                 // hist[0]
+    }
   }
   __syncthreads();
+  const uint32_t n_items = s_total, n_nonempty = s_nonempty;
   for (int t = tid; t < tiles; t += 1024) {
-    uint2 r = ranges[t];
-    order[atomicAdd(&s_cursor[32 - __clz(r.y - r.x)], 1u)] = (uint32_t)t;
+    const uint2 r = ranges[t];
+    const uint32_t len = r.y - r.x;
+    const uint32_t nch = min((len + GS_FWD_CHUNK - 1) / GS_FWD_CHUNK, (uint32_t)GS_FWD_NCH_BINS - 1);
+    const uint32_t pos = atomicAdd(&s_hist[nch], 1u);
+    if (nch == 0) {  // empty tile: one item behind everything else
+      const uint32_t fi = n_items + (pos - n_nonempty);
+      if (fi < max_fitems) fitems[fi] = make_uint4((uint32_t)t, 0u, 0xFFFFFFFFu, 0xFFFFFFFFu);
+      continue;
+    }
+    for (uint32_t c = 0; c < nch; c++) {
+      const uint32_t rem = nch - c;  // chunks remaining in this tile's chain, this one included
+      const uint32_t fi = n_items - s_base[rem] + pos;
+      if (fi < max_fitems)
+        fitems[fi] = make_uint4((uint32_t)t, c, rem > 1 ? n_items - s_base[rem - 1] + pos : 0xFFFFFFFFu,
+                                c > 0 ? n_items - s_base[rem + 1] + pos : 0xFFFFFFFFu);
+    }
   }
 }
 
@@ -664,6 +709,7 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
               (const unsigned long long*)&g.hdr->num_rendered, (unsigned long long)cap, im.ranges);
   }
   // 5. backward work plan (segments of GS_SEG entries per tile)
-  gs_launch(plan_kernel, dim3(1), dim3(1024), 0, st, tiles, im.ranges, im.seg_off, l.items, (uint32_t)l.max_items, im.order);
+  gs_launch(plan_kernel, dim3(1), dim3(1024), 0, st, tiles, im.ranges, im.seg_off, l.items, (uint32_t)l.max_items, l.fitems,
+            (uint32_t)l.max_fitems, g.hdr);
   return gs_check(cudaGetLastError());
 }

@@ -23,7 +23,7 @@ import time
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libgsplat_b200.so")
+_LIB_PATH = os.environ.get("GS_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libgsplat_b200.so")  # GS_LIB: experiment builds
 
 c_float_p = ctypes.c_void_p
 
@@ -85,6 +85,10 @@ def lib():
         L.gs_read_num_rendered.argtypes = [vp, vp, vp]
         L.gs_debug_read.restype = ctypes.c_int
         L.gs_debug_read.argtypes = [ctypes.c_int32, ctypes.POINTER(GsForwardArgs), vp, vp, vp, ctypes.c_int64, vp, sz, vp]
+        L.gs_set_exp_mode.restype = ctypes.c_int
+        L.gs_set_exp_mode.argtypes = [ctypes.c_int]
+        L.gs_read_counters.restype = ctypes.c_int
+        L.gs_read_counters.argtypes = [vp, vp, vp]
         L.gs_last_cuda_error.restype = ctypes.c_int
         L.gs_version.restype = ctypes.c_char_p
         _lib = L
@@ -242,6 +246,21 @@ def _forward(bg, means3D, colors, opacity, scales, rotations, scale_modifier, co
         return N, out_color, radii, geom, lst, img
 
 
+def set_exp_mode(mode):
+    """0: CUDA expf = the reference's instruction sequence (default); 1: the polynomial the CPU oracle reproduces bit for bit
+    (include/gsplat_b200.h: gs_set_exp_mode).  Returns the previous mode."""
+    return int(lib().gs_set_exp_mode(int(mode)))
+
+
+def read_counters(geomBuffer):
+    """(E_bwd, forward work items) of the forward call that filled `geomBuffer` (synchronises the current stream)."""
+    buf = (ctypes.c_uint64 * 2)()
+    with torch.cuda.device(geomBuffer.device):
+        _check(lib().gs_read_counters(geomBuffer.data_ptr(), ctypes.cast(buf, ctypes.c_void_p),
+                                      torch.cuda.current_stream(geomBuffer.device).cuda_stream), "gs_read_counters")
+    return int(buf[0]), int(buf[1])
+
+
 def release_cached():
     """Drops the per-device scratch caches (sort scratch, graph keep-alives, pinned words).  For an orderly shutdown: call
     after the CUDA graphs that captured rasterize_gaussians have been released."""
@@ -278,17 +297,18 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, scales, rotations, 
     dev = means3D.device
     M = int(sh.size(1)) if (sh is not None and sh.numel() != 0) else 0
     with torch.cuda.device(dev):
-        # one zero-filled slab carved into the 9 gradient tensors of rasterize_points.cu:151-159
-        sizes = [3, 3, 3, 4, 1, 6, 3 * M, 3, 4]  # means3D, means2D, colors, conic, opacity, cov3D, sh, scales, rot
-        pad4 = lambda n: (n + 3) // 4 * 4  # every part 16-byte aligned (the kernels read dL_dconic as float4) for any P
-        flat = torch.zeros(sum(pad4(P * s) for s in sizes), dtype=torch.float32, device=dev)
+        # one slab carved into the 8 gradient tensors of rasterize_points.cu:151-159 (dL_dconic stays inside the library).  NOT
+        # zero-filled: gs_backward writes every element of every output (culled Gaussians get explicit zeros)
+        sizes = [3, 3, 3, 1, 6, 3 * M, 3, 4]  # means3D, means2D, colors, opacity, cov3D, sh, scales, rot
+        pad4 = lambda n: (n + 3) // 4 * 4  # every part 16-byte aligned for any P
+        flat = torch.empty(sum(pad4(P * s) for s in sizes), dtype=torch.float32, device=dev)
         parts, off = [], 0
         for s in sizes:
             parts.append(flat[off:off + P * s])
             off += pad4(P * s)
-        dmeans3D, dmeans2D, dcolors, dconic, dopacity, dcov3D, dsh, dscales, drot = parts
+        dmeans3D, dmeans2D, dcolors, dopacity, dcov3D, dsh, dscales, drot = parts
         dmeans3D, dmeans2D, dcolors = dmeans3D.view(P, 3), dmeans2D.view(P, 3), dcolors.view(P, 3)
-        dconic, dopacity, dcov3D = dconic.view(P, 2, 2), dopacity.view(P, 1), dcov3D.view(P, 6)
+        dopacity, dcov3D = dopacity.view(P, 1), dcov3D.view(P, 6)
         dsh, dscales, drot = dsh.view(P, M, 3), dscales.view(P, 3), drot.view(P, 4)
         if P == 0:
             return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot
@@ -300,7 +320,7 @@ def rasterize_gaussians_backward(bg, means3D, radii, colors, scales, rotations, 
                            _ptr(colors, "colors_precomp"), _ptr(scales, "scales"), _ptr(rotations, "rotations"),
                            _ptr(cov3D_precomp, "cov3D_precomp"), _ptr(viewmatrix, "viewmatrix"),
                            _ptr(projmatrix, "projmatrix"), _ptr(campos, "campos"), _ptr(radii, "radii", torch.int32),
-                           _ptr(dL, "dL_dout_color"), dmeans2D.data_ptr(), dconic.data_ptr(), dopacity.data_ptr(),
+                           _ptr(dL, "dL_dout_color"), dmeans2D.data_ptr(), None, dopacity.data_ptr(),
                            dcolors.data_ptr(), dmeans3D.data_ptr(), dcov3D.data_ptr(),
                            dsh.data_ptr() if M else None, dscales.data_ptr(), drot.data_ptr(),
                            _ptr(dLo, "dL_dout_opacity"))

@@ -89,9 +89,11 @@ typedef struct GsBackwardArgs {
   const float* campos;
   const int32_t* radii;
   const float* dL_dpix;  /* [3,H,W] */
-  /* outputs; every one must be zero-filled by the caller (rasterize_points.cu:151-159) */
-  float* dL_dmean2D;     /* [P,3]  (.z stays 0) */
-  float* dL_dconic;      /* [P,4]  (2x2; .z never written) */
+  /* outputs: gs_backward writes EVERY element (culled Gaussians get explicit zeros), so the caller need not zero-fill them
+   * as rasterize_points.cu:151-159 does.  The per-pixel sums are accumulated in a 48-byte record per Gaussian inside the geom
+   * workspace, which the forward zeroes and the backward zeroes again after use. */
+  float* dL_dmean2D;     /* [P,3]  (.z = 0) */
+  float* dL_dconic;      /* [P,4]  (2x2; .z = 0) optional: NULL when the caller does not need it (the reference keeps it internal) */
   float* dL_dopacity;    /* [P] */
   float* dL_dcolor;      /* [P,3] */
   float* dL_dmean3D;     /* [P,3] */
@@ -374,6 +376,18 @@ int l1_loss_backward(const float* dL_dimage_unit, const float* dL_dloss, int64_t
 void gs_profile_enable(int on);
 int gs_profile_read(float* ms_host /* [7]: preprocess, binning, blend fwd, blend bwd, preprocess bwd, pose fwd, pose bwd */);
 int gs_fma_probe(int blocks, int threads, int iters, float* out_dev, void* stream);
+
+/* exp() of the blend kernels (cuda_rasterizer/forward.cu:344 `exp(power)`, backward.cu:483).  mode 0 (default): CUDA's expf,
+ * the instruction sequence nvcc emits for the reference, so that the alpha >= 1/255 and T < 1e-4 decisions -- n_contrib -- are
+ * the reference build's bit for bit.  mode 1 ("oracle mode"): a fixed FMA polynomial (<= 1 ulp) that oracle/gs_oracle.c
+ * reproduces bit for bit on the CPU, used by the parity tests that compare integer artefacts AND image bits with the
+ * oracle.  Process-wide; returns the previous mode.  GS_EXP_MODE=1 in the environment selects mode 1 initially. */
+int gs_set_exp_mode(int mode);
+/* counters_host[0] = number of (pixel, entry) pairs blended in the frame of `geom` (E_bwd of SURVEY.md 8(d)), counted by
+ * gs_backward -- the one word of the forward's workspaces the backward writes: it adds to this profiling counter in the
+ * header, so the value is E_bwd times the number of backward calls since the forward;
+ * counters_host[1] = forward work items (tile, 512-entry chunk) of that frame.  Synchronises `stream`. */
+int gs_read_counters(const void* geom, uint64_t* counters_host, void* stream);
 
 /* sizeof of the ABI structs: 0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs,
  * 6 ColorArgs, 7 AdamArgs, 8 PoseEncoderArgs, 9 SlabAllReduceArgs */

@@ -22,6 +22,15 @@ def _dev():
     return torch.device("cuda:0")
 
 
+@pytest.fixture(autouse=True)
+def oracle_exp_mode(built_lib):
+    """Bit-exact comparisons with the CPU oracle: the blend runs with the polynomial exp the oracle reproduces."""
+    from diff_gaussian_rasterization import _C
+    prev = _C.set_exp_mode(1)
+    yield
+    _C.set_exp_mode(prev)
+
+
 def rel_err(a, b):
     scale = max(float(np.abs(b).max()), 1e-30)
     return float(np.abs(a.astype(np.float64) - b.astype(np.float64)).max()) / scale
