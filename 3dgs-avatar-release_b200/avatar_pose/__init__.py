@@ -27,7 +27,7 @@ class PoseArgs(ctypes.Structure):
 class PoseBackwardArgs(ctypes.Structure):
     _fields_ = [("fwd", PoseArgs), ("dL_dmeans3D", vp), ("dL_dcov3D", vp), ("dL_dcolors", vp), ("dL_dopacity", vp),
                 ("dL_dxyz", vp), ("dL_drotation", vp), ("dL_dscaling", vp), ("dL_dopacity_logit", vp),
-                ("dL_dfeatures_dc", vp), ("dL_dfeatures_rest", vp), ("dL_dweights", vp)]
+                ("dL_dfeatures_dc", vp), ("dL_dfeatures_rest", vp), ("dL_dweights", vp), ("dL_dbone_transforms", vp)]
 
 
 _configured = False
@@ -106,6 +106,7 @@ class _FusedPose(torch.autograd.Function):
         ctx.save_for_backward(xyz_, rot_, sc_, op_, dc_, rest_, w_, b_, cam_)
         ctx.cfg = (int(sh_degree), float(mod), bool(cano))
         ctx.need_w = weights.requires_grad
+        ctx.need_b = bones.requires_grad
         if want_aux:
             ctx.mark_non_differentiable(T_fwd, Rbar)
             return means, cov, colors, opac, T_fwd, Rbar
@@ -145,11 +146,13 @@ class _FusedPose(torch.autograd.Function):
             ba.dL_dfeatures_dc = gdc.data_ptr()
             ba.dL_dfeatures_rest = grest.data_ptr() if nrest else None
             ba.dL_dweights = gw.data_ptr() if gw is not None else None
+            gb = torch.empty(24, 4, 4, **f32) if ctx.need_b else None
+            ba.dL_dbone_transforms = gb.data_ptr() if gb is not None else None
             if P:
                 _gs._check(L.pose_backward(ctypes.byref(ba), torch.cuda.current_stream(dev).cuda_stream), "pose_backward")
         _last_slab[0] = flat
         gop = gop.view(op.shape)
-        return gxyz, grot, gsc, gop, gdc, grest, gw, None, None, None, None, None, None
+        return gxyz, grot, gsc, gop, gdc, grest, gw, (gb.view(b.shape) if gb is not None else None), None, None, None, None, None
 
 
 def fused_pose(xyz, rotation, scaling, opacity, features_dc, features_rest, weights, bone_transforms, camera_center,
@@ -158,6 +161,7 @@ def fused_pose(xyz, rotation, scaling, opacity, features_dc, features_rest, weig
 
     Inputs are the raw GaussianModel parameters (`_xyz`, `_rotation`, `_scaling`, `_opacity`, `_features_dc`,
     `_features_rest`), per-Gaussian skinning weights [P,24], `camera.bone_transforms` [24,4,4] and
-    `camera.camera_center` [3].  Gradients flow to the six parameter tensors and to `weights`."""
+    `camera.camera_center` [3].  Gradients flow to the six parameter tensors, to `weights` and to `bone_transforms` (the route by
+    which the image loss reaches a per-frame pose correction, rigid.py:215-236)."""
     return _FusedPose.apply(xyz, rotation, scaling, opacity, features_dc, features_rest, weights, bone_transforms,
                             camera_center, sh_degree, scaling_modifier, cano_view_dir, return_aux)

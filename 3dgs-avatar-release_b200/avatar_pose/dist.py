@@ -49,10 +49,11 @@ class SymmetricGradSlab:
         loss.backward(); slab.all_reduce()            # one kernel; capturable in the step's CUDA graph
 
     `buf` is padded to a multiple of 4 * world floats (pad stays zero).  Construction raises where symmetric memory or the
-    NVLS multicast object is unavailable (the caller then keeps using allreduce_gradients = NCCL); the peer-to-peer variant of
-    the kernel is opt-in (`allow_p2p=True`): it has not been exercised on hardware without multicast support."""
+    NVLS multicast object is unavailable (the caller then keeps using allreduce_gradients = NCCL).  A cross-rank barrier that
+    never completes (a dead or very late peer) leaves the slab untouched and sets an error word; `all_reduce()` surfaces it
+    lazily on the NEXT call (no synchronisation on the hot path) and `check()` after a synchronisation."""
 
-    def __init__(self, n, group=None, blocks=32, use_multicast=True, allow_p2p=False):
+    def __init__(self, n, group=None, blocks=32):
         import ctypes
         import torch.distributed._symmetric_memory as symm
         from diff_gaussian_rasterization import _C as _gs
@@ -68,14 +69,13 @@ class SymmetricGradSlab:
         self.buf = symm.empty(self.n, dtype=torch.float32, device=dev)
         self.buf.zero_()
         self.hdl = symm.rendezvous(self.buf, group)
-        self.multicast = int(self.hdl.multicast_ptr) if (use_multicast and getattr(self.hdl, "has_multicast_support", False)) else 0
+        self.multicast = int(self.hdl.multicast_ptr) if getattr(self.hdl, "has_multicast_support", False) else 0
         if not self.multicast:
-            if not allow_p2p:
-                raise RuntimeError("SymmetricGradSlab: no NVLS multicast support for this group (peer-to-peer variant is opt-in)")
-            blocks = min(int(blocks), 128)
+            raise RuntimeError("SymmetricGradSlab: no NVLS multicast support for this group (use allreduce_gradients = NCCL)")
         self.byte_offset = int(self.buf.data_ptr()) - int(self.hdl.buffer_ptrs[self.rank])
         self.blocks = max(1, int(blocks))
         self.error_flag = torch.zeros(16, dtype=torch.int32, device=dev)  # [0] error code, [2:10] phase timestamps of block 0
+        self._err_host = torch.zeros(1, dtype=torch.int32).pin_memory()  # error word as of the previous call (async copy)
 
         class Args(ctypes.Structure):
             _fields_ = [("n", ctypes.c_int64), ("rank", ctypes.c_int32), ("world", ctypes.c_int32), ("peer_ptrs", ctypes.c_void_p),
@@ -91,6 +91,10 @@ class SymmetricGradSlab:
 
     def all_reduce(self, n=None):
         """In-place sum over the ranks of buf[:n] (default: the whole buffer), on the current stream."""
+        capturing = torch.cuda.is_current_stream_capturing()
+        if not capturing and int(self._err_host[0]) != 0:  # lazily: what an earlier call left behind, no synchronisation here
+            raise RuntimeError(f"slab_allreduce: an earlier call's cross-rank barrier timed out (code {int(self._err_host[0])}); "
+                               "the slab was left unreduced")
         a = self._Args()
         n = self.n if n is None else (int(n) + 3) // 4 * 4
         a.n, a.rank, a.world = n, self.rank, self.world
@@ -100,6 +104,7 @@ class SymmetricGradSlab:
         dev = self.buf.device
         with torch.cuda.device(dev):
             self._gs._check(self._L.slab_allreduce(self._ctypes.byref(a), torch.cuda.current_stream(dev).cuda_stream), "slab_allreduce")
+            self._err_host.copy_(self.error_flag[:1], non_blocking=True)
         return self.buf
 
     def close(self):

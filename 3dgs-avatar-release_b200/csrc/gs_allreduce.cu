@@ -1,10 +1,10 @@
 // gs_allreduce.cu -- the one collective of data-parallel training: sum of the per-rank flat gradient slabs
 // that pose_bwd_kernel writes, in place, as ONE hand-written kernel over NVLink / NVSwitch peer memory (the slab lives in
 // symmetric memory: every rank holds the peers' addresses and, with NVLS, a multicast address of the same buffer).
-// Two-shot: rank r owns the r-th slice.
-//   multicast (NVLS) variant: `multimem.ld_reduce` pulls the slice already summed by the switch, `multimem.st` writes the
-//     result into every replica: each GPU moves 2/N of the slab instead of NCCL's ring traffic, and there is no staging copy;
-//   peer-to-peer variant (no multicast object): reduce-scatter with P2P loads in fixed rank order, then all-gather.
+// Two-shot over the NVLS multicast object: rank r owns the r-th slice; `multimem.ld_reduce` pulls the slice already summed by
+// the switch, `multimem.st` writes the result into every replica: each GPU moves 2/N of the slab instead of NCCL's ring
+// traffic, and there is no staging copy.  (A peer-to-peer variant without the multicast object existed in round 1; it never
+// ran on hardware -- this pool always offers multicast -- and was removed; without multicast the caller uses NCCL.)
 // Ranks meet at in-kernel barriers over the symmetric signal pads (one flag per (block, peer)), so the launch sits inside the
 // step's CUDA graph right behind pose_bwd_kernel and overlaps its tail through programmatic dependent launch.  Sums are
 // identical on every rank (each slice is reduced once, then broadcast).
@@ -13,7 +13,8 @@
 namespace {
 
 #define AR_THREADS 512
-#define AR_SPIN_LIMIT (1u << 21)  // a stuck barrier gives up after about two seconds (error word set) instead of hanging the GPU
+#define AR_SPIN_LIMIT (1u << 25)  // a stuck barrier gives up after tens of seconds (error word set) instead of hanging the GPU:
+                                  // a rank may legitimately arrive seconds late (graph re-capture after an overflow, data stall)
 #define AR_UNROLL 8
 
 __device__ __forceinline__ uint32_t cas_sys_acq_rel(uint32_t* addr, uint32_t cmp, uint32_t val) {
@@ -39,22 +40,30 @@ __device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
 // Cross-rank barrier executed by ONE block per rank: thread t < world raises flag [rank] on peer t's signal pad and waits for
 // flag [t] on its own pad (load-spin, so that the waiting side does not flood its own memory with atomics while the peers'
 // remote atomics are trying to land); every flag returns to 0.
-__device__ __forceinline__ void barrier_ranks(uint32_t* const* pads, int rank, int world, uint32_t* error_flag) {
+// Returns false when a peer never arrived (error word set): the caller then leaves the slab untouched.  This rank's own flags
+// are cleared either way, so a later call starts from a clean pad.
+__device__ __forceinline__ bool barrier_ranks(uint32_t* const* pads, int rank, int world, uint32_t* error_flag) {
+  __shared__ uint32_t s_fail;
+  if (threadIdx.x == 0) s_fail = 0u;
+  __syncthreads();
   if ((int)threadIdx.x < world) {
     __threadfence_system();
     const int peer = (int)threadIdx.x;
     uint32_t* put = pads[peer] + rank;
     uint32_t* wait = pads[rank] + peer;
     uint32_t spins = 0;
+    bool ok = true;
     while (cas_sys_acq_rel(put, 0u, 1u) != 0u)
-      if (++spins > AR_SPIN_LIMIT) { *error_flag = 1u; break; }
+      if (++spins > AR_SPIN_LIMIT) { *error_flag = 1u; ok = false; break; }
     spins = 0;
-    while (ld_acquire_sys(wait) != 1u)
-      if (++spins > AR_SPIN_LIMIT) { *error_flag = 2u; break; }
+    while (ok && ld_acquire_sys(wait) != 1u)
+      if (++spins > AR_SPIN_LIMIT) { *error_flag = 2u; ok = false; break; }
     *wait = 0u;
+    if (!ok) s_fail = 1u;
     __threadfence_system();
   }
   __syncthreads();
+  return s_fail == 0u;
 }
 
 __device__ __forceinline__ float4 mm_ld_reduce(const float4* mc) {
@@ -96,8 +105,8 @@ slab_allreduce_kernel(long long n4, int rank, int world, void* const* peers, uin
   __shared__ bool s_last;
   auto open_gate = [&]() {   // every rank's slab is complete: block 0 meets the peers, the other blocks wait for block 0
     if (blockIdx.x == 0) {
-      barrier_ranks(pads, rank, world, error_flag);
-      if (threadIdx.x == 0) st_release_gpu(go, 1u);
+      const bool ok = barrier_ranks(pads, rank, world, error_flag);
+      if (threadIdx.x == 0) st_release_gpu(go, ok ? 1u : 2u);  // 2 = a peer is missing: nobody touches the slab
     } else {
       if (threadIdx.x == 0) {
         uint32_t spins = 0;
@@ -118,11 +127,12 @@ slab_allreduce_kernel(long long n4, int rank, int world, void* const* peers, uin
   };
   open_gate();
   stamp(1);
-  if (mc) {
+  const bool healthy = ld_acquire_gpu(go) == 1u && *error_flag == 0u;
+  {
     float4* const m = reinterpret_cast<float4*>(reinterpret_cast<char*>(mc) + byte_off);
     // AR_UNROLL independent switch reductions in flight per thread before the first store: the round trip through the
     // NVSwitch is microseconds, so the loop is latency-bound unless many are outstanding
-    for (long long i0 = begin + t0; i0 < end; i0 += stride * AR_UNROLL) {
+    for (long long i0 = begin + t0; healthy && i0 < end; i0 += stride * AR_UNROLL) {
       float4 v[AR_UNROLL];
 #pragma unroll
       for (int u = 0; u < AR_UNROLL; u++)
@@ -133,43 +143,11 @@ slab_allreduce_kernel(long long n4, int rank, int world, void* const* peers, uin
     }
     stamp(2);
     if (last_block()) {  // every block's stores are out: meet the peers, then leave the control words clean
-      barrier_ranks(pads, rank, world, error_flag);  // every slice has reached every replica
+      if (healthy) barrier_ranks(pads, rank, world, error_flag);  // every slice has reached every replica
       if (threadIdx.x == 0) { *go = 0u; *done = 0u; }
       if (threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); stamps[3] = t; }
     }
     return;
-  }
-  float4* const mine = reinterpret_cast<float4*>(reinterpret_cast<char*>(peers[rank]) + byte_off);
-  for (long long i = begin + t0; i < end; i += stride) {  // reduce-scatter: my slice, peers in rank order
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int r = 0; r < world; r++) {
-      const float4 v = ld_sys(reinterpret_cast<const float4*>(reinterpret_cast<const char*>(peers[r]) + byte_off) + i);
-      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-    }
-    mine[i] = acc;
-  }
-  // every slice is final on its owner: the last block meets the peers and re-opens the gate for the gather phase
-  uint32_t* const go2 = error_flag + 14;
-  if (last_block()) {
-    barrier_ranks(pads, rank, world, error_flag);
-    if (threadIdx.x == 0) { *done = 0u; st_release_gpu(go2, 1u); }
-  } else {
-    if (threadIdx.x == 0) {
-      uint32_t spins = 0;
-      while (ld_acquire_gpu(go2) == 0u)
-        if (++spins > AR_SPIN_LIMIT) { *error_flag = 4u; break; }
-    }
-    __syncthreads();
-  }
-  for (int r = 0; r < world; r++) {                      // all-gather
-    if (r == rank) continue;
-    const long long b = min(n4, per * r), e = min(n4, b + per);
-    const float4* src = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(peers[r]) + byte_off);
-    for (long long i = b + t0; i < e; i += stride) mine[i] = ld_sys(src + i);
-  }
-  if (last_block()) {  // nobody overwrites a slab a peer is still reading
-    barrier_ranks(pads, rank, world, error_flag);
-    if (threadIdx.x == 0) { *go = 0u; *go2 = 0u; *done = 0u; }
   }
 }
 
@@ -182,8 +160,7 @@ extern "C" int slab_allreduce(const SlabAllReduceArgs* args, void* stream) {
       !a.error_flag || a.blocks < 1 || (a.byte_offset & 15))
     return GS_ERR_BAD_ARG;
   if (a.n == 0 || a.world == 1) return GS_OK;
-  // the peer-to-peer variant has grid-wide gates in the middle of the kernel: every block must be resident at once
-  if (!a.multicast_ptr && a.blocks > 128) return GS_ERR_BAD_ARG;
+  if (!a.multicast_ptr) return GS_ERR_BAD_ARG;  // NVLS multicast only (without it the caller uses NCCL)
   gs_launch(slab_allreduce_kernel, dim3((unsigned)a.blocks), dim3(AR_THREADS), 0, (cudaStream_t)stream, (long long)(a.n >> 2), (int)a.rank,
             (int)a.world, a.peer_ptrs, a.signal_pads, (float4*)a.multicast_ptr, (long long)a.byte_offset, a.error_flag);
   return gs_check(cudaGetLastError());

@@ -181,6 +181,9 @@ size_t gs_sizeof(int32_t which) {
     case 7: return sizeof(AdamArgs);
     case 8: return sizeof(PoseEncoderArgs);
     case 9: return sizeof(SlabAllReduceArgs);
+    case 10: return sizeof(NonRigidBackwardArgs);
+    case 11: return sizeof(SkinBackwardArgs);
+    case 12: return sizeof(ColorBackwardArgs);
     default: return 0;
   }
 }

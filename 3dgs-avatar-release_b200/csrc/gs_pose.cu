@@ -227,6 +227,8 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
   for (int k = threadIdx.x; k < 24 * 16; k += blockDim.x) s_bones[k] = a.bone_transforms[k];
   if (threadIdx.x < 3) s_cam[threadIdx.x] = a.camera_center[threadIdx.x];
   __shared__ float s_rest_all[4][32 * POSE_MAXREST];  // SH coefficients in, their gradients out
+  __shared__ float s_gbones[288];                     // dL/dbone_transforms[:, :3, :4] of this block
+  for (int k = threadIdx.x; k < 288; k += blockDim.x) s_gbones[k] = 0.f;
   __syncthreads();
   const int lane = threadIdx.x & 31;
   float* const s_rest = s_rest_all[threadIdx.x >> 5];
@@ -236,6 +238,9 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
     const int nstaged = min(32, a.P - i0) * nrest;
     if (nrest) warp_stage_in(s_rest, a.features_rest + (size_t)i0 * nrest, nstaged, lane);
     float* rest_row = s_rest + lane * nrest;
+    float gT[12];  // dL/dT_fwd[:3, :4] of this Gaussian (zero for the lanes past P)
+#pragma unroll
+    for (int k = 0; k < 12; k++) gT[k] = 0.f;
     if (i < a.P) {
     PoseCore c;
     pose_core(a, i, s_bones, c);
@@ -328,13 +333,14 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
     for (int k = 0; k < 3; k++) ba.dL_dxyz[3 * (size_t)i + k] = c.A[0][k] * gxb[0] + c.A[1][k] * gxb[1] + c.A[2][k] * gxb[2];
     const float so = 1.0f / (1.0f + expf(-a.opacity[i]));
     ba.dL_dopacity_logit[i] = ba.dL_dopacity[i] * so * (1.0f - so);
-    if (ba.dL_dweights) {
-      float gT[12];
+    if (ba.dL_dweights || ba.dL_dbone_transforms) {
 #pragma unroll
       for (int r = 0; r < 3; r++) {
         gT[4 * r] = gA[r][0] + gxb[r] * x; gT[4 * r + 1] = gA[r][1] + gxb[r] * y; gT[4 * r + 2] = gA[r][2] + gxb[r] * z;
         gT[4 * r + 3] = gxb[r];
       }
+    }
+    if (ba.dL_dweights) {
       float* gw = ba.dL_dweights + (size_t)i * 24;
       for (int j = 0; j < 24; j++) {
         float acc = 0.f;
@@ -344,7 +350,37 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
       }
     }
     }  // i < P
+    if (ba.dL_dbone_transforms) {
+      // T_fwd = sum_j w_j B_j (rigid.py:215-236)  ->  dL/dB_j[:3, :4] = sum over Gaussians of w_j dL/dT_fwd: the route by which the image
+      // loss reaches the per-frame pose correction.  288 sums over the warp's 32 Gaussians, 32 at a time (transposing butterfly:
+      // lane L ends with the total of value L), then shared-memory and finally global accumulation.
+      const float* wrow = a.weights + (size_t)min(i, a.P - 1) * 24;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 288; c0 += 32) {
+        float v[32];
+#pragma unroll
+        for (int q = 0; q < 32; q++) {
+          const int e = c0 + q;  // e = j * 12 + k
+          v[q] = (i < a.P) ? wrow[e / 12] * gT[e % 12] : 0.f;
+        }
+#define POSE_BSTEP(N, X)                                                        \
+  _Pragma("unroll") for (int k = 0; k < (N) / 2; k++) {                         \
+    const bool up = lane & (X);                                                 \
+    const float send = up ? v[k] : v[k + (N) / 2];                              \
+    const float keepv = up ? v[k + (N) / 2] : v[k];                             \
+    v[k] = keepv + __shfl_xor_sync(0xFFFFFFFFu, send, (X));                     \
+  }
+        POSE_BSTEP(32, 16) POSE_BSTEP(16, 8) POSE_BSTEP(8, 4) POSE_BSTEP(4, 2) POSE_BSTEP(2, 1)
+#undef POSE_BSTEP
+        if (v[0] != 0.f) atomicAdd(&s_gbones[c0 + lane], v[0]);
+      }
+    }
     if (nrest) warp_stage_out(ba.dL_dfeatures_rest + (size_t)i0 * nrest, s_rest, nstaged, lane);
+  }
+  if (ba.dL_dbone_transforms) {
+    __syncthreads();
+    for (int e = threadIdx.x; e < 288; e += blockDim.x)
+      if (s_gbones[e] != 0.f) atomicAdd(ba.dL_dbone_transforms + (e / 12) * 16 + (e % 12), s_gbones[e]);
   }
 }
 
@@ -375,6 +411,8 @@ extern "C" int pose_backward(const PoseBackwardArgs* args, void* stream) {
   if (!args->dL_dmeans3D || !args->dL_dcov3D || !args->dL_dcolors || !args->dL_dopacity) return GS_ERR_BAD_ARG;
   if (!args->dL_dxyz || !args->dL_drotation || !args->dL_dscaling || !args->dL_dopacity_logit || !args->dL_dfeatures_dc) return GS_ERR_BAD_ARG;
   if (args->fwd.M > 1 && !args->dL_dfeatures_rest) return GS_ERR_BAD_ARG;
+  if (args->dL_dbone_transforms &&
+      gs_check(cudaMemsetAsync(args->dL_dbone_transforms, 0, 24 * 16 * sizeof(float), (cudaStream_t)stream)) != GS_OK) return GS_ERR_CUDA;
   if (args->fwd.P == 0) return GS_OK;
   int blocks = (args->fwd.P + 127) / 128;
   if (blocks > 148 * 16) blocks = 148 * 16;

@@ -489,7 +489,7 @@ def ours_main(args):
     from avatar_pose import dist as apd
 
     # the one collective of the data-parallel step: the hand-written NVLink all-reduce over the symmetric gradient slab
-    # (gs_allreduce.cu: NVLS multimem two-shot, P2P fallback); NCCL only where symmetric memory cannot be set up
+    # (gs_allreduce.cu: NVLS multimem two-shot); NCCL only where symmetric memory / multicast cannot be set up
     symm_slab, collective = None, "none (single GPU)"
     if world > 1:
         collective = "nccl all_reduce of the flat gradient slab"
@@ -501,7 +501,7 @@ def ours_main(args):
                 symm_slab = apd.SymmetricGradSlab(59 * P)
                 avatar_pose.set_grad_slab_buffer(symm_slab.buf)
                 collective = ("slab_allreduce kernel over symmetric memory (" +
-                              ("NVLS multimem.ld_reduce / multimem.st two-shot" if symm_slab.multicast else "peer-to-peer two-shot") + ")")
+                              "NVLS multimem.ld_reduce / multimem.st two-shot)")
             except Exception as ex:
                 symm_slab = None
                 print(f"[bench] symmetric-memory all-reduce unavailable, using NCCL: {str(ex)[:200]}", file=sys.stderr)

@@ -183,6 +183,8 @@ typedef struct PoseBackwardArgs {
   float* dL_dfeatures_dc;   /* [P,1,3] */
   float* dL_dfeatures_rest; /* [P,M-1,3] */
   float* dL_dweights;  /* [P,24] or NULL */
+  float* dL_dbone_transforms; /* [24,4,4] or NULL: sum_p w[p,j] dL/dT_fwd[p] (rigid.py:215-236), the gradient that reaches the
+                               * per-frame pose correction (models/pose_correction); zeroed by the call, bottom rows stay 0 */
 } PoseBackwardArgs;
 
 int pose_forward(const PoseArgs* args, void* stream);
@@ -230,6 +232,39 @@ typedef struct NonRigidArgs {
 size_t nonrigid_workspace_bytes(const NonRigidArgs* args);
 int nonrigid_forward(const NonRigidArgs* args, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- non-rigid deformation, training: forward that keeps its activations + hand-written backward ----
+ * Replaces the autograd backward of HashGridwithMLP.forward (models/deformer/non_rigid.py:226-300): VanillaCondMLP
+ * (models/network_utils.py:182-249: dX = G.W, dW = G^T.H, db = column sums, LeakyReLU' from the saved activations),
+ * HashGrid (models/network_utils.py:329-344 -> tiny-cuda-nn: dL/dtable scattered with red.global.add over the 8 corners of
+ * every level, dL/dx through the trilinear weights) and the delta application (identity for xyz / scaling, Hamilton product
+ * for the rotation).  nonrigid_forward_train = nonrigid_forward + `saved` (nonrigid_saved_bytes(P) bytes: per tile of 128
+ * Gaussians the input features and the three hidden activations in the BF16 hi/lo operand layout of the tensor cores).
+ * nonrigid_backward: `fwd` as in the forward call with fwd.deltas = the forward's raw MLP output (read here);  upstream
+ * gradients may be NULL (= zero).  Per-Gaussian outputs are assigned; parameter gradients (table, W*, b*, cond) are zeroed
+ * by the call and then accumulated.  All GEMMs run on tcgen05 (dW contracts over the tile's 128 Gaussians with MN-major
+ * descriptors on the very buffers dX reads K-major), 2-way BF16 split, FP32 accumulate in TMEM. */
+typedef struct NonRigidBackwardArgs {
+  NonRigidArgs fwd;
+  const float* dL_dxyz_out;       /* [P,3] or NULL */
+  const float* dL_dscaling_out;   /* [P,3] or NULL */
+  const float* dL_drotation_out;  /* [P,4] or NULL */
+  const float* dL_ddeltas;        /* [P,n_out] or NULL (regularisers on the raw deltas, non_rigid.py:283-298) */
+  float* dL_dxyz;                 /* [P,3] */
+  float* dL_dscaling;             /* [P,3] */
+  float* dL_drotation;            /* [P,4] */
+  float* dL_dcond;                /* [C] or NULL */
+  float* dL_dtable;               /* [level_offset[L], 2] */
+  float* dL_dW0; float* dL_db0;   /* [H, L*n_feat + C], [H] */
+  float* dL_dW1; float* dL_db1;
+  float* dL_dW2; float* dL_db2;
+  float* dL_dW3; float* dL_db3;   /* [n_out, H], [n_out] */
+} NonRigidBackwardArgs;
+size_t nonrigid_saved_bytes(int32_t P);
+int nonrigid_forward_train(const NonRigidArgs* args, void* workspace, size_t workspace_bytes, void* saved, size_t saved_bytes,
+                           void* stream);
+int nonrigid_backward(const NonRigidBackwardArgs* args, void* workspace, size_t workspace_bytes, const void* saved,
+                      size_t saved_bytes, void* stream);
+
 /* ---- skinning field: per-Gaussian LBS weights from the skinning MLP (forward) ----
  * Replaces SkinningField.get_forward_transform's weight part, models/deformer/rigid.py:160-171,189-196 (non-distilled
  * path): AABB.normalize(sym=True) -> VanillaCondMLP(3 -> H x4 -> n_out) (models/network_utils.py:182-249,251-257;
@@ -251,6 +286,24 @@ typedef struct SkinArgs {
 } SkinArgs;
 size_t skinning_workspace_bytes(const SkinArgs* args);
 int skinning_forward(const SkinArgs* args, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- skinning field, training: forward that keeps its activations + hand-written backward ----
+ * Replaces the autograd backward of the weight part of SkinningField (rigid.py:85-129 hierarchical_softmax, :160-171 softmax,
+ * :189-196 lbs_network): adjoint of the (hierarchical) softmax per Gaussian, then the MLP backward on tcgen05 as in
+ * nonrigid_backward; dL/dxyz through AABB.normalize.  `fwd.logits` must hold the forward's logits [P,n_out] (read here).
+ * Parameter gradients are zeroed by the call and accumulated; dL_dxyz is assigned. */
+typedef struct SkinBackwardArgs {
+  SkinArgs fwd;
+  const float* dL_dweights;  /* [P,24] */
+  float* dL_dxyz;            /* [P,3] */
+  float* dL_dW[5];
+  float* dL_db[5];
+} SkinBackwardArgs;
+size_t skinning_saved_bytes(int32_t P);
+int skinning_forward_train(const SkinArgs* args, void* workspace, size_t workspace_bytes, void* saved, size_t saved_bytes,
+                           void* stream);
+int skinning_backward(const SkinBackwardArgs* args, void* workspace, size_t workspace_bytes, const void* saved,
+                      size_t saved_bytes, void* stream);
 
 /* ---- colour MLP texture (forward) ----
  * Replaces ColorMLP.forward, models/texture/texture.py:40-125 (registry key "mlp", the repository's default texture,
@@ -286,6 +339,31 @@ typedef struct ColorArgs {
 } ColorArgs;
 size_t color_workspace_bytes(const ColorArgs* args);
 int color_forward(const ColorArgs* args, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- colour MLP texture, training: forward that keeps its activations + hand-written backward ----
+ * Replaces the autograd backward of ColorMLP.forward (models/texture/texture.py:74-125): sigmoid', the three linear layers
+ * on tcgen05 (dX = G.W, dW = G^T.A over the tile's 128 Gaussians, MN-major descriptors; see nonrigid_backward), LeakyReLU'
+ * from the saved activations, then the adjoint of compose_input: per-Gaussian feature, SH basis -> view direction ->
+ * (view noise) -> canonical rotation T_fwd[:3,:3]^T -> xyz, non-rigid feature; the latent code through the folded bias.
+ * `fwd.colors` must hold the forward's colours (read here).  Per-Gaussian outputs (each may be NULL) are assigned; parameter
+ * gradients are zeroed by the call and accumulated. */
+typedef struct ColorBackwardArgs {
+  ColorArgs fwd;
+  const float* dL_dcolors;        /* [P,3] */
+  float* dL_dfeatures;            /* [P,F] or NULL */
+  float* dL_dxyz;                 /* [P,3] or NULL */
+  float* dL_dT_fwd;               /* [P,16] or NULL */
+  float* dL_dnon_rigid_feature;   /* [P,R] or NULL */
+  float* dL_dlatent;              /* [Z] or NULL */
+  float* dL_dW0; float* dL_db0;
+  float* dL_dW1; float* dL_db1;
+  float* dL_dW2; float* dL_db2;
+} ColorBackwardArgs;
+size_t color_saved_bytes(int32_t P);
+int color_forward_train(const ColorArgs* args, void* workspace, size_t workspace_bytes, void* saved, size_t saved_bytes,
+                        void* stream);
+int color_backward(const ColorBackwardArgs* args, void* workspace, size_t workspace_bytes, const void* saved, size_t saved_bytes,
+                   void* stream);
 
 /* ---- optimiser-side per-Gaussian work of a training iteration ----
  * adam_step: torch.optim.Adam as configured by GaussianModel.training_setup (scene/gaussian_model.py:201-221: six
@@ -344,9 +422,11 @@ int pose_encoder_forward(const PoseEncoderArgs* args, void* stream);
  * behind pose_backward instead of an NCCL call.  The slab must live in symmetric memory (same allocation on every rank,
  * peers' addresses exchanged once): `peer_ptrs[world]` / `signal_pads[world]` are DEVICE arrays of the peers' buffer and
  * signal-pad addresses (zero-initialised pads, >= blocks * world * 4 bytes), `multicast_ptr` the NVLS multicast address of
- * the buffer or NULL (then peer-to-peer loads are used).  Every rank must call it with the same n / blocks; ranks meet at
- * in-kernel barriers.  `error_flag`: 16 device u32; [0] is set if a barrier gives up (a peer never arrived), [2:10] receive
- * four 64-bit %globaltimer stamps of block 0 (start, after the first barrier, after the data phase, end). */
+ * the buffer (required: without NVLS multicast support the caller uses NCCL).  Every rank must call it with the same
+ * n / blocks; ranks meet at in-kernel barriers.  `error_flag`: 16 device u32; [0] is set if a barrier gives up after tens of
+ * seconds (a peer never arrived): the slab is then left UNTOUCHED, this rank's flags are cleared, and every later call is a
+ * no-op until the caller resets [0]; [2:10] receive four 64-bit %globaltimer stamps of block 0 (start, after the first
+ * barrier, after the data phase, end). */
 typedef struct SlabAllReduceArgs {
   int64_t n;               /* floats, multiple of 4 */
   int32_t rank, world;
@@ -390,7 +470,8 @@ int gs_set_exp_mode(int mode);
 int gs_read_counters(const void* geom, uint64_t* counters_host, void* stream);
 
 /* sizeof of the ABI structs: 0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs,
- * 6 ColorArgs, 7 AdamArgs, 8 PoseEncoderArgs, 9 SlabAllReduceArgs */
+ * 6 ColorArgs, 7 AdamArgs, 8 PoseEncoderArgs, 9 SlabAllReduceArgs, 10 NonRigidBackwardArgs, 11 SkinBackwardArgs,
+ * 12 ColorBackwardArgs */
 size_t gs_sizeof(int32_t which);
 int gs_last_cuda_error(void);
 const char* gs_version(void);

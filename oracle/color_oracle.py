@@ -54,13 +54,14 @@ def compose_input(features, xyz, T_fwd, camera_center, non_rigid_feature, latent
 
 
 def color_forward(features, xyz, T_fwd, camera_center, non_rigid_feature, latent, Ws, bs, sh_degree=3,
-                  cano_view_dir=True, view_noise=None):
-    """-> colors [P,3]: sigmoid(lin2(lrelu(lin1(lrelu(lin0(input))))))."""
+                  cano_view_dir=True, view_noise=None, masks=None):
+    """-> colors [P,3]: sigmoid(lin2(lrelu(lin1(lrelu(lin0(input)))))).  `masks` (optional): the LeakyReLU branch of every
+    hidden unit prescribed from outside (see oracle/nonrigid_oracle.py:_lrelu)."""
     h = compose_input(features, xyz, T_fwd, camera_center, non_rigid_feature, latent, sh_degree, cano_view_dir, view_noise)
     for l in range(len(Ws)):
         h = F.linear(h, Ws[l], bs[l])
         if l < len(Ws) - 1:
-            h = F.leaky_relu(h, 0.01)
+            h = F.leaky_relu(h, 0.01) if masks is None else torch.where(masks[l], h, 0.01 * h)
     return torch.sigmoid(h)
 
 

@@ -63,16 +63,23 @@ def hash_encode(x01, table, level_offset, level_res, level_scale):
     return torch.cat(outs, 1)
 
 
-def nonrigid_forward(xyz, scaling, rotation, aabb_min, aabb_max, table, levels, cond, W, b, features=None):
+def _lrelu(h, mask=None):
+    """LeakyReLU(0.01).  `mask` (optional, bool like h): the branch each unit takes, prescribed from outside instead of h > 0 --
+    lets a gradient test use the SAME branches as the implementation under test for the few units whose pre-activation is
+    within rounding of zero (their derivative jumps between 1 and 0.01)."""
+    return torch.nn.functional.leaky_relu(h, 0.01) if mask is None else torch.where(mask, h, 0.01 * h)
+
+
+def nonrigid_forward(xyz, scaling, rotation, aabb_min, aabb_max, table, levels, cond, W, b, features=None, masks=None):
     """W = [W0 [H, F+C], W1, W2, W3 [n_out, H]], b likewise.  Returns dict(xyz, scaling, rotation, deltas, features).
-    `features` (optional) replaces the hash-grid encoding (to check the MLP on its own)."""
+    `features` (optional) replaces the hash-grid encoding (to check the MLP on its own); `masks`: see _lrelu."""
     xn = 2.0 * ((xyz - aabb_min) / (aabb_max - aabb_min)) - 1.0  # AABB.normalize(sym=True)
     feat = hash_encode((xn + 1.0) * 0.5, table, *levels) if features is None else features
     h = torch.cat([feat, cond.reshape(1, -1).expand(xyz.shape[0], -1)], 1)  # cond_in: [0]
     for l in range(4):
         h = h @ W[l].T + b[l]
         if l < 3:
-            h = torch.nn.functional.leaky_relu(h, 0.01)
+            h = _lrelu(h, None if masks is None else masks[l])
     d = h
     q1 = torch.cat([torch.ones_like(d[:, 6:7]), d[:, 7:10]], 1)  # q1[:, 0] = 1 (non_rigid.py:276-277)
     aw, ax, ay, az = q1.unbind(1)
@@ -110,13 +117,13 @@ def hierarchical_softmax(x):
     return p
 
 
-def skinning_weights_forward(xyz, aabb_min, aabb_max, W, b):
+def skinning_weights_forward(xyz, aabb_min, aabb_max, W, b, masks=None):
     """SkinningField.get_forward_transform's weights (rigid.py:160-171, 189-196, non-distilled): AABB.normalize(sym) ->
     VanillaCondMLP(3 -> H x4 -> n_out), LeakyReLU(0.01) -> hierarchical softmax (25 logits) / softmax (24)."""
     h = 2.0 * ((xyz - aabb_min) / (aabb_max - aabb_min)) - 1.0
     for l in range(len(W)):
         h = h @ W[l].T + b[l]
         if l < len(W) - 1:
-            h = torch.nn.functional.leaky_relu(h, 0.01)
+            h = _lrelu(h, None if masks is None else masks[l])
     w = hierarchical_softmax(h) if h.shape[1] == 25 else torch.softmax(h, -1)
     return w, h

@@ -13,7 +13,7 @@ P = int(sys.argv[1]) if len(sys.argv) > 1 else 50000
 n = 59 * P
 res = {}
 for blocks, mc in ((32, True), (144, True)):
-    slab = SymmetricGradSlab(n, blocks=blocks, use_multicast=mc, allow_p2p=True)
+    slab = SymmetricGradSlab(n, blocks=blocks)
     x = torch.randn(n, device=dev)
     ref = x.clone()
 

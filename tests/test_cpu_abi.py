@@ -46,11 +46,11 @@ def test_struct_layout_matches_header(built_lib):
     assert ctypes.sizeof(_C.GsForwardArgs) == 40 + 14 * 8
     assert ctypes.sizeof(_C.GsBackwardArgs) == 40 + 22 * 8
     assert ctypes.sizeof(avatar_pose.PoseArgs) == 24 + 15 * 8
-    assert ctypes.sizeof(avatar_pose.PoseBackwardArgs) == ctypes.sizeof(avatar_pose.PoseArgs) + 11 * 8
+    assert ctypes.sizeof(avatar_pose.PoseBackwardArgs) == ctypes.sizeof(avatar_pose.PoseArgs) + 12 * 8
     # and against the library itself
-    from avatar_pose.nonrigid import NonRigidArgs
-    from avatar_pose.skinning import SkinArgs
-    from avatar_pose.texture import ColorArgs
+    from avatar_pose.nonrigid import NonRigidArgs, NonRigidBackwardArgs
+    from avatar_pose.skinning import SkinArgs, SkinBackwardArgs
+    from avatar_pose.texture import ColorArgs, ColorBackwardArgs
     from avatar_pose.optim import AdamArgs
     from avatar_pose.pose_encoder import PoseEncoderArgs
     L = _C.lib()
@@ -58,6 +58,8 @@ def test_struct_layout_matches_header(built_lib):
     L.gs_sizeof.argtypes = [ctypes.c_int32]
     for which, st in enumerate((_C.GsForwardArgs, _C.GsBackwardArgs, avatar_pose.PoseArgs, avatar_pose.PoseBackwardArgs,
                                 NonRigidArgs, SkinArgs, ColorArgs, AdamArgs, PoseEncoderArgs)):
+        assert L.gs_sizeof(which) == ctypes.sizeof(st), st.__name__
+    for which, st in ((10, NonRigidBackwardArgs), (11, SkinBackwardArgs), (12, ColorBackwardArgs)):
         assert L.gs_sizeof(which) == ctypes.sizeof(st), st.__name__
 
 

@@ -89,10 +89,30 @@ def test_skinning_field_weights(built_lib, P, d_out):
     assert torch.isfinite(means).all()
 
 
+def saved_masks(saved, P, in_cols, n_layers):
+    """LeakyReLU branches (activation > 0) of the hidden layers, decoded from the activations the training forward keeps:
+    per tile of 128 Gaussians [input hi|lo 128 x in_cols][layer: hi|lo 128 x 128] BF16 in the tensor cores' core-matrix
+    layout (element (row, k) at (k >> 3) * 1024 + row * 8 + (k & 7))."""
+    x = saved.view(torch.bfloat16)
+    tiles = (P + 127) // 128
+    per_tile = 2 * 128 * in_cols + n_layers * 2 * 16384
+    x = x[:tiles * per_tile].view(tiles, per_tile)
+    out = []
+    for l in range(n_layers):
+        o = 2 * 128 * in_cols + l * 32768
+        hi = x[:, o:o + 16384].float().view(tiles, 16, 128, 8).permute(0, 2, 1, 3).reshape(tiles * 128, 128)[:P]
+        out.append((hi > 0).cpu())
+    return out
+
+
 def test_nonrigid_and_skinning_gradients(built_lib):
     """deform_autograd / query_weights_autograd: forward values from the tcgen05 kernels, gradients (inputs, hash table,
-    linear layers) against fp64 autograd of the oracle, <= 2e-3 of each gradient's max (fp32 re-evaluation + FP32 hash
-    positions)."""
+    linear layers) from the hand-written backward kernels (nonrigid_backward / skinning_backward) against fp64 autograd of
+    the oracle, <= 1e-4 of each gradient's max (north_star's gradient tolerance).  The oracle takes the LeakyReLU branch
+    of every hidden unit from the implementation's own saved activations: a unit whose pre-activation is within rounding
+    of zero has a derivative that jumps between 1 and 0.01, which is not a property of the backward under test.  xyz and
+    the hash table: d(feature)/d(position) is piecewise constant per cell, so the FP32 positions that fall into the
+    neighbouring cell of the finest levels are judged on the 99.5 % quantile."""
     from avatar_pose.nonrigid import HashGridMLPFused
     from avatar_pose.skinning import SkinningFieldFused
     dev = torch.device("cuda:0")
@@ -112,22 +132,30 @@ def test_nonrigid_and_skinning_gradients(built_lib):
     r_in = [d64(t) for t in (xyz, sc, rot, cond, m.table)]
     rW = [d64(l.weight) for l in (m.lin0, m.lin1, m.lin2, m.lin3)]
     rb = [d64(l.bias) for l in (m.lin0, m.lin1, m.lin2, m.lin3)]
+    import copy
+    md = copy.deepcopy(m).to(dev)
+    sv = md.saved_buffer(P, dev)
+    md.deform(xyz.to(dev), sc.to(dev), rot.to(dev), cond.to(dev), _saved=sv)
     ref = nro.nonrigid_forward(r_in[0], r_in[1], r_in[2], m.aabb_min.double(), m.aabb_max.double(), r_in[4], m.levels,
-                               r_in[3], rW, rb)
+                               r_in[3], rW, rb, masks=saved_masks(sv, P, 32, 3))
     loss = sum((ref[k] * go.double()).sum() for k, go in zip(("xyz", "scaling", "rotation", "deltas"), gouts))
     loss.backward()
     # ours
-    md = m.to(dev)
     ins = [t.to(dev).requires_grad_(True) for t in (xyz, sc, rot, cond)]
     outs = md.deform_autograd(*ins)
     sum((o * go.to(dev)).sum() for o, go in zip(outs, gouts)).backward()
     torch.cuda.synchronize()
+
+    report = {}
 
     def close(a, b, name, robust=False):
         a, b = a.detach().cpu().double(), b.detach().double()
         s = float(b.abs().max())
         assert s > 0, name
         err = (a - b).abs().flatten()
+        report[name] = (float(err.max()) / s, float(err.quantile(0.995)) / s)
+        print(f"GRAD {name}: max {float(err.max()) / s:.3e} q99.5 {float(err.quantile(0.995)) / s:.3e}")
+        return
         if robust:  # d(feature)/d(position) is piecewise constant per cell: an FP32 position within ~1e-4 cells of a cell
             # face of the finest levels (scale 2047) falls into the neighbouring cell of the fp64 oracle
             assert float(err.quantile(0.995)) <= 2e-3 * s and float(err.max()) <= 5e-2 * s, (name, float(err.max()), s)
@@ -149,9 +177,12 @@ def test_nonrigid_and_skinning_gradients(built_lib):
     x64 = d64(xyz)
     sW = [d64(getattr(s, f"lin{l}").weight) for l in range(5)]
     sb = [d64(getattr(s, f"lin{l}").bias) for l in range(5)]
-    w_ref, _ = nro.skinning_weights_forward(x64, s.aabb_min.double(), s.aabb_max.double(), sW, sb)
+    sd = copy.deepcopy(s).to(dev)
+    from avatar_pose import skinning as _sk
+    sv = torch.empty(_sk._lib().skinning_saved_bytes(P), dtype=torch.uint8, device=dev)
+    sd.query_weights(xyz.to(dev), _saved=sv)
+    w_ref, _ = nro.skinning_weights_forward(x64, s.aabb_min.double(), s.aabb_max.double(), sW, sb, masks=saved_masks(sv, P, 16, 4))
     (w_ref * gw.double()).sum().backward()
-    sd = s.to(dev)
     x = xyz.to(dev).requires_grad_(True)
     w = sd.query_weights_autograd(x)
     (w * gw.to(dev)).sum().backward()
@@ -159,3 +190,6 @@ def test_nonrigid_and_skinning_gradients(built_lib):
     for l in range(5):
         close(getattr(sd, f"lin{l}").weight.grad, sW[l].grad, f"skin W{l}")
         close(getattr(sd, f"lin{l}").bias.grad, sb[l].grad, f"skin b{l}")
+    bad = {k: v for k, v in report.items()
+           if ((v[1] > 1e-4 or v[0] > 5e-2) if k in ("xyz", "table", "skin xyz") else v[0] > 1e-4)}
+    assert not bad, bad

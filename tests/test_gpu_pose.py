@@ -25,7 +25,7 @@ def _inputs(P, seed=0, pose_seed=1, random_init=False):
 
 
 def _oracle(t, deg, dtype=torch.float32, grads=None, cano=True, mod=1.0):
-    leaf = {k: v.to(dtype).clone().requires_grad_(k not in ("bones", "cam")) for k, v in t.items()}
+    leaf = {k: v.to(dtype).clone().requires_grad_(k != "cam") for k, v in t.items()}
     feat = torch.cat([leaf["features_dc"], leaf["features_rest"]], 1)
     out = pose_oracle.pose_forward(leaf["xyz"], leaf["rotation"], leaf["scaling"], leaf["opacity"], feat, leaf["weights"],
                                    leaf["bones"], leaf["cam"], deg, mod, cano)
@@ -49,7 +49,7 @@ def test_pose_forward_backward(built_lib, deg, cano, mod, P):
     gen = torch.Generator().manual_seed(7)
     grads = {"means3D": torch.randn(P, 3, generator=gen), "cov3D": torch.randn(P, 6, generator=gen) * 10,
              "colors": torch.randn(P, 3, generator=gen), "opacity": torch.randn(P, 1, generator=gen)}
-    d = {k: v.to(dev).requires_grad_(k not in ("bones", "cam")) for k, v in t.items()}
+    d = {k: v.to(dev).requires_grad_(k != "cam") for k, v in t.items()}
     means, cov, col, op, T_fwd, Rbar = fused_pose(d["xyz"], d["rotation"], d["scaling"], d["opacity"], d["features_dc"],
                                                   d["features_rest"], d["weights"], d["bones"], d["cam"], deg, mod, cano,
                                                   return_aux=True)
@@ -81,3 +81,5 @@ def test_pose_forward_backward(built_lib, deg, cano, mod, P):
     _, leaf = _oracle(t, deg, torch.float64, grads, cano=cano, mod=mod)
     for k in ("xyz", "rotation", "scaling", "opacity", "features_dc", "features_rest", "weights"):
         assert rel(d[k].grad.cpu(), leaf[k].grad) <= 1e-4, k
+    # bone transforms (the gradient a per-frame pose correction receives): rows 0..2 of every 4x4; the bottom row is a constant
+    assert rel(d["bones"].grad.cpu()[:, :3, :], leaf["bones"].grad[:, :3, :]) <= 1e-4, "bone_transforms"
