@@ -21,7 +21,7 @@ class PoseArgs(ctypes.Structure):
                 ("xyz", vp), ("rotation", vp), ("scaling", vp), ("opacity", vp), ("features_dc", vp),
                 ("features_rest", vp), ("weights", vp), ("bone_transforms", vp), ("camera_center", vp),
                 ("means3D", vp), ("cov3D", vp), ("colors", vp), ("opacity_out", vp), ("T_fwd", vp),
-                ("rotation_bar", vp)]
+                ("rotation_bar", vp), ("view_noise", vp)]
 
 
 class PoseBackwardArgs(ctypes.Structure):
@@ -65,7 +65,7 @@ def _p(t, name):
     return _gs._ptr(t, name)
 
 
-def _fill_fwd(xyz, rotation, scaling, opacity, f_dc, f_rest, weights, bones, cam, sh_degree, mod, cano):
+def _fill_fwd(xyz, rotation, scaling, opacity, f_dc, f_rest, weights, bones, cam, sh_degree, mod, cano, view_noise=None):
     P = xyz.shape[0]
     M = 1 + (f_rest.shape[1] if f_rest is not None and f_rest.numel() else 0)
     a = PoseArgs()
@@ -73,6 +73,7 @@ def _fill_fwd(xyz, rotation, scaling, opacity, f_dc, f_rest, weights, bones, cam
     a.xyz, a.rotation, a.scaling, a.opacity = _p(xyz, "xyz"), _p(rotation, "rotation"), _p(scaling, "scaling"), _p(opacity, "opacity")
     a.features_dc, a.features_rest = _p(f_dc, "features_dc"), _p(f_rest, "features_rest")
     a.weights, a.bone_transforms, a.camera_center = _p(weights, "weights"), _p(bones, "bone_transforms"), _p(cam, "camera_center")
+    a.view_noise = _p(view_noise, "view_noise") if view_noise is not None else None
     if weights.shape[-1] != 24 or bones.numel() != 24 * 16:
         raise _gs.GsError("weights must be [P,24] and bone_transforms [24,4,4]")
     return a
@@ -81,7 +82,7 @@ def _fill_fwd(xyz, rotation, scaling, opacity, f_dc, f_rest, weights, bones, cam
 class _FusedPose(torch.autograd.Function):
     @staticmethod
     def forward(ctx, xyz, rotation, scaling, opacity, f_dc, f_rest, weights, bones, cam, sh_degree, mod, cano,
-                want_aux):
+                want_aux, view_noise=None):
         L = _lib()
         dev = xyz.device
         if not xyz.is_cuda:
@@ -97,7 +98,8 @@ class _FusedPose(torch.autograd.Function):
             colors, opac = flat[9 * P:12 * P].view(P, 3), flat[12 * P:].view(P, 1)
             T_fwd = torch.empty(P, 4, 4, **f32) if want_aux else None
             Rbar = torch.empty(P, 3, 3, **f32) if want_aux else None
-            a = _fill_fwd(xyz_, rot_, sc_, op_, dc_, rest_, w_, b_, cam_, sh_degree, mod, cano)
+            vn_ = None if view_noise is None else view_noise.detach().contiguous().float().reshape(-1)
+            a = _fill_fwd(xyz_, rot_, sc_, op_, dc_, rest_, w_, b_, cam_, sh_degree, mod, cano, vn_)
             a.means3D, a.cov3D, a.colors, a.opacity_out = means.data_ptr(), cov.data_ptr(), colors.data_ptr(), opac.data_ptr()
             a.T_fwd = T_fwd.data_ptr() if want_aux else None
             a.rotation_bar = Rbar.data_ptr() if want_aux else None
@@ -105,6 +107,7 @@ class _FusedPose(torch.autograd.Function):
                 _gs._check(L.pose_forward(ctypes.byref(a), torch.cuda.current_stream(dev).cuda_stream), "pose_forward")
         ctx.save_for_backward(xyz_, rot_, sc_, op_, dc_, rest_, w_, b_, cam_)
         ctx.cfg = (int(sh_degree), float(mod), bool(cano))
+        ctx.view_noise = vn_
         ctx.need_w = weights.requires_grad
         ctx.need_b = bones.requires_grad
         if want_aux:
@@ -138,7 +141,7 @@ class _FusedPose(torch.autograd.Function):
             gdc, grest = parts[4].view(P, 1, 3), parts[5].view(P, nrest, 3)
             gw = torch.empty(P, 24, **f32) if ctx.need_w else None
             ba = PoseBackwardArgs()
-            ba.fwd = _fill_fwd(xyz, rot, sc, op, dc, rest, w, b, cam, sh_degree, mod, cano)
+            ba.fwd = _fill_fwd(xyz, rot, sc, op, dc, rest, w, b, cam, sh_degree, mod, cano, ctx.view_noise)
             ba.dL_dmeans3D, ba.dL_dcov3D, ba.dL_dcolors, ba.dL_dopacity = (g_means.data_ptr(), g_cov.data_ptr(),
                                                                            g_col.data_ptr(), g_op.data_ptr())
             ba.dL_dxyz, ba.dL_drotation, ba.dL_dscaling, ba.dL_dopacity_logit = (gxyz.data_ptr(), grot.data_ptr(),
@@ -152,16 +155,17 @@ class _FusedPose(torch.autograd.Function):
                 _gs._check(L.pose_backward(ctypes.byref(ba), torch.cuda.current_stream(dev).cuda_stream), "pose_backward")
         _last_slab[0] = flat
         gop = gop.view(op.shape)
-        return gxyz, grot, gsc, gop, gdc, grest, gw, (gb.view(b.shape) if gb is not None else None), None, None, None, None, None
+        return gxyz, grot, gsc, gop, gdc, grest, gw, (gb.view(b.shape) if gb is not None else None), None, None, None, None, None, None
 
 
 def fused_pose(xyz, rotation, scaling, opacity, features_dc, features_rest, weights, bone_transforms, camera_center,
-               sh_degree=3, scaling_modifier=1.0, cano_view_dir=True, return_aux=False):
+               sh_degree=3, scaling_modifier=1.0, cano_view_dir=True, return_aux=False, view_noise=None):
     """-> (means3D [P,3], cov3D [P,6], colors [P,3], opacity [P,1]) (+ T_fwd [P,4,4], rotation_bar [P,3,3]).
 
     Inputs are the raw GaussianModel parameters (`_xyz`, `_rotation`, `_scaling`, `_opacity`, `_features_dc`,
     `_features_rest`), per-Gaussian skinning weights [P,24], `camera.bone_transforms` [24,4,4] and
-    `camera.camera_center` [3].  Gradients flow to the six parameter tensors, to `weights` and to `bone_transforms` (the route by
+    `camera.camera_center` [3]; `view_noise` [3,3]: the training-time view augmentation of SH2RGB (texture.py:28-33: the matrix the
+    reference multiplies the canonical view direction with, i.e. augm_rots(...).T), None in eval mode.  Gradients flow to the six parameter tensors, to `weights` and to `bone_transforms` (the route by
     which the image loss reaches a per-frame pose correction, rigid.py:215-236)."""
     return _FusedPose.apply(xyz, rotation, scaling, opacity, features_dc, features_rest, weights, bone_transforms,
-                            camera_center, sh_degree, scaling_modifier, cano_view_dir, return_aux)
+                            camera_center, sh_degree, scaling_modifier, cano_view_dir, return_aux, view_noise)

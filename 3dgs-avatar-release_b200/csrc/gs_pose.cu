@@ -143,6 +143,12 @@ __device__ __forceinline__ void view_dir(const PoseArgs& a, const PoseCore& c, c
     d[0] = c.A[0][0] * v0 + c.A[1][0] * v1 + c.A[2][0] * v2;
     d[1] = c.A[0][1] * v0 + c.A[1][1] * v1 + c.A[2][1] * v2;
     d[2] = c.A[0][2] * v0 + c.A[1][2] * v1 + c.A[2][2] * v2;
+    if (a.view_noise) {  // training augmentation, texture.py:28-33: dir <- dir @ view_noise (row vector times matrix)
+      const float* N = a.view_noise;
+      const float n0 = d[0] * N[0] + d[1] * N[3] + d[2] * N[6], n1 = d[0] * N[1] + d[1] * N[4] + d[2] * N[7];
+      const float n2 = d[0] * N[2] + d[1] * N[5] + d[2] * N[8];
+      d[0] = n0; d[1] = n1; d[2] = n2;
+    }
   } else { d[0] = v0; d[1] = v1; d[2] = v2; }
   n = sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
 }
@@ -271,7 +277,13 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
       // u = d / (n + eps):  dL/dd = g/(n+eps) - d (d.g) / (n (n+eps)^2)
       const float dg = d[0] * gu[0] + d[1] * gu[1] + d[2] * gu[2];
       const float k2 = n > 0.f ? dg * inv * inv / n : 0.f;
-      const float gd[3] = {gu[0] * inv - d[0] * k2, gu[1] * inv - d[1] * k2, gu[2] * inv - d[2] * k2};
+      float gd[3] = {gu[0] * inv - d[0] * k2, gu[1] * inv - d[1] * k2, gu[2] * inv - d[2] * k2};
+      if (a.cano_view_dir && a.view_noise) {  // d' = d @ N  ->  dL/dd_j = sum_k N[j][k] g'_k
+        const float* N = a.view_noise;
+        const float t0 = N[0] * gd[0] + N[1] * gd[1] + N[2] * gd[2], t1 = N[3] * gd[0] + N[4] * gd[1] + N[5] * gd[2];
+        const float t2 = N[6] * gd[0] + N[7] * gd[1] + N[8] * gd[2];
+        gd[0] = t0; gd[1] = t1; gd[2] = t2;
+      }
       if (a.cano_view_dir) {  // d = A^T v with A detached -> dL/dv = A gd
 #pragma unroll
         for (int r = 0; r < 3; r++) gxb[r] += c.A[r][0] * gd[0] + c.A[r][1] * gd[1] + c.A[r][2] * gd[2];
@@ -419,5 +431,51 @@ extern "C" int pose_backward(const PoseBackwardArgs* args, void* stream) {
   gs_prof_mark(6, 0, (cudaStream_t)stream);
   gs_launch(pose_bwd_kernel, dim3(blocks), dim3(128), 0, (cudaStream_t)stream, *args);
   gs_prof_mark(6, 1, (cudaStream_t)stream);
+  return gs_check(cudaGetLastError());
+}
+
+// ================================= smpl_nn: nearest SMPL vertex per Gaussian =================================
+// Replaces SMPLNN.query_weights (models/deformer/rigid.py:41-47: pytorch3d knn_points(xyz, smpl_verts, K = 1) + gather of the
+// vertex skinning weights).  Exact brute force: a thread owns a Gaussian, the 6890 vertices stream through shared memory in
+// tiles; squared distance dx*dx + dy*dy + dz*dz in FP32, ties resolved to the lowest vertex index (first minimum).
+namespace {
+constexpr int NN_TILE = 1024;
+__global__ void __launch_bounds__(256)
+smpl_nn_kernel(int P, const float* __restrict__ xyz, int V, const float* __restrict__ verts, const float* __restrict__ vert_weights,
+               int32_t* __restrict__ idx_out, float* __restrict__ weights_out) {
+  __shared__ float s_v[NN_TILE * 3];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = i < P;
+  const float x = live ? xyz[3 * (size_t)i] : 0.f, y = live ? xyz[3 * (size_t)i + 1] : 0.f, z = live ? xyz[3 * (size_t)i + 2] : 0.f;
+  float best = 3.0e38f;
+  int best_j = 0;
+  for (int v0 = 0; v0 < V; v0 += NN_TILE) {
+    const int n = min(NN_TILE, V - v0);
+    __syncthreads();
+    for (int k = threadIdx.x; k < n * 3; k += blockDim.x) s_v[k] = verts[(size_t)v0 * 3 + k];
+    __syncthreads();
+#pragma unroll 4
+    for (int j = 0; j < n; j++) {
+      const float dx = x - s_v[3 * j], dy = y - s_v[3 * j + 1], dz = z - s_v[3 * j + 2];
+      const float d = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+      if (d < best) { best = d; best_j = v0 + j; }  // strict: the first minimum wins
+    }
+  }
+  if (!live) return;
+  if (idx_out) idx_out[i] = best_j;
+  if (weights_out) {
+    const float4* src = reinterpret_cast<const float4*>(vert_weights + (size_t)best_j * 24);
+    float4* dst = reinterpret_cast<float4*>(weights_out + (size_t)i * 24);
+#pragma unroll
+    for (int k = 0; k < 6; k++) dst[k] = __ldg(src + k);
+  }
+}
+}  // namespace
+
+extern "C" int smpl_nn_forward(int32_t P, const float* xyz, int32_t V, const float* verts, const float* vert_weights,
+                               int32_t* idx_out, float* weights_out, void* stream) {
+  if (P < 0 || V <= 0 || !xyz || !verts || (weights_out && !vert_weights) || (!idx_out && !weights_out)) return GS_ERR_BAD_ARG;
+  if (P == 0) return GS_OK;
+  smpl_nn_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream>>>(P, xyz, V, verts, vert_weights, idx_out, weights_out);
   return gs_check(cudaGetLastError());
 }

@@ -241,6 +241,56 @@ class HotPath:
         return self.forward(f)[0]
 
 
+def default_config_step(hp, g, frame, f, GraphedStep, flush, dev, eager, n_steps):
+    """fwd+bwd of the reference's default model (configs/config.yaml: non_rigid hashgrid, rigid skinning_field, texture shallow_mlp,
+    use_sh false / 32 features per Gaussian, return_opacity + L1 mask loss) through FusedGaussianConverter + the rasterizer."""
+    import types
+    from avatar_pose.modules import FusedGaussianConverter
+    from avatar_pose.nonrigid import HashGridMLPFused
+    from avatar_pose.skinning import SkinningFieldFused
+    from avatar_pose.texture import ColorMLPFused
+    from avatar_pose.pose_encoder import HierarchicalPoseEncoderFused
+    P = hp.P
+    torch.manual_seed(0)
+    gm = types.SimpleNamespace(active_sh_degree=0, max_sh_degree=0)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    for k in ("xyz", "rotation", "scaling", "opacity"):
+        setattr(gm, "_" + k, t(g[k]).requires_grad_(True))
+    gm._features_dc = (0.5 * torch.randn(P, 1, 1, device=dev)).requires_grad_(True)   # gaussian_model.py:182: [P, feature_dim, 1]
+    gm._features_rest = (0.5 * torch.randn(P, 31, 1, device=dev)).requires_grad_(True)
+    lo, hi = (g["xyz"].min(0) - 0.05).tolist(), (g["xyz"].max(0) + 0.05).tolist()
+    nr = HashGridMLPFused(n_cond=144, feature_dim=16, aabb_min=lo, aabb_max=hi, delay=0)
+    with torch.no_grad():
+        nr.lin3.weight.mul_(0.01)  # small initial deformation, like the reference's last_layer_init
+    conv = FusedGaussianConverter(SkinningFieldFused(aabb_min=lo, aabb_max=hi), nr, HierarchicalPoseEncoderFused(),
+                                  texture=ColorMLPFused(n_frames=8)).to(dev).eval()
+    params = [p for p in conv.parameters()] + [getattr(gm, "_" + k) for k in ("xyz", "rotation", "scaling", "opacity", "features_dc", "features_rest")]
+    rots, Jtrs = t(frame["pose"]["rots"]), t(frame["pose"]["Jtrs"])
+
+    def step():
+        for p in params:
+            p.grad = None
+        camera = types.SimpleNamespace(bone_transforms=f["bones"], camera_center=f["campos"], rots=rots, Jtrs=Jtrs, latent_idx=3)
+        deformed, loss_reg, colors = conv(gm, camera, 100)
+        rs = hp.Settings(hp.H, hp.W, f["tanx"], f["tany"], hp.bg, 1.0, f["view"], f["proj"], 0, f["campos"], False, False)
+        means2D = torch.zeros_like(deformed.get_xyz, requires_grad=True)
+        img, radii, opim = hp.Rasterizer(rs)(means3D=deformed.get_xyz, means2D=means2D, opacities=deformed.get_opacity,
+                                             colors_precomp=colors, cov3D_precomp=deformed.get_covariance(1.0), return_opacity=True)
+        loss = hp.l1_loss(img, f["target"]) + 0.1 * hp.l1_loss(opim, f["target"][:1])
+        loss.backward()
+        return loss
+
+    fn = step if eager else GraphedStep(step).replay
+    ms = float(np.mean(time_steps(fn, n_steps, 3, flush, dev)))
+    loss = float(fn().item())
+    grads_ok = all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in params if p is not conv.texture.latent.weight)
+    return {"ms_per_step": ms, "iter_s": 1e3 / ms, "loss": loss, "all_parameters_receive_finite_gradients": grads_ok,
+            "what": "fwd+bwd of the reference's default configuration at cfg-A size: hash-grid non-rigid MLP -> skinning-field MLP -> fused "
+                    "posing -> colour MLP -> rasterizer with fused opacity pass -> L1 + mask loss; the three MLP stages run hand-written "
+                    "tcgen05 forward AND backward kernels (no torch / cuBLAS on the path); the pose encoder's batch-1 backward is a torch "
+                    "re-evaluation"}
+
+
 def time_steps(fn, steps, warmup, flush, dev, drain=None):
     """Per-step CUDA-event timing on the current stream with an L2 flush (outside the events) before every step.
     `drain` (pipelined end-to-end legs): completes whatever the last step left in flight, INSIDE its timed region."""
@@ -717,6 +767,15 @@ def ours_main(args):
                                  "vs torch.optim.Adam(capturable) + the reference's torch statements, both around this library's hot path"}
         except Exception as ex:  # informational leg
             full_iter = {"unavailable": str(ex)[:300]}
+    # The reference's DEFAULT configuration (configs/config.yaml:1-9): hashgrid non-rigid + skinning_field + shallow colour MLP +
+    # return_opacity mask loss -- every stage hand-written (tcgen05 forward and backward of the three MLPs), one training step
+    default_step = None
+    if world == 1:
+        try:
+            default_step = default_config_step(hp, g, frames[rank], f_static if not eager else f_dev, GraphedStep, flush, dev, eager,
+                                               max(args.steps // 2, 5))
+        except Exception as ex:  # informational leg
+            default_step = {"unavailable": str(ex)[:300]}
     if symm_slab is not None:
         torch.cuda.synchronize(dev)
         symm_slab.check()  # raises if an in-kernel cross-rank barrier gave up
@@ -810,7 +869,7 @@ def ours_main(args):
                            "d2h_bytes_per_step": 3 * H * W * 4},
             "eager_ms_per_step": ms_eager, "ms_per_step_hot_l2": float(np.mean(hot)), "ms_per_step_p10_p90": [float(np.percentile(ts_train, 10)), float(np.percentile(ts_train, 90))],
             "gpu_launches": launches, "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": fp32_peak,
-            "cpu_baseline": cpu, "ref_cuda": ref_cuda, "return_opacity_step": mask_pass, "full_iteration": full_iter, "clocks": sampler.summary(), "regrows": _C.stats["capacity_regrows"]}
+            "cpu_baseline": cpu, "ref_cuda": ref_cuda, "return_opacity_step": mask_pass, "full_iteration": full_iter, "default_config_step": default_step, "clocks": sampler.summary(), "regrows": _C.stats["capacity_regrows"]}
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)

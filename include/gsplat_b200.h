@@ -167,6 +167,8 @@ typedef struct PoseArgs {
   float* opacity_out; /* [P] sigmoid */
   float* T_fwd;     /* [P,16] or NULL */
   float* rotation_bar; /* [P,9] or NULL */
+  const float* view_noise; /* [9] row-major 3x3 or NULL: training-time view augmentation of SH2RGB (texture.py:28-33), applied to the
+                            * canonical view direction as dir @ view_noise; only with cano_view_dir */
 } PoseArgs;
 
 typedef struct PoseBackwardArgs {
@@ -189,6 +191,13 @@ typedef struct PoseBackwardArgs {
 
 int pose_forward(const PoseArgs* args, void* stream);
 int pose_backward(const PoseBackwardArgs* args, void* stream);
+
+/* smpl_nn skinning weights: index of the nearest of the V (6890) SMPL vertices per Gaussian and the gather of that vertex's
+ * 24 skinning weights.  Replaces SMPLNN.query_weights, models/deformer/rigid.py:41-47 (pytorch3d knn_points K = 1, P x V).
+ * Exact brute force in FP32 (dx*dx + dy*dy + dz*dz), the first minimum wins.  `idx_out` [P] and `weights_out` [P,24] may each
+ * be NULL; `vert_weights` [V,24] is needed for weights_out. */
+int smpl_nn_forward(int32_t P, const float* xyz, int32_t V, const float* verts, const float* vert_weights, int32_t* idx_out,
+                    float* weights_out, void* stream);
 
 /* ---- non-rigid deformation: multiresolution hash grid + conditional MLP (forward) ----
  * Replaces HashGridwithMLP.forward, models/deformer/non_rigid.py:226-286: AABB.normalize (utils/dataset_utils.py:66-76),

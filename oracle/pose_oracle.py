@@ -102,23 +102,26 @@ def covariance(rotation_bar, scaling_log, scaling_modifier=1.0):
     return torch.stack([cov[:, 0, 0], cov[:, 0, 1], cov[:, 0, 2], cov[:, 1, 1], cov[:, 1, 2], cov[:, 2, 2]], dim=-1)
 
 
-def sh2rgb(features, x_bar, T_fwd, camera_center, active_sh_degree, cano_view_dir=True):
-    """models/texture/texture.py:21-38 (eval mode: no view noise).  features [P,16,3].
+def sh2rgb(features, x_bar, T_fwd, camera_center, active_sh_degree, cano_view_dir=True, view_noise=None):
+    """models/texture/texture.py:21-38.  features [P,16,3].  `view_noise` [3,3] (training mode, :28-33): the matrix the canonical
+    view direction is multiplied with (augm_rots(...).T), None in eval mode.
     T_fwd is used detached, as set_fwd_transform(T_fwd.detach()) rigid.py:223."""
     shs_view = features.transpose(1, 2).reshape(features.shape[0], 3, -1)
     dir_pp = x_bar - camera_center.reshape(1, 3)
     if cano_view_dir:
         R_bwd = T_fwd.detach()[:, :3, :3].transpose(1, 2)
         dir_pp = torch.matmul(R_bwd, dir_pp.unsqueeze(-1)).squeeze(-1)
+        if view_noise is not None:
+            dir_pp = torch.matmul(dir_pp, view_noise.to(dir_pp.dtype))
     dir_n = dir_pp / (dir_pp.norm(dim=1, keepdim=True) + 1e-12)
     return torch.clamp_min(eval_sh(active_sh_degree, shs_view, dir_n) + 0.5, 0.0)
 
 
 def pose_forward(xyz, rotation, scaling, opacity, features, pts_W, bone_transforms, camera_center,
-                 active_sh_degree=3, scaling_modifier=1.0, cano_view_dir=True):
+                 active_sh_degree=3, scaling_modifier=1.0, cano_view_dir=True, view_noise=None):
     """The whole rigid posing stage (config 1 of BASELINE.json): what gaussian_renderer/__init__.py:73-129
     hands to the rasterizer.  Returns dict(means3D, cov3D, colors, opacity, T_fwd, rotation_bar)."""
     T_fwd, x_bar, R_bar = lbs(xyz, rotation, pts_W, bone_transforms)
     cov = covariance(R_bar, scaling, scaling_modifier)
-    col = sh2rgb(features, x_bar, T_fwd, camera_center, active_sh_degree, cano_view_dir)
+    col = sh2rgb(features, x_bar, T_fwd, camera_center, active_sh_degree, cano_view_dir, view_noise)
     return dict(means3D=x_bar, cov3D=cov, colors=col, opacity=torch.sigmoid(opacity), T_fwd=T_fwd, rotation_bar=R_bar)

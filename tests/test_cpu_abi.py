@@ -45,7 +45,7 @@ def test_struct_layout_matches_header(built_lib):
     # 10 x 4-byte scalars + 14 pointers / 9 scalars (+pad) + 22 pointers / 5 scalars (+pad) + 15 pointers
     assert ctypes.sizeof(_C.GsForwardArgs) == 40 + 14 * 8
     assert ctypes.sizeof(_C.GsBackwardArgs) == 40 + 22 * 8
-    assert ctypes.sizeof(avatar_pose.PoseArgs) == 24 + 15 * 8
+    assert ctypes.sizeof(avatar_pose.PoseArgs) == 24 + 16 * 8
     assert ctypes.sizeof(avatar_pose.PoseBackwardArgs) == ctypes.sizeof(avatar_pose.PoseArgs) + 12 * 8
     # and against the library itself
     from avatar_pose.nonrigid import NonRigidArgs, NonRigidBackwardArgs

@@ -177,3 +177,31 @@ def test_converter_default_config_mlp_texture_and_mask(built_lib):
             continue
         assert p.grad is not None and torch.isfinite(p.grad).all() and float(p.grad.abs().max()) > 0, name
     assert float(screenspace.grad.abs().max()) > 0
+
+
+def test_smpl_nn_kernel_exact_nearest_vertex(built_lib):
+    """smpl_nn_forward (rigid.py:41-47: knn_points K = 1 over the 6890 SMPL vertices) at the bench size: the chosen vertex is
+    the fp64 argmin, except where two vertices are equidistant within FP32 rounding (then the chosen one is as near as the
+    best within 1e-6 relative); duplicated vertices resolve to the lowest index; the gathered weights are that vertex's."""
+    from avatar_pose.modules import SMPLNNFused
+    dev = torch.device("cuda:0")
+    P, V = 50000, 6890
+    g = synth.canonical_gaussians(P, seed=0)
+    rng = np.random.default_rng(9)
+    verts = g["xyz"][rng.choice(P, V, replace=False)] + rng.normal(0, 0.004, size=(V, 3)).astype(np.float32)
+    verts[4000] = verts[17]  # an exact duplicate: index 17 must win
+    vw = synth.skinning_weights(verts)
+    m = SMPLNNFused(verts, vw).to(dev)
+    w, idx = m.query_weights(torch.from_numpy(g["xyz"]).to(dev), return_index=True)
+    idx = idx.cpu().numpy().astype(np.int64)
+    x64, v64 = g["xyz"].astype(np.float64), verts.astype(np.float64)
+    best = np.empty(P, np.int64)
+    for s in range(0, P, 5000):
+        best[s:s + 5000] = ((x64[s:s + 5000, None, :] - v64[None]) ** 2).sum(-1).argmin(1)
+    d_got = ((x64 - v64[idx]) ** 2).sum(1)
+    d_best = ((x64 - v64[best]) ** 2).sum(1)
+    differ = idx != best
+    assert differ.mean() < 1e-3, f"{differ.sum()} indices differ from the fp64 argmin"
+    assert np.all(d_got[differ] <= d_best[differ] * (1 + 1e-6) + 1e-14)
+    assert not np.any(idx == 4000)
+    assert torch.equal(w.cpu(), torch.from_numpy(vw)[torch.from_numpy(idx)])

@@ -83,3 +83,33 @@ def test_pose_forward_backward(built_lib, deg, cano, mod, P):
         assert rel(d[k].grad.cpu(), leaf[k].grad) <= 1e-4, k
     # bone transforms (the gradient a per-frame pose correction receives): rows 0..2 of every 4x4; the bottom row is a constant
     assert rel(d["bones"].grad.cpu()[:, :3, :], leaf["bones"].grad[:, :3, :]) <= 1e-4, "bone_transforms"
+
+
+def test_pose_view_noise_training_mode(built_lib):
+    """SH2RGB's training-time view augmentation (texture.py:28-33): fused_pose(view_noise=R) against the oracle with the same
+    matrix, forward <= 1e-5, gradients <= 1e-4; sample_view_noise restates augm_rots(...).T (a rotation; pitch in [0, scale])."""
+    from avatar_pose import fused_pose
+    from avatar_pose.modules import sample_view_noise
+    dev = torch.device("cuda:0")
+    P = 4000
+    t = _inputs(P)
+    np.random.seed(3)
+    vn = sample_view_noise(45.0)
+    assert float((vn @ vn.T - torch.eye(3)).abs().max()) <= 1e-6 and abs(float(torch.det(vn)) - 1) <= 1e-6
+    gen = torch.Generator().manual_seed(5)
+    gcol = torch.randn(P, 3, generator=gen)
+    d = {k: v.to(dev).requires_grad_(k not in ("bones", "cam")) for k, v in t.items()}
+    col = fused_pose(d["xyz"], d["rotation"], d["scaling"], d["opacity"], d["features_dc"], d["features_rest"], d["weights"], d["bones"],
+                     d["cam"], 3, 1.0, True, view_noise=vn.to(dev))[2]
+    (col * gcol.to(dev)).sum().backward()
+    leaf = {k: v.double().clone().requires_grad_(k not in ("bones", "cam")) for k, v in t.items()}
+    feat = torch.cat([leaf["features_dc"], leaf["features_rest"]], 1)
+    o = pose_oracle.pose_forward(leaf["xyz"], leaf["rotation"], leaf["scaling"], leaf["opacity"], feat, leaf["weights"], leaf["bones"],
+                                 leaf["cam"], 3, 1.0, True, view_noise=vn.double())
+    (o["colors"] * gcol.double()).sum().backward()
+    assert float((col.detach().cpu().double() - o["colors"].detach()).abs().max()) <= 1e-5
+    o_plain = pose_oracle.pose_forward(leaf["xyz"], leaf["rotation"], leaf["scaling"], leaf["opacity"], feat, leaf["weights"],
+                                       leaf["bones"], leaf["cam"], 3, 1.0, True)
+    assert float((o["colors"] - o_plain["colors"]).abs().max()) > 1e-3  # the noise does something
+    for k in ("xyz", "features_dc", "features_rest"):
+        assert rel(d[k].grad.cpu(), leaf[k].grad) <= 1e-4, k
