@@ -62,6 +62,7 @@ class ColorMLPFused(nn.Module):
         if latent_dim > 0:
             self.latent = nn.Embedding(n_frames, latent_dim)  # texture.py:66-67
         self._ws = None
+        self._idx_cache = {}
 
     def params(self):
         return [t for l in range(3) for t in (getattr(self, f"lin{l}").weight, getattr(self, f"lin{l}").bias)]
@@ -69,7 +70,10 @@ class ColorMLPFused(nn.Module):
     def latent_code(self, latent_idx):
         if self.latent_dim == 0:
             return None
-        idx = torch.as_tensor([min(int(latent_idx), self.latent.num_embeddings - 1)], device=self.latent.weight.device)
+        i, dev = min(int(latent_idx), self.latent.num_embeddings - 1), self.latent.weight.device
+        idx = self._idx_cache.get((i, dev))  # device-resident index: a host -> device copy here could not be graph-captured
+        if idx is None:
+            idx = self._idx_cache[(i, dev)] = torch.full((1,), i, dtype=torch.long, device=dev)
         return self.latent(idx).reshape(-1)  # texture.py:107-114
 
     def _fill(self, a, features, xyz, T_fwd, camera_center, non_rigid_feature, latent, view_noise, keep):

@@ -34,17 +34,24 @@ int gs_check(cudaError_t e) {
 // ---- optional per-stage timing (bench.py's roofline leg): CUDA events on the launching stream ----
 enum { ST_PRE = 0, ST_BIN, ST_BLEND_F, ST_BLEND_B, ST_PRE_B, ST_POSE_F, ST_POSE_B, ST_COUNT };
 static int g_prof_on = 0;
-static cudaEvent_t g_ev[ST_COUNT][2];
-static int g_ev_valid[ST_COUNT];
-static int g_ev_init = 0;
+constexpr int GS_MAX_DEV = 64;
+struct ProfDev { cudaEvent_t ev[ST_COUNT][2]; int valid[ST_COUNT]; int init; };
+static ProfDev g_prof[GS_MAX_DEV];  // events belong to the device that was current when they were created: one set per device
+static ProfDev* prof_dev() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= GS_MAX_DEV) return nullptr;
+  return &g_prof[dev];
+}
 void gs_prof_mark(int stage, int end, cudaStream_t st) {
   if (!g_prof_on) return;
-  if (!g_ev_init) {
-    for (int i = 0; i < ST_COUNT; i++) { cudaEventCreate(&g_ev[i][0]); cudaEventCreate(&g_ev[i][1]); g_ev_valid[i] = 0; }
-    g_ev_init = 1;
+  ProfDev* p = prof_dev();
+  if (!p) return;
+  if (!p->init) {
+    for (int i = 0; i < ST_COUNT; i++) { cudaEventCreate(&p->ev[i][0]); cudaEventCreate(&p->ev[i][1]); p->valid[i] = 0; }
+    p->init = 1;
   }
-  cudaEventRecord(g_ev[stage][end], st);
-  if (end) g_ev_valid[stage] = 1;
+  cudaEventRecord(p->ev[stage][end], st);
+  if (end) p->valid[stage] = 1;
 }
 
 static int debug_sync(int debug, cudaStream_t st) {
@@ -212,11 +219,12 @@ int gs_read_counters(const void* geom, uint64_t* counters_host, void* stream) {
 /* ms[7] = preprocess, binning (sorts+emit+ranges), blend fwd, blend bwd, preprocess bwd, pose fwd, pose bwd of the LAST call
  * (-1 where no stage was recorded).  Synchronises on the recorded events. */
 int gs_profile_read(float* ms_host) {
+  ProfDev* p = prof_dev();  // the CURRENT device's events
   for (int i = 0; i < ST_COUNT; i++) {
     ms_host[i] = -1.f;
-    if (g_ev_init && g_ev_valid[i]) {
-      if (cudaEventSynchronize(g_ev[i][1]) != cudaSuccess) return GS_ERR_CUDA;
-      if (cudaEventElapsedTime(&ms_host[i], g_ev[i][0], g_ev[i][1]) != cudaSuccess) return GS_ERR_CUDA;
+    if (p && p->init && p->valid[i]) {
+      if (cudaEventSynchronize(p->ev[i][1]) != cudaSuccess) return GS_ERR_CUDA;
+      if (cudaEventElapsedTime(&ms_host[i], p->ev[i][0], p->ev[i][1]) != cudaSuccess) return GS_ERR_CUDA;
     }
   }
   return GS_OK;

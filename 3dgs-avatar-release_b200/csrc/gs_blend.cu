@@ -588,6 +588,9 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 #pragma unroll
   for (int b = 3; b >= 0; b--) {  // back to front
     uint32_t m = mine[b];
+    // a strip that has run out of entries (or holds an odd count) evaluates a STAGED entry of the batch with ok = false: an
+    // unstaged slot is whatever the previous kernel left in shared memory, and 0 * (NaN or inf) would reach the atomics
+    const int j_idle = mall[b] ? (__ffs(mall[b]) - 1) : 0;
     while (__any_sync(0xFFFFFFFFu, m != 0u)) {
       float v[16], v8[2];
       uint32_t ids[2];
@@ -595,7 +598,7 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 #pragma unroll
       for (int k = 0; k < 2; k++) {
         const bool valid = m != 0u;
-        const int j = valid ? (31 - __clz(m)) : 0;
+        const int j = valid ? (31 - __clz(m)) : j_idle;
         m &= ~(valid ? (1u << j) : 0u);
         const int e = b * 32 + j;
         ids[k] = sl.id[e];

@@ -317,8 +317,8 @@ static int color_forward_impl(const ColorArgs* args, void* workspace, size_t wor
   ClWs w;
   if (carve_cl((char*)workspace, &w) > workspace_bytes) return GS_ERR_WORKSPACE_SMALL;
   color_prep_kernel<<<16, 256, 0, st>>>(a, w);
-  static int sms = 0;
-  if (!sms) {
+  int sms = 0;
+  {  // per call: function attributes are per DEVICE, and one process may drive several
     if (gs_check(cudaFuncSetAttribute(color_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ClSmem) + 1024)) != GS_OK ||
         gs_check(cudaFuncSetAttribute(color_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ClSmem) + 1024)) != GS_OK)
       return GS_ERR_CUDA;

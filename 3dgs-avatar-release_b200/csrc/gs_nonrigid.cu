@@ -280,12 +280,9 @@ static int nonrigid_forward_impl(const NonRigidArgs* args, void* workspace, size
   if (carve_ws((char*)workspace, a.n_out, &w) > workspace_bytes) return GS_ERR_WORKSPACE_SMALL;
   const int npad = nout_pad(a.n_out);
   nr_prep_kernel<<<64, 256, 0, st>>>(a, w, npad);
-  static bool configured = false;
-  if (!configured) {
-    if (gs_check(cudaFuncSetAttribute(nr_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NrSmem) + 1024)) != GS_OK)
-      return GS_ERR_CUDA;
-    configured = true;
-  }
+  // per call: function attributes are per DEVICE, and one process may drive several
+  if (gs_check(cudaFuncSetAttribute(nr_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NrSmem) + 1024)) != GS_OK)
+    return GS_ERR_CUDA;
   nr_fwd_kernel<<<(a.P + NR_TILE - 1) / NR_TILE, NR_TILE, sizeof(NrSmem) + 1024, st>>>(a, w, npad, (__nv_bfloat16*)saved);
   return gs_check(cudaGetLastError());
 }
@@ -492,12 +489,9 @@ static int skinning_forward_impl(const SkinArgs* args, void* workspace, size_t w
   SkWs w;
   if (carve_sk((char*)workspace, &w) > workspace_bytes) return GS_ERR_WORKSPACE_SMALL;
   sk_prep_kernel_impl<<<64, 256, 0, st>>>(a, w);
-  static bool configured = false;
-  if (!configured) {
-    if (gs_check(cudaFuncSetAttribute(sk_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NrSmem) + 1024)) != GS_OK)
-      return GS_ERR_CUDA;
-    configured = true;
-  }
+  // per call: function attributes are per DEVICE, and one process may drive several
+  if (gs_check(cudaFuncSetAttribute(sk_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NrSmem) + 1024)) != GS_OK)
+    return GS_ERR_CUDA;
   sk_fwd_kernel<<<(a.P + NR_TILE - 1) / NR_TILE, NR_TILE, sizeof(NrSmem) + 1024, st>>>(a, w, (__nv_bfloat16*)saved);
   return gs_check(cudaGetLastError());
 }

@@ -658,15 +658,13 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   const int blocks_c = (P + GS_BIN_THREADS - 1) / GS_BIN_THREADS;
   if (gs_direct_binning(P, tiles, cap)) {
     // 2-4 (direct): count pairs per (block of 1024 Gaussians, tile), then place every pair; no pair sort
-    static bool attr_done = false;
     const size_t smem_c = (size_t)64 * tiles, smem_p = (size_t)68 * tiles;
-    if (!attr_done) {
+    {  // per call: function attributes are per DEVICE, and one process may drive several
       const int max_smem = 68 * GS_BIN_MAX_TILES;
       if (cudaFuncSetAttribute(bin_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess ||
           cudaFuncSetAttribute(bin_place_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess ||
           cudaFuncSetAttribute(bin_place_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess)
         return gs_check(cudaGetLastError());
-      attr_done = true;
     }
     uint32_t* blockcount = s.tkey[0];  // [blocks_c][tiles] <= cap words
     const bool fused = blocks_c <= GS_BIN_FUSED_MAX_BLOCKS;  // co-resident: one 1024-thread block per SM

@@ -55,6 +55,7 @@ def parse():
     ap.add_argument("--cpu-steps", type=int, default=3, help="steps of the cpu_baseline sample inside the ours arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--eager", action="store_true", help="time the eager Python path instead of CUDA-graph replay of the same step")
+    ap.add_argument("--no-stress", action="store_true", help="skip the 1M-Gaussian / 1080p stress leg (BASELINE.json configs[3])")
     ap.add_argument("--profile-only", action="store_true", help="run warmup+steps training steps and exit (for ncu)")
     return ap.parse_args()
 
@@ -130,6 +131,10 @@ class HotPath:
         self.weights = t(wts)
         self.bg = torch.zeros(3, device=dev)
         self.P = g["xyz"].shape[0]
+        # screenspace_points (gaussian_renderer/__init__.py:76-80) only receives a gradient: one persistent leaf instead of a
+        # zeros_like fill per step; `one` = the upstream gradient of the scalar loss (no ones_like fill either)
+        self.means2D = torch.zeros(self.P, 3, device=dev, requires_grad=True)
+        self.one = torch.ones((), device=dev)
 
     def frame_to_device(self, fr):
         t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(self.dev)
@@ -171,10 +176,7 @@ class HotPath:
         means, cov, col, op = self.fused_pose(p["xyz"], p["rotation"], p["scaling"], p["opacity"], p["features_dc"],
                                               p["features_rest"], self.weights, f["bones"], f["campos"], 3)
         rs = self.Settings(self.H, self.W, f["tanx"], f["tany"], self.bg, 1.0, f["view"], f["proj"], 3, f["campos"], False, False)
-        if torch.is_grad_enabled():
-            means2D = torch.zeros_like(means, requires_grad=True)  # screenspace_points, gaussian_renderer/__init__.py:76-80
-        else:
-            means2D = means
+        means2D = self.means2D if torch.is_grad_enabled() else means
         img, radii = self.Rasterizer(rs)(means3D=means, means2D=means2D, opacities=op, colors_precomp=col, cov3D_precomp=cov)
         return img, radii
 
@@ -231,9 +233,10 @@ class HotPath:
     def train_step(self, f):
         for v in self.params.values():
             v.grad = None
+        self.means2D.grad = None
         img, _ = self.forward(f)
         loss = self.l1_loss(img, f["target"])  # l1_loss, train.py:121 (fused forward + gradient kernel)
-        loss.backward()
+        loss.backward(self.one)
         return loss
 
     @torch.no_grad()
@@ -289,6 +292,105 @@ def default_config_step(hp, g, frame, f, GraphedStep, flush, dev, eager, n_steps
                     "posing -> colour MLP -> rasterizer with fused opacity pass -> L1 + mask loss; the three MLP stages run hand-written "
                     "tcgen05 forward AND backward kernels (no torch / cuBLAS on the path); the pose encoder's batch-1 backward is a torch "
                     "re-evaluation"}
+
+
+def render_sequence(hp, args, rank, world, dev, GraphedStep, eager, n_frames=64):
+    """SURVEY 8(d) metric 1 as the reference's render.py loop runs it: a 64-frame animation (slerp between seeded key poses, ring
+    camera), frames sharded f mod N over the ranks, every frame end to end -- H2D of its pose + camera from pinned memory, posing
+    + rasterizer forward, D2H of the image into pinned memory (double-buffered: the copy of frame k overlaps frame k+1).
+    Returns (frames of this rank, device milliseconds for them)."""
+    import synth
+    W, H = hp.W, hp.H
+    poses = synth.pose_sequence(n_frames, seed=11)
+    mine = list(range(rank, n_frames, world))
+    frames = [dict(cam=synth.camera(W=W, H=H, fx=537.0 * W / 512.0, fy=537.0 * H / 512.0, azimuth_deg=360.0 * f / n_frames),
+                   pose=poses[f], target=np.zeros((3, H, W), np.float32)) for f in mine]
+    smalls = torch.stack([hp.frame_to_pinned(fr)["small"] for fr in frames]).pin_memory()
+    statics = [hp.static_frame(frames[0]), hp.static_frame(frames[0])]
+    with torch.no_grad():  # untimed eager pass over the shard: sizes the pair capacity for the busiest frame before capture
+        for i in range(len(mine)):
+            statics[0]["small"].copy_(smalls[i], non_blocking=True)
+            hp.render(statics[0])
+    torch.cuda.synchronize(dev)
+    fns = [(lambda s=s: hp.render(s)) if eager else GraphedStep(lambda s=s: hp.render(s)).replay for s in statics]
+    pins = [torch.empty(3, H, W).pin_memory(), torch.empty(3, H, W).pin_memory()]
+    copy_stream = torch.cuda.Stream(dev)
+    main = torch.cuda.current_stream(dev)
+    done = [None, None]
+    checksum = 0.0
+
+    def run(timed):
+        nonlocal checksum
+        for i in range(len(mine)):
+            slot = i & 1
+            if done[slot] is not None:
+                main.wait_event(done[slot])          # this slot's previous image has left the device
+            statics[slot]["small"].copy_(smalls[i], non_blocking=True)
+            img = fns[slot]()
+            ev = torch.cuda.Event()
+            ev.record(main)
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(ev)
+                pins[slot].copy_(img, non_blocking=True)
+                d = torch.cuda.Event()
+                d.record(copy_stream)
+            done[slot] = d
+            if i and done[slot ^ 1] is not None:
+                done[slot ^ 1].synchronize()         # the caller holds frame i-1 in host memory
+                if timed:
+                    checksum += float(pins[slot ^ 1][0, H // 2, W // 2])
+        for d in done:
+            if d is not None:
+                main.wait_event(d)
+
+    run(False)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(main)
+    run(True)
+    e1.record(main)
+    torch.cuda.synchronize(dev)
+    return len(mine), e0.elapsed_time(e1), checksum
+
+
+def stress_step(dev, GraphedStep, eager, flush, n_steps, P=1_000_000, W=1920, H=1080):
+    """BASELINE.json configs[3]: 1M Gaussians at 1080p, fwd+bwd of posing + rasterizer.  The 50k avatar proxy is densified to
+    1M points in the same capsules (scales shrunk by the cube root of the density ratio, times 6 so that the screen footprint
+    stays a few pixels at 1080p from 3.5 m)."""
+    import synth
+    g = synth.canonical_gaussians(P, seed=5, random_init=True)
+    g = dict(g)
+    g["scaling"] = (g["scaling"] + np.log(6.0) - np.log(P / 50_000.0) / 3.0).astype(np.float32)
+    wts = synth.skinning_weights(g["xyz"])
+    hp = HotPath(dev, g, wts, W, H)
+    fr = dict(cam=synth.camera(W=W, H=H, fx=537.0 * H / 512.0, fy=537.0 * H / 512.0), pose=synth.pose(1), target=synth.l1_target(H, W, seed=2))
+    f = hp.static_frame(fr)
+    fn = (lambda: hp.train_step(f)) if eager else GraphedStep(lambda: hp.train_step(f)).replay
+    ms = float(np.mean(time_steps(fn, n_steps, 3, flush, dev)))
+    ms_r = float(np.mean(time_steps(lambda: hp.render(f), n_steps, 3, flush, dev)))
+    img, _ = hp.forward(f)
+    N = int(img.grad_fn.num_rendered)
+    return {"ms_per_step": ms, "iter_s": 1e3 / ms, "render_ms_eager": ms_r, "N_pairs": N, "P": P, "W": W, "H": H,
+            "what": "BASELINE.json configs[3] (stress: 1M Gaussians, 1920x1080, SH deg 3): fwd+bwd training step, one GPU"}
+
+
+def allreduce_check(symm_slab, n, dev):
+    """The hand-written NVLS all-reduce against NCCL on the same slab contents (one seeded pattern per rank)."""
+    import torch.distributed as dist
+    rank = dist.get_rank()
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    x = torch.randn(n, device=dev, generator=gen)
+    ref = x.clone()
+    dist.all_reduce(ref)
+    symm_slab.buf[:n].copy_(x)
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    symm_slab.all_reduce(n)
+    torch.cuda.synchronize(dev)
+    symm_slab.check()
+    err = (symm_slab.buf[:n] - ref).abs().max() / ref.abs().max()
+    dist.all_reduce(err, op=dist.ReduceOp.MAX)
+    return float(err.item())
 
 
 def time_steps(fn, steps, warmup, flush, dev, drain=None):
@@ -776,9 +878,36 @@ def ours_main(args):
                                                max(args.steps // 2, 5))
         except Exception as ex:  # informational leg
             default_step = {"unavailable": str(ex)[:300]}
+    # metric 1 as a job: a 64-frame animation rendered end to end, frames sharded over the ranks (all ranks take part)
+    render_seq = None
+    try:
+        if world > 1:
+            dist.barrier()
+        n_mine, ms_mine, chk = render_sequence(hp, args, rank, world, dev, GraphedStep, eager)
+        tot = torch.tensor([ms_mine], device=dev)
+        if world > 1:
+            dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+        _, over = _C.graph_overflow(dev) if not eager else (0, False)
+        render_seq = {"frames": 64, "ms_total_max_over_ranks": float(tot.item()), "frames_per_s": 64 * 1e3 / float(tot.item()),
+                      "pair_capacity_overflow": bool(over),
+                      "h2d_bytes_per_frame": 419 * 4, "d2h_bytes_per_frame": 3 * H * W * 4,
+                      "what": "render.py's loop: 64-frame slerp animation + ring camera, frame f on rank f mod N, per frame H2D pose+camera -> "
+                              "posing + rasterizer forward -> D2H image (pinned, double-buffered); no collective"}
+    except Exception as ex:  # informational leg
+        if world > 1:
+            raise
+        render_seq = {"unavailable": str(ex)[:300]}
+    stress = None
+    if world == 1 and not args.no_stress:
+        try:
+            stress = stress_step(dev, GraphedStep, eager, flush, 5)
+        except Exception as ex:  # informational leg
+            stress = {"unavailable": str(ex)[:300]}
+    ar_check = None
     if symm_slab is not None:
         torch.cuda.synchronize(dev)
         symm_slab.check()  # raises if an in-kernel cross-rank barrier gave up
+        ar_check = {"max_rel_err_vs_nccl": allreduce_check(symm_slab, 59 * P, dev)}
     if rank != 0:
         finish(world, dev, graphs_alive, symm_slab, sampler)
         return
@@ -869,7 +998,7 @@ def ours_main(args):
                            "d2h_bytes_per_step": 3 * H * W * 4},
             "eager_ms_per_step": ms_eager, "ms_per_step_hot_l2": float(np.mean(hot)), "ms_per_step_p10_p90": [float(np.percentile(ts_train, 10)), float(np.percentile(ts_train, 90))],
             "gpu_launches": launches, "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": fp32_peak,
-            "cpu_baseline": cpu, "ref_cuda": ref_cuda, "return_opacity_step": mask_pass, "full_iteration": full_iter, "default_config_step": default_step, "clocks": sampler.summary(), "regrows": _C.stats["capacity_regrows"]}
+            "cpu_baseline": cpu, "ref_cuda": ref_cuda, "return_opacity_step": mask_pass, "full_iteration": full_iter, "default_config_step": default_step, "render_seq64": render_seq, "stress_1m": stress, "allreduce_check": ar_check, "clocks": sampler.summary(), "regrows": _C.stats["capacity_regrows"]}
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)

@@ -66,12 +66,12 @@ def test_color_forward_variants(built_lib, cano, latent_dim, non_rigid_dim, sh_d
     assert float((col.double().cpu() - truth).abs().max()) <= COL_TOL
 
 
-def test_color_autograd_matches_oracle_autograd(built_lib):
+@pytest.mark.parametrize("P", [2000, 60000])  # 60 000 = 469 tiles: more than the 444 forward / 148 backward persistent CTAs
+def test_color_autograd_matches_oracle_autograd(built_lib, P):
     """Forward on the tensor cores, backward = the hand-written color_backward kernel: gradients against fp64 autograd of the
     oracle (which takes the LeakyReLU branch of every hidden unit from the implementation's saved activations: see
     tests/test_gpu_nonrigid.py), <= 1e-4 of each gradient's max."""
     dev = _dev()
-    P = 2000
     c = co.synthetic_case(P, seed=9)
     m = _module(c, dev)
     d = lambda t: t.to(dev).requires_grad_(True)

@@ -1,6 +1,7 @@
 """GPU test of the posing drop-in boundary: FusedGaussianConverter(gaussians, camera, iteration) against the oracle chain
 (1-NN skinning weights -> pose oracle), then the deformed set drives the drop-in rasterizer exactly as
 gaussian_renderer/__init__.py:100-129 does."""
+import os
 import types
 
 import numpy as np
@@ -205,3 +206,18 @@ def test_smpl_nn_kernel_exact_nearest_vertex(built_lib):
     assert np.all(d_got[differ] <= d_best[differ] * (1 + 1e-6) + 1e-14)
     assert not np.any(idx == 4000)
     assert torch.equal(w.cpu(), torch.from_numpy(vw)[torch.from_numpy(idx)])
+
+
+@pytest.mark.parametrize("variant,mode", [("nr", "eager"), ("sk", "eager"), ("nr+sk+tex+enc", "eager"), ("nr+sk+tex+enc", "graph")])
+def test_chain_fwd_bwd_at_bench_size(built_lib, variant, mode):
+    """fwd+bwd of the converter chain + rasterizer at the bench size (50 000 Gaussians, 512x512), stage subsets included: the
+    tcgen05 kernels run right before the blend kernels here and leave BF16 patterns in shared memory -- the backward blend once
+    evaluated unstaged shared-memory slots for a strip that had run out of entries, and 0 * NaN reached its atomics (an illegal
+    address at this size only).  Separate process: a device fault must not take the rest of the suite down.
+    `graph`: the whole default-configuration step is captured in one CUDA graph (no host <-> device copy may occur inside it)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "profiles", "default_chain_run.py"), "50000", "512", "3", mode, variant],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "CHAIN OK" in r.stdout and "finite=True" in r.stdout, (r.stdout[-500:], r.stderr[-1500:])

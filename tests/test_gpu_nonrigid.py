@@ -105,7 +105,8 @@ def saved_masks(saved, P, in_cols, n_layers):
     return out
 
 
-def test_nonrigid_and_skinning_gradients(built_lib):
+@pytest.mark.parametrize("P", [3000, 50000])  # 50 000 = 391 tiles on 148 persistent CTAs: every CTA walks several tiles
+def test_nonrigid_and_skinning_gradients(built_lib, P):
     """deform_autograd / query_weights_autograd: forward values from the tcgen05 kernels, gradients (inputs, hash table,
     linear layers) from the hand-written backward kernels (nonrigid_backward / skinning_backward) against fp64 autograd of
     the oracle, <= 1e-4 of each gradient's max (north_star's gradient tolerance).  The oracle takes the LeakyReLU branch
@@ -117,7 +118,6 @@ def test_nonrigid_and_skinning_gradients(built_lib):
     from avatar_pose.skinning import SkinningFieldFused
     dev = torch.device("cuda:0")
     torch.manual_seed(11)
-    P = 3000
     g = synth.canonical_gaussians(P, seed=2)
     xyz, sc, rot = (torch.from_numpy(g[k]) for k in ("xyz", "scaling", "rotation"))
     lo, hi = xyz.min(0).values - 0.05, xyz.max(0).values + 0.05
@@ -152,15 +152,17 @@ def test_nonrigid_and_skinning_gradients(built_lib):
         a, b = a.detach().cpu().double(), b.detach().double()
         s = float(b.abs().max())
         assert s > 0, name
-        err = (a - b).abs().flatten()
-        report[name] = (float(err.max()) / s, float(err.quantile(0.995)) / s)
-        print(f"GRAD {name}: max {float(err.max()) / s:.3e} q99.5 {float(err.quantile(0.995)) / s:.3e}")
-        return
-        if robust:  # d(feature)/d(position) is piecewise constant per cell: an FP32 position within ~1e-4 cells of a cell
-            # face of the finest levels (scale 2047) falls into the neighbouring cell of the fp64 oracle
-            assert float(err.quantile(0.995)) <= 2e-3 * s and float(err.max()) <= 5e-2 * s, (name, float(err.max()), s)
-        else:
-            assert float(err.max()) <= 2e-3 * s, (name, float(err.max()), s)
+        err = (a - b).abs()
+        flat = err.flatten()
+        # share of outliers in the worst tile of 128 Gaussians (per-Gaussian tensors): a wrong TILE would be 100 % there while
+        # staying below the 99.5 % quantile of a 391-tile tensor
+        worst_tile = 0.0
+        if err.dim() == 2 and err.shape[0] == P:
+            bad_rows = (err > 1e-3 * s).any(1).float()
+            pad = (-P) % 128
+            worst_tile = float(torch.nn.functional.pad(bad_rows, (0, pad)).view(-1, 128).mean(1).max())
+        report[name] = (float(flat.max()) / s, float(flat.quantile(0.995)) / s, worst_tile)
+        print(f"GRAD {name}: max {float(flat.max()) / s:.3e} q99.5 {float(flat.quantile(0.995)) / s:.3e} worst-tile outliers {worst_tile:.3f}")
 
     for a, b, name in zip(ins, r_in[:4], ("xyz", "scaling", "rotation", "cond")):
         close(a.grad, b.grad, name, robust=(name == "xyz"))
@@ -190,6 +192,8 @@ def test_nonrigid_and_skinning_gradients(built_lib):
     for l in range(5):
         close(getattr(sd, f"lin{l}").weight.grad, sW[l].grad, f"skin W{l}")
         close(getattr(sd, f"lin{l}").bias.grad, sb[l].grad, f"skin b{l}")
+    # cell-face outliers of the piecewise-constant position gradient are isolated Gaussians (a handful among 50 000, each off
+    # by O(1) of the local gradient): judged on the quantile + no tile with more than a few of them
     bad = {k: v for k, v in report.items()
-           if ((v[1] > 1e-4 or v[0] > 5e-2) if k in ("xyz", "table", "skin xyz") else v[0] > 1e-4)}
+           if ((v[1] > 1e-4 or v[2] > 0.05) if k in ("xyz", "table", "skin xyz") else v[0] > 1e-4)}
     assert not bad, bad
