@@ -2,6 +2,8 @@
 // forward and the per-pixel gradient in ONE pass over the two images: the PyTorch chain (sub, abs, mean; backward: fill,
 // expand/div, sign, mul) is seven launches and six image-sized round trips through HBM per step.  The sum is
 // deterministic: per-block partials, the last block to finish adds them in block order.
+#include <atomic>
+
 #include "gs_common.cuh"
 
 namespace {
@@ -91,6 +93,58 @@ int l1_loss_forward(const float* image, const float* target, int64_t n, float* l
   unsigned int* ticket = (unsigned int*)(partial + GS_L1_MAX_BLOCKS);  // zero on first use (caller), self-resetting after
   gs_launch(l1_loss_kernel, dim3(l1_blocks(n)), dim3(L1_THREADS), 0, (cudaStream_t)stream, image, target, (long long)n,
             1.0f / (float)n, loss, dL_dimage, partial, ticket);
+  return gs_check(cudaGetLastError());
+}
+
+/* No-allocation variant of l1_loss_forward (no counterpart in the reference; added for
+ * callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The
+ * kernel's scratch -- one partial sum per block + the completion ticket -- lives in the file-scope device array below instead
+ * of a caller workspace: (GS_L1_MAX_BLOCKS + 1) words = 2372 bytes, held by every GPU that loads the library until exit.
+ * Limit: n <= L1_STATIC_MAX_N = 2^26 elements (a 3 x 4096 x 4096 image is 50.3 M); larger -> GS_ERR_STATIC_LIMIT.
+ * Every call on a device shares the one array and finds the previous call's contents in it: the ticket word is cleared on the
+ * stream before every launch (the partials are overwritten before they are read).  Calls that overlap on the GPU (two streams,
+ * or two host threads on one device) RACE on it -- serialise them.  Calls cudaGetSymbolAddress once per device (no allocation),
+ * cudaMemsetAsync and the kernel launch; no cudaMalloc / cudaFree / allocating library routine. */
+}  // extern "C"
+
+namespace {
+constexpr long long L1_STATIC_MAX_N = 1ll << 26;
+constexpr int L1_STATIC_MAX_DEV = 64;
+static __device__ __align__(256) float g_l1_static_scratch[GS_L1_MAX_BLOCKS + 1];
+// In HOST code the array's name is only a stand-in: the device address comes from cudaGetSymbolAddress, per device (each GPU
+// that loaded the module holds its own copy), taken once with that device current.
+std::atomic<float*> g_l1_static_ptr[L1_STATIC_MAX_DEV];
+
+int l1_static_scratch(float** out) {
+  int dev = -1;
+  if (gs_check(cudaGetDevice(&dev)) != GS_OK) return GS_ERR_CUDA;
+  if (dev < 0 || dev >= L1_STATIC_MAX_DEV) return GS_ERR_BAD_ARG;
+  float* p = g_l1_static_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    if (gs_check(cudaGetSymbolAddress((void**)&p, g_l1_static_scratch)) != GS_OK || !p) return GS_ERR_CUDA;
+    g_l1_static_ptr[dev].store(p, std::memory_order_release);  // racing first calls store the same address
+  }
+  *out = p;
+  return GS_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int64_t l1_loss_static_max_n(void) { return (int64_t)L1_STATIC_MAX_N; }
+
+int l1_loss_forward_static(const float* image, const float* target, int64_t n, float* loss, float* dL_dimage, void* stream) {
+  if (!image || !target || !loss || !dL_dimage || n <= 0) return GS_ERR_BAD_ARG;
+  if (n > L1_STATIC_MAX_N) return GS_ERR_STATIC_LIMIT;
+  if (((uintptr_t)image | (uintptr_t)target | (uintptr_t)dL_dimage) & 15) return GS_ERR_BAD_ARG;
+  float* partial = nullptr;
+  const int s = l1_static_scratch(&partial);
+  if (s != GS_OK) return s;
+  unsigned int* ticket = (unsigned int*)(partial + GS_L1_MAX_BLOCKS);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (gs_check(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st)) != GS_OK) return GS_ERR_CUDA;  // must start at zero
+  gs_launch(l1_loss_kernel, dim3(l1_blocks(n)), dim3(L1_THREADS), 0, st, image, target, (long long)n, 1.0f / (float)n, loss,
+            dL_dimage, partial, ticket);
   return gs_check(cudaGetLastError());
 }
 

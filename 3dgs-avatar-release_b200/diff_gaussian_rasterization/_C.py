@@ -100,7 +100,8 @@ class GsError(RuntimeError):
     pass
 
 
-_STATUS = {-1: "bad argument", -2: "workspace too small", -3: "CUDA error", -4: "For non-RGB, provide precomputed Gaussian colors!"}
+_STATUS = {-1: "bad argument", -2: "workspace too small", -3: "CUDA error", -4: "For non-RGB, provide precomputed Gaussian colors!",
+           -5: "size exceeds the limit of the built-in static scratch"}
 
 
 def _check(status, what):

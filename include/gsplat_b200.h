@@ -42,6 +42,7 @@ extern "C" {
 #define GS_ERR_WORKSPACE_SMALL (-2) /* a caller buffer is smaller than gs_*_bytes() says */
 #define GS_ERR_CUDA (-3)           /* a CUDA call failed; gs_last_cuda_error() has the code */
 #define GS_ERR_NON_RGB (-4)        /* rasterizer_impl.cu:242-245 */
+#define GS_ERR_STATIC_LIMIT (-5)   /* l1_loss_forward_static: n exceeds l1_loss_static_max_n() (the built-in scratch limit) */
 
 typedef struct GsForwardArgs {
   int32_t P;             /* number of Gaussians */
@@ -459,6 +460,17 @@ size_t l1_loss_workspace_bytes(void);
 int l1_loss_forward(const float* image, const float* target, int64_t n, float* loss, float* dL_dimage, void* workspace,
                     size_t workspace_bytes, void* stream);
 int l1_loss_backward(const float* dL_dimage_unit, const float* dL_dloss, int64_t n, float* dL_dimage, void* stream);
+/* l1_loss_forward without a caller workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and results as l1_loss_forward; the kernel's scratch (per-block partial sums + the
+ * completion ticket, 2372 bytes) is a file-scope `static __device__` array inside the library, which every GPU that loads the
+ * library holds until exit.  Limit: n <= l1_loss_static_max_n() = 2^26 elements, beyond that GS_ERR_STATIC_LIMIT and nothing is
+ * launched.  All calls on a device share that one array (it keeps the last call's contents; the entry point clears the ticket
+ * word on `stream` before each launch): calls that OVERLAP on the GPU -- different streams or host threads on one device -- race
+ * and must be serialised by the caller.  Calls no cudaMalloc / cudaFree / allocating routine (cudaGetSymbolAddress once per
+ * device, cudaMemsetAsync of 4 bytes, one kernel launch). */
+int64_t l1_loss_static_max_n(void);
+int l1_loss_forward_static(const float* image, const float* target, int64_t n, float* loss, float* dL_dimage, void* stream);
 
 /* Bench support (no reference counterpart): per-stage CUDA-event timing of the last forward/backward call, and an
  * FP32 FMA throughput probe (8 independent FMA chains per thread, `iters` rounds: 16*iters flop per thread). */
