@@ -2,13 +2,12 @@
 HierarchicalPoseEncoder (models/network_utils.py:119-178; built from cfg.pose_encoder at models/deformer/non_rigid.py:206
 and called at :236 as `pose_encoder(rots, Jtrs)`): `forward(rots [1,24,9], Jtrs [1,24,3]) -> [1,144]`, the condition the
 non-rigid MLP folds into its first bias.  Parameters are stored packed ([24,19,19] ...) so that a forward is ONE kernel;
-`load_reference_state_dict` maps the reference's names (layer_0.*, layers.{j}.0.*, layers.{j}.2.*).  The backward
-re-evaluates the ~11k multiply-adds with torch ops on the GPU.  No CPU fallback."""
+`load_reference_state_dict` maps the reference's names (layer_0.*, layers.{j}.0.*, layers.{j}.2.*).  The backward is ONE
+kernel too (`pose_encoder_backward`: the reference's autograd runs several hundred launches for it).  No CPU fallback."""
 import ctypes
 
 import torch
 import torch.nn as nn
-import torch.nn.functional as F
 
 from diff_gaussian_rasterization import _C as _gs
 
@@ -22,6 +21,11 @@ class PoseEncoderArgs(ctypes.Structure):
                 ("Wa", vp), ("ba", vp), ("Wb", vp), ("bb", vp), ("out", vp)]
 
 
+class PoseEncoderBackwardArgs(ctypes.Structure):
+    _fields_ = [("fwd", PoseEncoderArgs), ("dL_dout", vp), ("dL_drots", vp), ("dL_dJtrs", vp), ("dL_dW0", vp), ("dL_db0", vp),
+                ("dL_dWa", vp), ("dL_dba", vp), ("dL_dWb", vp), ("dL_dbb", vp)]
+
+
 _configured = False
 
 
@@ -31,23 +35,10 @@ def _lib():
     if not _configured:
         L.pose_encoder_forward.restype = ctypes.c_int
         L.pose_encoder_forward.argtypes = [ctypes.POINTER(PoseEncoderArgs), vp]
+        L.pose_encoder_backward.restype = ctypes.c_int
+        L.pose_encoder_backward.argtypes = [ctypes.POINTER(PoseEncoderBackwardArgs), vp]
         _configured = True
     return L
-
-
-def _torch_encode(rots, Jtrs, W0, b0, Wa, ba, Wb, bb, rel_joints):
-    """Differentiable re-evaluation (network_utils.py:152-178), used by the backward only."""
-    J = Jtrs
-    if rel_joints:
-        J = torch.cat([Jtrs[:1], Jtrs[1:] - Jtrs[KTREE_PARENTS[1:]]]).detach()  # the reference computes this under no_grad
-    glob = F.linear(torch.cat([rots.reshape(-1), J.reshape(-1)]), W0, b0)
-    out = [None] * 24
-    for j in range(24):
-        p = KTREE_PARENTS[j]
-        d = J[j] if (p == -1 or rel_joints) else J[j] - J[p]
-        x = torch.cat([rots[j], J[j], d.norm().reshape(1), glob if p == -1 else out[p]])
-        out[j] = F.linear(F.relu(F.linear(x, Wa[j], ba[j])), Wb[j], bb[j])
-    return torch.cat(out)
 
 
 class HierarchicalPoseEncoderFused(nn.Module):
@@ -75,27 +66,50 @@ class HierarchicalPoseEncoderFused(nn.Module):
     def params(self):
         return [self.W0, self.b0, self.Wa, self.ba, self.Wb, self.bb]
 
+    def _fill(self, a, rots, Jtrs, keep):
+        c = lambda t: t.detach().contiguous().float()
+        rots, Jtrs = c(rots.reshape(24, 9)), c(Jtrs.reshape(24, 3))
+        a.num_joints, a.dim_per_joint, a.rel_joints = 24, 6, int(self.rel_joints)
+        for j, p in enumerate(KTREE_PARENTS):
+            a.parents[j] = p
+        params = [c(t) for t in self.params()]
+        keep += [rots, Jtrs] + params
+        p = _gs._ptr
+        a.rots, a.Jtrs = p(rots, "rots"), p(Jtrs, "Jtrs")
+        a.W0, a.b0, a.Wa, a.ba, a.Wb, a.bb = (p(t, "param") for t in params)
+
     @torch.no_grad()
     def encode(self, rots, Jtrs):
         if not rots.is_cuda:
             raise _gs.GsError("HierarchicalPoseEncoderFused needs CUDA tensors (there is no CPU path)")
         L = _lib()
         dev = rots.device
-        c = lambda t: t.detach().contiguous().float()
-        rots, Jtrs = c(rots.reshape(24, 9)), c(Jtrs.reshape(24, 3))
-        a = PoseEncoderArgs()
-        a.num_joints, a.dim_per_joint, a.rel_joints = 24, 6, int(self.rel_joints)
-        for j, p in enumerate(KTREE_PARENTS):
-            a.parents[j] = p
-        keep = [c(t) for t in self.params()]
-        p = _gs._ptr
-        a.rots, a.Jtrs = p(rots, "rots"), p(Jtrs, "Jtrs")
-        a.W0, a.b0, a.Wa, a.ba, a.Wb, a.bb = (p(t, "param") for t in keep)
+        a, keep = PoseEncoderArgs(), []
         with torch.cuda.device(dev):
+            self._fill(a, rots, Jtrs, keep)
             out = torch.empty(1, 144, dtype=torch.float32, device=dev)
             a.out = out.data_ptr()
             _gs._check(L.pose_encoder_forward(ctypes.byref(a), torch.cuda.current_stream(dev).cuda_stream), "pose_encoder_forward")
         return out
+
+    @torch.no_grad()
+    def encode_backward(self, rots, Jtrs, g):
+        """Hand-written backward (pose_encoder_backward, one launch): -> (drots [24,9], dJtrs [24,3] or None with rel_joints (the
+        reference cuts that gradient, network_utils.py:155-159), [dW0, db0, dWa, dba, dWb, dbb])."""
+        L = _lib()
+        dev = rots.device
+        b, keep = PoseEncoderBackwardArgs(), []
+        with torch.cuda.device(dev):
+            self._fill(b.fwd, rots, Jtrs, keep)
+            g = g.detach().contiguous().float().reshape(-1)
+            f32 = dict(dtype=torch.float32, device=dev)
+            drots = torch.empty(24, 9, **f32)
+            dJ = None if self.rel_joints else torch.empty(24, 3, **f32)
+            dP = [torch.empty_like(t, dtype=torch.float32) for t in self.params()]
+            b.dL_dout, b.dL_drots, b.dL_dJtrs = g.data_ptr(), drots.data_ptr(), (dJ.data_ptr() if dJ is not None else None)
+            b.dL_dW0, b.dL_db0, b.dL_dWa, b.dL_dba, b.dL_dWb, b.dL_dbb = (t.data_ptr() for t in dP)
+            _gs._check(L.pose_encoder_backward(ctypes.byref(b), torch.cuda.current_stream(dev).cuda_stream), "pose_encoder_backward")
+        return drots, dJ, dP
 
     def forward(self, rots, Jtrs, skinning_weight=None):
         if torch.is_grad_enabled() and (any(t.requires_grad for t in self.params()) or rots.requires_grad or Jtrs.requires_grad):
@@ -112,12 +126,7 @@ class _EncFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g):
-        leaves = [t.detach().float().requires_grad_(True) for t in ctx.saved_tensors]
-        with torch.enable_grad():
-            y = _torch_encode(leaves[0].reshape(24, 9), leaves[1].reshape(24, 3), *leaves[2:], ctx.mod.rel_joints)
-            need = [i for i, n in enumerate(ctx.needs_input_grad[1:]) if n]
-            grads = torch.autograd.grad([y], [leaves[i] for i in need], [g.reshape(-1)], allow_unused=True)
-        out = [None] * len(leaves)
-        for i, gr in zip(need, grads):
-            out[i] = gr
-        return (None, *out)
+        rots, Jtrs = ctx.saved_tensors[:2]
+        drots, dJ, dP = ctx.mod.encode_backward(rots, Jtrs, g)
+        grads = [drots.view(rots.shape), None if dJ is None else dJ.view(Jtrs.shape)] + dP
+        return (None, *[gr if n else None for gr, n in zip(grads, ctx.needs_input_grad[1:])])

@@ -191,6 +191,7 @@ size_t gs_sizeof(int32_t which) {
     case 10: return sizeof(NonRigidBackwardArgs);
     case 11: return sizeof(SkinBackwardArgs);
     case 12: return sizeof(ColorBackwardArgs);
+    case 13: return sizeof(PoseEncoderBackwardArgs);
     default: return 0;
   }
 }

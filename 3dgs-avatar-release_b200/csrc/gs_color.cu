@@ -407,6 +407,7 @@ color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ 
   }
   if (tid == 0) {
     nr_mbar_init(&sm.bar, 1);
+    nr_mbar_init(&sm.ld_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   for (int k = tid; k < 5 * BW_H; k += NR_TILE) (&sm.dbias[0][0])[k] = 0.f;
@@ -420,13 +421,17 @@ color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ 
   const uint32_t tmem = sm.tmem_base;
   const uint32_t tmem_row = tmem + ((uint32_t)(warp * 32) << 16);
   const int F = a.feature_dim, S = cl_n_sh(a.sh_degree), R = a.non_rigid_dim, n_in = F + S + R, d_in = n_in + a.latent_dim;
-  uint32_t phase = 0;
+  uint32_t phase = 0, ld_phase = 0;
+  uint32_t signs[4];  // LeakyReLU branches of this thread's row in the activations loaded last
   const int HALF = 128 * 64;  // elements of one saved half (hi or lo)
 
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int i = tile * NR_TILE + row;
     const bool live = i < a.P;
     const __nv_bfloat16* const st = saved + (size_t)tile * CL_SAVE_TILE;
+    if (tid == 0)  // operands of lin2 (A1, W2^T) stream in while the sigmoid adjoint runs (A / W are free: see the tile's last barrier)
+      bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st + 2 * CL_SAVE_LAYER, st + 2 * CL_SAVE_LAYER + HALF, HALF * 2, sm.W_hi, sm.W_lo,
+                         w.w2t_hi, w.w2t_lo, CL_H * CL_NOUT * 2);
     float g[32];
 #pragma unroll
     for (int k = 0; k < 32; k++) g[k] = 0.f;
@@ -439,16 +444,17 @@ color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ 
     }
     store_grad32(sm, row, 0, g, sm.dbias[2], lane);
     // ---- lin2: Z2 = A1 . W2^T ----
-    copy16(sm.A_hi, st + 2 * CL_SAVE_LAYER, HALF * 2);
-    copy16(sm.A_lo, st + 2 * CL_SAVE_LAYER + HALF, HALF * 2);
-    copy_weights(sm.W_hi, w.w2t_hi, CL_H * CL_NOUT);
-    copy_weights(sm.W_lo, w.w2t_lo, CL_H * CL_NOUT);
+    bw_wait_loads(sm, ld_phase);
+    bw_row_signs(sm, row, CL_H, signs);  // of A1
     bw_sync_mma_inputs();
     if (tid == 0) {
       issue_dw(tmem + 128, sm.A_hi, sm.A_lo, sm.G_hi, sm.G_lo, CL_NOUT);    // dW2^T [k_in][n_out] (rows >= 64 are zero)
       issue_da(tmem, sm.G_hi, sm.G_lo, sm.W_hi, sm.W_lo, CL_NOUT, CL_H);    // dA1
     }
     bw_commit_wait(sm, tid == 0, phase);
+    if (tid == 0)  // A / W are free again: A0 and W1^T
+      bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st + CL_SAVE_LAYER, st + CL_SAVE_LAYER + HALF, HALF * 2, sm.W_hi, sm.W_lo, w.w1t_hi,
+                         w.w1t_lo, CL_H * CL_H * 2);
     {
       float v[32];
       tmem_ld32(tmem_row + 128, v);
@@ -462,21 +468,19 @@ color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ 
         float v[32];
         tmem_ld32(tmem_row + c * 32, v);
 #pragma unroll
-        for (int j = 0; j < 32; j += 8) lrelu_mask8(sm, row, c * 32 + j, v + j);
+        for (int j = 0; j < 32; j += 8) lrelu_mask8_bits(signs, c * 32 + j, v + j);
         store_grad32(sm, row, c * 32, v, sm.dbias[1 - hl], lane);
       }
-      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-      __syncthreads();
-      copy16(sm.A_hi, st + (size_t)(1 - hl) * CL_SAVE_LAYER, HALF * 2);
-      copy16(sm.A_lo, st + (size_t)(1 - hl) * CL_SAVE_LAYER + HALF, HALF * 2);
-      copy_weights(sm.W_hi, hl == 0 ? w.w1t_hi : w.w0t_hi, CL_H * CL_H);
-      copy_weights(sm.W_lo, hl == 0 ? w.w1t_lo : w.w0t_lo, CL_H * CL_H);
-      bw_sync_mma_inputs();
+      bw_wait_loads(sm, ld_phase);                          // this layer's A_in and W^T
+      if (hl == 0) bw_row_signs(sm, row, CL_H, signs);      // of A0, for the next epilogue
+      bw_sync_mma_inputs();                                 // G complete; every row has read its dA from TMEM and its signs
       if (tid == 0) {
         issue_dw(tmem + 128, sm.G_hi, sm.G_lo, sm.A_hi, sm.A_lo, CL_H);     // dW [n_out][k_in] (rows >= 64 are zero)
         issue_da(tmem, sm.G_hi, sm.G_lo, sm.W_hi, sm.W_lo, CL_H, CL_H);     // dA_in
       }
       bw_commit_wait(sm, tid == 0, phase);
+      if (tid == 0 && hl == 0)  // lin0's operands (composed input, W0^T) stream in during the dW flush and the epilogue
+        bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st, st + HALF, HALF * 2, sm.W_hi, sm.W_lo, w.w0t_hi, w.w0t_lo, CL_H * CL_H * 2);
       if (row < CL_H) {
         if (hl == 0) {
           flush_dw_rows(tmem_row + 128, CL_H, b.dL_dW1 + (size_t)row * CL_H);
@@ -588,6 +592,7 @@ __global__ void color_bwd_finish_kernel(ColorBackwardArgs b) {
 extern "C" int color_backward(const ColorBackwardArgs* args, void* workspace, size_t workspace_bytes, const void* saved,
                               size_t saved_bytes, void* stream) {
   if (!args || !workspace || !saved || !color_inputs_ok(args->fwd)) return GS_ERR_BAD_ARG;
+  if (((uintptr_t)workspace | (uintptr_t)saved) & 15) return GS_ERR_BAD_ARG;  // bulk copies: 16-byte aligned operands
   const ColorBackwardArgs& b = *args;
   const ColorArgs& a = b.fwd;
   if (!a.colors || !b.dL_dcolors || !b.dL_dW0 || !b.dL_db0 || !b.dL_dW1 || !b.dL_db1 || !b.dL_dW2 || !b.dL_db2) return GS_ERR_BAD_ARG;

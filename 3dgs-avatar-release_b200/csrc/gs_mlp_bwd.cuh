@@ -24,9 +24,39 @@ struct BwSmem {
   __nv_bfloat16 A_hi[BW_H * BW_H], A_lo[BW_H * BW_H];  // saved input activations of the current layer, [point][unit]
   __nv_bfloat16 W_hi[BW_H * BW_H], W_lo[BW_H * BW_H];  // W^T of the current layer as the B operand of dA = G . W
   float dbias[5][BW_H];                                // per-CTA bias gradients, flushed at the end
-  unsigned long long bar;
+  unsigned long long bar;     // MMA completion (tcgen05.commit)
+  unsigned long long ld_bar;  // operand loads (cp.async.bulk complete_tx)
   uint32_t tmem_base;
 };
+
+// Everyone: wait for the operand loads issued with bulk_load_operands on sm.ld_bar (`ld_phase` counts them, kept per thread).
+__device__ __forceinline__ void bw_wait_loads(BwSmem& sm, uint32_t& ld_phase) {
+  nr_mbar_wait(&sm.ld_bar, ld_phase & 1u);
+  ld_phase++;
+}
+
+// Signs of this thread's row of the saved activations in sm.A (bit k of the 128-bit mask = activation (row, k) > 0), taken right
+// after the load so that the buffer can be refilled while the epilogue that needs the signs still runs.
+__device__ __forceinline__ void bw_row_signs(const BwSmem& sm, int row, int units, uint32_t* signs /*[4]*/) {
+  signs[0] = signs[1] = signs[2] = signs[3] = 0u;
+  for (int s8 = 0; s8 < units / 8; s8++) {
+    const uint4 h = *reinterpret_cast<const uint4*>(sm.A_hi + core_idx(row, s8 * 8, BW_H));
+    const uint32_t w[4] = {h.x, h.y, h.z, h.w};
+    uint32_t bits = 0u;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const uint32_t b = (w[i >> 1] >> ((i & 1) * 16)) & 0xFFFFu;  // bf16 bits of element i
+      bits |= ((!(b & 0x8000u) && (b & 0x7FFFu) != 0u) ? 1u : 0u) << i;  // strictly positive
+    }
+    signs[s8 >> 2] |= bits << ((s8 & 3) * 8);
+  }
+}
+// LeakyReLU'(z) from the sign mask: 1 for z > 0, 0.01 otherwise (a > 0 <=> z > 0)
+__device__ __forceinline__ void lrelu_mask8_bits(const uint32_t* signs, int k0, float* g) {
+  const uint32_t bits = (signs[k0 >> 5] >> (k0 & 31)) & 0xFFu;
+#pragma unroll
+  for (int i = 0; i < 8; i++) g[i] = ((bits >> i) & 1u) ? g[i] : 0.01f * g[i];
+}
 
 __device__ __forceinline__ void copy16(void* dst, const void* src, int bytes) {  // whole CTA, 16-byte granules
   const uint4* s = reinterpret_cast<const uint4*>(src);

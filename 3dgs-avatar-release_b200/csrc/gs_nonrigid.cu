@@ -122,7 +122,8 @@ struct NrSmem {
   __nv_bfloat16 A_hi[NR_TILE * NR_H], A_lo[NR_TILE * NR_H];  // activations, operand layout (32 KB each)
   __nv_bfloat16 W_hi[NR_H * NR_H], W_lo[NR_H * NR_H];        // weights of the current layer
   float bias[NR_H];
-  unsigned long long bar;
+  unsigned long long bar;     // MMA completion
+  unsigned long long ld_bar;  // weight loads (cp.async.bulk complete_tx)
   uint32_t tmem_base;
 };
 
@@ -156,7 +157,10 @@ __global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs
   }
   if (tid == 0) {
     nr_mbar_init(&sm.bar, 1);
+    nr_mbar_init(&sm.ld_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    // W0 streams in (one bulk copy per half) while every thread encodes its Gaussian
+    bulk_load_operands(&sm.ld_bar, nullptr, nullptr, nullptr, nullptr, 0u, sm.W_hi, sm.W_lo, w.w0_hi, w.w0_lo, NR_H * NR_F * 2);
   }
   // ---- layer-0 operands: hash-grid features of this thread's Gaussian, W0, folded bias ----
   float x = 0.f, y = 0.f, z = 0.f;
@@ -177,13 +181,12 @@ __global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs
 #pragma unroll
     for (int k = 0; k < NR_F; k += 8) store_act8(sm.A_hi, sm.A_lo, row, k, feat + k);
   }
-  copy_weights(sm.W_hi, w.w0_hi, NR_H * NR_F);
-  copy_weights(sm.W_lo, w.w0_lo, NR_H * NR_F);
   sm.bias[tid] = w.bias0[tid];
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to the tensor core
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  nr_mbar_wait(&sm.ld_bar, 0u);  // W0 has landed (after the barrier: the mbarrier was initialised by thread 0)
   __nv_bfloat16* const save_tile = saved ? saved + (size_t)blockIdx.x * NR_SAVE_TILE : nullptr;
   if (save_tile) {  // the first 32 K columns (4 K-slabs of 128 rows x 16 B) of A_hi / A_lo are the layer-0 operand
     copy16(save_tile, sm.A_hi, 128 * 32 * 2);
@@ -200,10 +203,11 @@ __global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs
     if (tid == 0) issue_layer(tmem, sm.A_hi, sm.A_lo, sm.W_hi, sm.W_lo, layer == 0 ? NR_F : NR_H, NR_H, &sm.bar);
     nr_mbar_wait(&sm.bar, (uint32_t)layer & 1u);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    hidden_epilogue(sm, tmem_row, row);  // A and W are free: the MMAs that read them have completed
-    const int nrows = layer == 2 ? npad : NR_H;
-    copy_weights(sm.W_hi, next_hi[layer], nrows * NR_H);
-    copy_weights(sm.W_lo, next_lo[layer], nrows * NR_H);
+    // A and W are free: the MMAs that read them have completed.  The next layer's weights stream in during the epilogue.
+    if (tid == 0)
+      bulk_load_operands(&sm.ld_bar, nullptr, nullptr, nullptr, nullptr, 0u, sm.W_hi, sm.W_lo, next_hi[layer], next_lo[layer],
+                         (uint32_t)((layer == 2 ? npad : NR_H) * NR_H * 2));
+    hidden_epilogue(sm, tmem_row, row);
     __syncthreads();  // everyone has read the old bias (and written its row of the new activations)
     if (save_tile) {
       copy16(save_tile + NR_SAVE_IN + (size_t)layer * NR_SAVE_LAYER, sm.A_hi, 128 * 128 * 2);
@@ -211,6 +215,7 @@ __global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs
     }
     if (layer < 2) sm.bias[tid] = next_b[layer][tid];
     else sm.bias[tid] = tid < a.n_out ? a.b3[tid] : 0.f;
+    nr_mbar_wait(&sm.ld_bar, (uint32_t)(layer + 1) & 1u);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -273,6 +278,7 @@ extern "C" int nonrigid_forward_train(const NonRigidArgs* args, void* workspace,
 }
 static int nonrigid_forward_impl(const NonRigidArgs* args, void* workspace, size_t workspace_bytes, void* saved, void* stream) {
   if (!args || !workspace || !nr_args_ok(*args)) return GS_ERR_BAD_ARG;
+  if (((uintptr_t)workspace | (uintptr_t)saved) & 15) return GS_ERR_BAD_ARG;  // bulk copies: 16-byte aligned operands
   const NonRigidArgs& a = *args;
   if (a.P == 0) return GS_OK;
   cudaStream_t st = (cudaStream_t)stream;
@@ -377,7 +383,9 @@ __global__ void __launch_bounds__(NR_TILE, 1) sk_fwd_kernel(SkinArgs a, SkWs w, 
   }
   if (tid == 0) {
     nr_mbar_init(&sm.bar, 1);
+    nr_mbar_init(&sm.ld_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    bulk_load_operands(&sm.ld_bar, nullptr, nullptr, nullptr, nullptr, 0u, sm.W_hi, sm.W_lo, w.w0_hi, w.w0_lo, NR_H * SK_K0 * 2);
   }
   {
     float in[SK_K0];
@@ -391,13 +399,12 @@ __global__ void __launch_bounds__(NR_TILE, 1) sk_fwd_kernel(SkinArgs a, SkWs w, 
     store_act8(sm.A_hi, sm.A_lo, row, 0, in);
     store_act8(sm.A_hi, sm.A_lo, row, 8, in + 8);
   }
-  copy_weights(sm.W_hi, w.w0_hi, NR_H * SK_K0);
-  copy_weights(sm.W_lo, w.w0_lo, NR_H * SK_K0);
   sm.bias[tid] = a.b[0][tid];
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  nr_mbar_wait(&sm.ld_bar, 0u);  // W0 has landed (after the barrier: the mbarrier was initialised by thread 0)
   __nv_bfloat16* const save_tile = saved ? saved + (size_t)blockIdx.x * SK_SAVE_TILE : nullptr;
   if (save_tile) {
     copy16(save_tile, sm.A_hi, 128 * SK_K0 * 2);
@@ -410,14 +417,13 @@ __global__ void __launch_bounds__(NR_TILE, 1) sk_fwd_kernel(SkinArgs a, SkWs w, 
     if (tid == 0) issue_layer(tmem, sm.A_hi, sm.A_lo, sm.W_hi, sm.W_lo, layer == 0 ? SK_K0 : NR_H, NR_H, &sm.bar);
     nr_mbar_wait(&sm.bar, (uint32_t)layer & 1u);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    hidden_epilogue(sm, tmem_row, row);
-    if (layer < 3) {
-      copy_weights(sm.W_hi, w.wh_hi[layer], NR_H * NR_H);
-      copy_weights(sm.W_lo, w.wh_lo[layer], NR_H * NR_H);
-    } else {
-      copy_weights(sm.W_hi, w.w4_hi, SK_NOUT * NR_H);
-      copy_weights(sm.W_lo, w.w4_lo, SK_NOUT * NR_H);
+    if (tid == 0) {  // W is free (the MMAs have completed): the next layer's weights stream in during the epilogue
+      if (layer < 3)
+        bulk_load_operands(&sm.ld_bar, nullptr, nullptr, nullptr, nullptr, 0u, sm.W_hi, sm.W_lo, w.wh_hi[layer], w.wh_lo[layer], NR_H * NR_H * 2);
+      else
+        bulk_load_operands(&sm.ld_bar, nullptr, nullptr, nullptr, nullptr, 0u, sm.W_hi, sm.W_lo, w.w4_hi, w.w4_lo, SK_NOUT * NR_H * 2);
     }
+    hidden_epilogue(sm, tmem_row, row);
     __syncthreads();
     if (save_tile) {
       copy16(save_tile + SK_SAVE_IN + (size_t)layer * NR_SAVE_LAYER, sm.A_hi, 128 * 128 * 2);
@@ -425,6 +431,7 @@ __global__ void __launch_bounds__(NR_TILE, 1) sk_fwd_kernel(SkinArgs a, SkWs w, 
     }
     if (layer < 3) sm.bias[tid] = a.b[layer + 1][tid];
     else sm.bias[tid] = tid < a.n_out ? a.b[4][tid] : 0.f;
+    nr_mbar_wait(&sm.ld_bar, (uint32_t)(layer + 1) & 1u);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -480,6 +487,7 @@ extern "C" int skinning_forward_train(const SkinArgs* args, void* workspace, siz
 }
 static int skinning_forward_impl(const SkinArgs* args, void* workspace, size_t workspace_bytes, void* saved, void* stream) {
   if (!args || !workspace) return GS_ERR_BAD_ARG;
+  if (((uintptr_t)workspace | (uintptr_t)saved) & 15) return GS_ERR_BAD_ARG;  // bulk copies: 16-byte aligned operands
   const SkinArgs& a = *args;
   if (a.P < 0 || a.hidden != NR_H || (a.n_out != 25 && a.n_out != 24) || !a.aabb_min || !a.aabb_max || !a.xyz || !a.weights)
     return GS_ERR_BAD_ARG;
@@ -566,6 +574,7 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
   }
   if (tid == 0) {
     nr_mbar_init(&sm.bar, 1);
+    nr_mbar_init(&sm.ld_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   for (int k = tid; k < 5 * BW_H; k += NR_TILE) (&sm.dbias[0][0])[k] = 0.f;
@@ -575,12 +584,18 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
   const uint32_t tmem = sm.tmem_base;
   const uint32_t tmem_row = tmem + ((uint32_t)(warp * 32) << 16);
   const int in0 = NR_F + a.n_cond;
-  uint32_t phase = 0;
+  uint32_t phase = 0, ld_phase = 0;
+  uint32_t signs[4];  // LeakyReLU branches of this thread's row in the activations loaded last
 
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int i = tile * NR_TILE + row;
     const bool live = i < a.P;
     const __nv_bfloat16* const st = saved + (size_t)tile * NR_SAVE_TILE;
+    // operands of the output layer (A2, W3^T) stream in while the upstream gradient is read: A / W are free (the previous tile's
+    // MMAs have completed and the barrier at its end has been passed)
+    if (tid == 0)
+      bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st + NR_SAVE_IN + 2 * NR_SAVE_LAYER, st + NR_SAVE_IN + 2 * NR_SAVE_LAYER + 128 * 128,
+                         128 * 128 * 2, sm.W_hi, sm.W_lo, w.w3t_hi, w.w3t_lo, (uint32_t)(NR_H * npad * 2));
     // ---- gradient of the raw MLP output (delta application, non_rigid.py:262-282) ----
     float g[32];
 #pragma unroll
@@ -613,24 +628,23 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
     }
     store_grad32(sm, row, 0, g, sm.dbias[3], lane);
     // ---- layer 3: Z3 = A2 . W3^T ----
-    copy16(sm.A_hi, st + NR_SAVE_IN + 2 * NR_SAVE_LAYER, 128 * 128 * 2);
-    copy16(sm.A_lo, st + NR_SAVE_IN + 2 * NR_SAVE_LAYER + 128 * 128, 128 * 128 * 2);
-    copy_weights(sm.W_hi, w.w3t_hi, NR_H * npad);
-    copy_weights(sm.W_lo, w.w3t_lo, NR_H * npad);
+    bw_wait_loads(sm, ld_phase);
+    bw_row_signs(sm, row, NR_H, signs);  // of A2: used by the epilogue that forms G2
     bw_sync_mma_inputs();
     if (tid == 0) {
       issue_dw(tmem + 128, sm.A_hi, sm.A_lo, sm.G_hi, sm.G_lo, npad);   // dW3^T [k_in][n_out]
       issue_da(tmem, sm.G_hi, sm.G_lo, sm.W_hi, sm.W_lo, npad, NR_H);   // dA2
     }
     bw_commit_wait(sm, tid == 0, phase);
+    if (tid == 0)  // A / W are free again (MMAs done, signs taken before the barrier above): next layer's operands, A1 and W2^T
+      bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st + NR_SAVE_IN + NR_SAVE_LAYER, st + NR_SAVE_IN + NR_SAVE_LAYER + 128 * 128,
+                         128 * 128 * 2, sm.W_hi, sm.W_lo, w.w2t_hi, w.w2t_lo, NR_H * NR_H * 2);
     {
       float v[32];
       tmem_ld32(tmem_row + 128, v);
       for (int n = 0; n < a.n_out; n++) atomicAdd(b.dL_dW3 + (size_t)n * NR_H + row, v[n]);
     }
     const float* const dWh[2] = {b.dL_dW2, b.dL_dW1};
-    const __nv_bfloat16* const wth[2] = {w.w2t_hi, w.w1t_hi};
-    const __nv_bfloat16* const wtl[2] = {w.w2t_lo, w.w1t_lo};
 #pragma unroll 1
     for (int hl = 0; hl < 3; hl++) {  // hl = 0: layer 2 (input A1), 1: layer 1 (input A0), 2: layer 0 (input = hash features)
       // G of this layer from dA (TMEM) and the sign of the saved activation still in sm.A
@@ -639,29 +653,26 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
         float v[32];
         tmem_ld32(tmem_row + c * 32, v);
 #pragma unroll
-        for (int j = 0; j < 32; j += 8) lrelu_mask8(sm, row, c * 32 + j, v + j);
+        for (int j = 0; j < 32; j += 8) lrelu_mask8_bits(signs, c * 32 + j, v + j);
         store_grad32(sm, row, c * 32, v, sm.dbias[2 - hl], lane);
       }
-      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-      __syncthreads();  // every row has read its signs from sm.A and its dA from TMEM
       const int kin = hl < 2 ? NR_H : NR_F;
-      if (hl < 2) {
-        copy16(sm.A_hi, st + NR_SAVE_IN + (size_t)(1 - hl) * NR_SAVE_LAYER, 128 * 128 * 2);
-        copy16(sm.A_lo, st + NR_SAVE_IN + (size_t)(1 - hl) * NR_SAVE_LAYER + 128 * 128, 128 * 128 * 2);
-        copy_weights(sm.W_hi, wth[hl], NR_H * NR_H);
-        copy_weights(sm.W_lo, wtl[hl], NR_H * NR_H);
-      } else {
-        copy16(sm.A_hi, st, 128 * NR_F * 2);
-        copy16(sm.A_lo, st + 128 * NR_F, 128 * NR_F * 2);
-        copy_weights(sm.W_hi, w.w0t_hi, NR_F * NR_H);
-        copy_weights(sm.W_lo, w.w0t_lo, NR_F * NR_H);
-      }
-      bw_sync_mma_inputs();
+      bw_wait_loads(sm, ld_phase);                             // this layer's A_in and W^T (issued after the previous MMAs)
+      if (hl < 2) bw_row_signs(sm, row, NR_H, signs);          // of A1 / A0, for the next epilogue
+      bw_sync_mma_inputs();                                    // G complete; every row has read its dA from TMEM and its signs
       if (tid == 0) {
         issue_dw(tmem + 128, sm.G_hi, sm.G_lo, sm.A_hi, sm.A_lo, kin);      // dW [n_out][k_in]
         issue_da(tmem, sm.G_hi, sm.G_lo, sm.W_hi, sm.W_lo, NR_H, kin);      // dA_in
       }
       bw_commit_wait(sm, tid == 0, phase);
+      if (tid == 0 && hl < 2) {  // the next layer's operands stream in during the dW flush and the epilogue
+        if (hl == 0)
+          bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st + NR_SAVE_IN, st + NR_SAVE_IN + 128 * 128, 128 * 128 * 2, sm.W_hi, sm.W_lo,
+                             w.w1t_hi, w.w1t_lo, NR_H * NR_H * 2);
+        else
+          bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st, st + 128 * NR_F, 128 * NR_F * 2, sm.W_hi, sm.W_lo, w.w0t_hi, w.w0t_lo,
+                             NR_F * NR_H * 2);
+      }
       if (hl < 2) flush_dw_rows(tmem_row + 128, NR_H, const_cast<float*>(dWh[hl]) + (size_t)row * NR_H);
       else flush_dw_rows(tmem_row + 128, NR_F, b.dL_dW0 + (size_t)row * in0);
     }
@@ -721,6 +732,7 @@ __global__ void nr_bwd_finish_kernel(NonRigidBackwardArgs b) {
 extern "C" int nonrigid_backward(const NonRigidBackwardArgs* args, void* workspace, size_t workspace_bytes, const void* saved,
                                  size_t saved_bytes, void* stream) {
   if (!args || !workspace || !saved || !nr_inputs_ok(args->fwd)) return GS_ERR_BAD_ARG;
+  if (((uintptr_t)workspace | (uintptr_t)saved) & 15) return GS_ERR_BAD_ARG;  // bulk copies: 16-byte aligned operands
   const NonRigidBackwardArgs& b = *args;
   const NonRigidArgs& a = b.fwd;
   if (!a.deltas || !b.dL_dxyz || !b.dL_dscaling || !b.dL_drotation || !b.dL_dtable) return GS_ERR_BAD_ARG;
@@ -862,6 +874,7 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
   }
   if (tid == 0) {
     nr_mbar_init(&sm.bar, 1);
+    nr_mbar_init(&sm.ld_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   for (int k = tid; k < 5 * BW_H; k += NR_TILE) (&sm.dbias[0][0])[k] = 0.f;
@@ -870,12 +883,16 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = sm.tmem_base;
   const uint32_t tmem_row = tmem + ((uint32_t)(warp * 32) << 16);
-  uint32_t phase = 0;
+  uint32_t phase = 0, ld_phase = 0;
+  uint32_t signs[4];  // LeakyReLU branches of this thread's row in the activations loaded last
 
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int i = tile * NR_TILE + row;
     const bool live = i < a.P;
     const __nv_bfloat16* const st = saved + (size_t)tile * SK_SAVE_TILE;
+    if (tid == 0)  // operands of the output layer (A3, W4^T) stream in while the softmax adjoint runs
+      bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st + SK_SAVE_IN + 3 * NR_SAVE_LAYER, st + SK_SAVE_IN + 3 * NR_SAVE_LAYER + 128 * 128,
+                         128 * 128 * 2, sm.W_hi, sm.W_lo, w.w4t_hi, w.w4t_lo, NR_H * SK_NOUT * 2);
     // ---- dL/dlogits through the (hierarchical) softmax ----
     float g[32];
 #pragma unroll
@@ -900,16 +917,17 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
     }
     store_grad32(sm, row, 0, g, sm.dbias[4], lane);
     // ---- output layer: Z4 = A3 . W4^T ----
-    copy16(sm.A_hi, st + SK_SAVE_IN + 3 * NR_SAVE_LAYER, 128 * 128 * 2);
-    copy16(sm.A_lo, st + SK_SAVE_IN + 3 * NR_SAVE_LAYER + 128 * 128, 128 * 128 * 2);
-    copy_weights(sm.W_hi, w.w4t_hi, NR_H * SK_NOUT);
-    copy_weights(sm.W_lo, w.w4t_lo, NR_H * SK_NOUT);
+    bw_wait_loads(sm, ld_phase);
+    bw_row_signs(sm, row, NR_H, signs);  // of A3
     bw_sync_mma_inputs();
     if (tid == 0) {
       issue_dw(tmem + 128, sm.A_hi, sm.A_lo, sm.G_hi, sm.G_lo, SK_NOUT);   // dW4^T [k_in][n_out]
       issue_da(tmem, sm.G_hi, sm.G_lo, sm.W_hi, sm.W_lo, SK_NOUT, NR_H);   // dA3
     }
     bw_commit_wait(sm, tid == 0, phase);
+    if (tid == 0)  // A / W are free again: A2 and W3^T
+      bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st + SK_SAVE_IN + 2 * NR_SAVE_LAYER, st + SK_SAVE_IN + 2 * NR_SAVE_LAYER + 128 * 128,
+                         128 * 128 * 2, sm.W_hi, sm.W_lo, w.wht_hi[2], w.wht_lo[2], NR_H * NR_H * 2);
     {
       float v[32];
       tmem_ld32(tmem_row + 128, v);
@@ -922,29 +940,27 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
         float v[32];
         tmem_ld32(tmem_row + c * 32, v);
 #pragma unroll
-        for (int j = 0; j < 32; j += 8) lrelu_mask8(sm, row, c * 32 + j, v + j);
+        for (int j = 0; j < 32; j += 8) lrelu_mask8_bits(signs, c * 32 + j, v + j);
         store_grad32(sm, row, c * 32, v, sm.dbias[3 - hl], lane);
       }
-      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-      __syncthreads();
       const int kin = hl < 3 ? NR_H : SK_K0;
-      if (hl < 3) {
-        copy16(sm.A_hi, st + SK_SAVE_IN + (size_t)(2 - hl) * NR_SAVE_LAYER, 128 * 128 * 2);
-        copy16(sm.A_lo, st + SK_SAVE_IN + (size_t)(2 - hl) * NR_SAVE_LAYER + 128 * 128, 128 * 128 * 2);
-        copy_weights(sm.W_hi, w.wht_hi[2 - hl], NR_H * NR_H);
-        copy_weights(sm.W_lo, w.wht_lo[2 - hl], NR_H * NR_H);
-      } else {
-        copy16(sm.A_hi, st, 128 * SK_K0 * 2);
-        copy16(sm.A_lo, st + 128 * SK_K0, 128 * SK_K0 * 2);
-        copy_weights(sm.W_hi, w.w0t_hi, SK_K0 * NR_H);
-        copy_weights(sm.W_lo, w.w0t_lo, SK_K0 * NR_H);
-      }
-      bw_sync_mma_inputs();
+      bw_wait_loads(sm, ld_phase);                             // this layer's A_in and W^T
+      if (hl < 3) bw_row_signs(sm, row, NR_H, signs);          // for the next epilogue
+      bw_sync_mma_inputs();                                    // G complete; every row has read its dA from TMEM and its signs
       if (tid == 0) {
         issue_dw(tmem + 128, sm.G_hi, sm.G_lo, sm.A_hi, sm.A_lo, kin);
         issue_da(tmem, sm.G_hi, sm.G_lo, sm.W_hi, sm.W_lo, NR_H, kin);
       }
       bw_commit_wait(sm, tid == 0, phase);
+      if (tid == 0 && hl < 3) {  // the next layer's operands stream in during the dW flush and the epilogue
+        if (hl < 2)
+          bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st + SK_SAVE_IN + (size_t)(1 - hl) * NR_SAVE_LAYER,
+                             st + SK_SAVE_IN + (size_t)(1 - hl) * NR_SAVE_LAYER + 128 * 128, 128 * 128 * 2, sm.W_hi, sm.W_lo,
+                             w.wht_hi[1 - hl], w.wht_lo[1 - hl], NR_H * NR_H * 2);
+        else
+          bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st, st + 128 * SK_K0, 128 * SK_K0 * 2, sm.W_hi, sm.W_lo, w.w0t_hi, w.w0t_lo,
+                             SK_K0 * NR_H * 2);
+      }
       if (hl < 3) {
         flush_dw_rows(tmem_row + 128, NR_H, b.dL_dW[3 - hl] + (size_t)row * NR_H);
       } else {
@@ -977,6 +993,7 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
 extern "C" int skinning_backward(const SkinBackwardArgs* args, void* workspace, size_t workspace_bytes, const void* saved,
                                  size_t saved_bytes, void* stream) {
   if (!args || !workspace || !saved) return GS_ERR_BAD_ARG;
+  if (((uintptr_t)workspace | (uintptr_t)saved) & 15) return GS_ERR_BAD_ARG;  // bulk copies: 16-byte aligned operands
   const SkinBackwardArgs& b = *args;
   const SkinArgs& a = b.fwd;
   if (a.P < 0 || a.hidden != NR_H || (a.n_out != 25 && a.n_out != 24) || !a.aabb_min || !a.aabb_max || !a.xyz || !a.logits)

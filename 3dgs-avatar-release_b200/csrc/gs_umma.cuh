@@ -59,6 +59,29 @@ __device__ __forceinline__ void nr_mbar_wait(unsigned long long* bar, uint32_t p
       "NRD_%=:\n"
       "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+// ---- bulk asynchronous copy global -> shared (TMA, 1-D): one thread moves a whole operand; the bytes land on an mbarrier ----
+// (the per-thread LDG -> STS loops these replace kept ONE load in flight per thread: with 4 warps per SM the operand loads were
+// a chain of L2 round trips and ~60 % of the MLP kernels' time, profiles/r2/r2_v2_mlp_kernels.json)
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// One thread: the four operand halves of a layer (A hi | lo, W hi | lo; 16-byte aligned, sizes multiples of 16) on `bar`.
+// The fence orders earlier generic-proxy accesses to the destination buffers (made visible to this thread by a barrier)
+// before the async-proxy writes.
+__device__ __forceinline__ void bulk_load_operands(unsigned long long* bar, void* a_hi, void* a_lo, const void* ga_hi, const void* ga_lo,
+                                                   uint32_t a_bytes, void* w_hi, void* w_lo, const void* gw_hi, const void* gw_lo,
+                                                   uint32_t w_bytes) {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  mbar_expect_tx(bar, 2 * a_bytes + 2 * w_bytes);
+  if (a_bytes) { bulk_g2s(a_hi, ga_hi, a_bytes, bar); bulk_g2s(a_lo, ga_lo, a_bytes, bar); }
+  if (w_bytes) { bulk_g2s(w_hi, gw_hi, w_bytes, bar); bulk_g2s(w_lo, gw_lo, w_bytes, bar); }
+}
+
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {  // 32 lanes x 32 columns: lane = this thread's row
   uint32_t r[32];
   asm volatile(

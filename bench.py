@@ -290,8 +290,8 @@ def default_config_step(hp, g, frame, f, GraphedStep, flush, dev, eager, n_steps
     return {"ms_per_step": ms, "iter_s": 1e3 / ms, "loss": loss, "all_parameters_receive_finite_gradients": grads_ok,
             "what": "fwd+bwd of the reference's default configuration at cfg-A size: hash-grid non-rigid MLP -> skinning-field MLP -> fused "
                     "posing -> colour MLP -> rasterizer with fused opacity pass -> L1 + mask loss; the three MLP stages run hand-written "
-                    "tcgen05 forward AND backward kernels (no torch / cuBLAS on the path); the pose encoder's batch-1 backward is a torch "
-                    "re-evaluation"}
+                    "tcgen05 forward AND backward kernels, the pose encoder one launch forward and one backward (no torch / cuBLAS kernels on the "
+                    "path apart from the mask-loss scaling and the latent embedding lookup)"}
 
 
 def render_sequence(hp, args, rank, world, dev, GraphedStep, eager, n_frames=64):

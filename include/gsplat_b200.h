@@ -426,6 +426,20 @@ typedef struct PoseEncoderArgs {
   float* out;              /* [144] */
 } PoseEncoderArgs;
 int pose_encoder_forward(const PoseEncoderArgs* args, void* stream);
+/* Backward of pose_encoder_forward (the reference: autograd over the ~150 nn.Linear nodes of network_utils.py:152-178) in one
+ * launch: re-evaluates the forward from `fwd`'s inputs (fwd.out is not read) and writes every element of every gradient (no
+ * clearing needed; deterministic).  dL_drots / dL_dJtrs may be NULL; with rel_joints the reference forms the relative joints
+ * under no_grad (:155-159), so dL_dJtrs is all zeros. */
+typedef struct PoseEncoderBackwardArgs {
+  PoseEncoderArgs fwd;
+  const float* dL_dout;    /* [144] */
+  float* dL_drots;         /* [24,9] or NULL */
+  float* dL_dJtrs;         /* [24,3] or NULL */
+  float* dL_dW0; float* dL_db0;  /* [6,288], [6] */
+  float* dL_dWa; float* dL_dba;  /* [24,19,19], [24,19] */
+  float* dL_dWb; float* dL_dbb;  /* [24,6,19], [24,6] */
+} PoseEncoderBackwardArgs;
+int pose_encoder_backward(const PoseEncoderBackwardArgs* args, void* stream);
 
 /* ---- data-parallel training: in-place sum of the per-rank gradient slabs over NVLink / NVSwitch peer memory ----
  * The reference has no multi-GPU path; this is the one collective the data-parallel step needs, as one kernel
@@ -492,7 +506,7 @@ int gs_read_counters(const void* geom, uint64_t* counters_host, void* stream);
 
 /* sizeof of the ABI structs: 0 GsForwardArgs, 1 GsBackwardArgs, 2 PoseArgs, 3 PoseBackwardArgs, 4 NonRigidArgs, 5 SkinArgs,
  * 6 ColorArgs, 7 AdamArgs, 8 PoseEncoderArgs, 9 SlabAllReduceArgs, 10 NonRigidBackwardArgs, 11 SkinBackwardArgs,
- * 12 ColorBackwardArgs */
+ * 12 ColorBackwardArgs, 13 PoseEncoderBackwardArgs */
 size_t gs_sizeof(int32_t which);
 int gs_last_cuda_error(void);
 const char* gs_version(void);

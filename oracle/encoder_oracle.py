@@ -15,6 +15,7 @@ def encode(rots, Jtrs, W0, b0, Wa, ba, Wb, bb, rel_joints=False):
     J = Jtrs.clone()
     if rel_joints:  # :155-159
         J[1:] = Jtrs[1:] - Jtrs[KTREE_PARENTS[1:]]
+        J = J.detach()  # formed under torch.no_grad() in the reference: no gradient reaches Jtrs in this mode
     glob = F.linear(torch.cat([rots.reshape(-1), J.reshape(-1)]), W0, b0)  # :161-162
     out = [None] * 24
     for j in range(24):

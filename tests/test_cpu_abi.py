@@ -52,14 +52,14 @@ def test_struct_layout_matches_header(built_lib):
     from avatar_pose.skinning import SkinArgs, SkinBackwardArgs
     from avatar_pose.texture import ColorArgs, ColorBackwardArgs
     from avatar_pose.optim import AdamArgs
-    from avatar_pose.pose_encoder import PoseEncoderArgs
+    from avatar_pose.pose_encoder import PoseEncoderArgs, PoseEncoderBackwardArgs
     L = _C.lib()
     L.gs_sizeof.restype = ctypes.c_size_t
     L.gs_sizeof.argtypes = [ctypes.c_int32]
     for which, st in enumerate((_C.GsForwardArgs, _C.GsBackwardArgs, avatar_pose.PoseArgs, avatar_pose.PoseBackwardArgs,
                                 NonRigidArgs, SkinArgs, ColorArgs, AdamArgs, PoseEncoderArgs)):
         assert L.gs_sizeof(which) == ctypes.sizeof(st), st.__name__
-    for which, st in ((10, NonRigidBackwardArgs), (11, SkinBackwardArgs), (12, ColorBackwardArgs)):
+    for which, st in ((10, NonRigidBackwardArgs), (11, SkinBackwardArgs), (12, ColorBackwardArgs), (13, PoseEncoderBackwardArgs)):
         assert L.gs_sizeof(which) == ctypes.sizeof(st), st.__name__
 
 
