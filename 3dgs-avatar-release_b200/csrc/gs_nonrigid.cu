@@ -86,27 +86,44 @@ __device__ __forceinline__ uint32_t grid_index(uint32_t x, uint32_t y, uint32_t 
   return index % size;
 }
 
+// Levels are processed four at a time: the 32 table reads of a group are issued before the first one is used.  With one warp per
+// scheduler nothing else hides the latency, and level by level the encode was 16 dependent L2 round trips per Gaussian.
+constexpr int HG_GROUP = 4;
+constexpr int HG_LEVELS = NR_F / 2;  // n_levels is fixed by the MLP's input width (nr_inputs_ok): loops unroll, features stay in registers
 __device__ __forceinline__ void hash_encode(const NonRigidArgs& a, float x, float y, float z, float* feat /*[2L]*/) {
-  for (int l = 0; l < a.n_levels; l++) {
-    const float scale = a.level_scale[l];
-    const uint32_t res = a.level_res[l];
-    const uint32_t off = a.level_offset[l], size = a.level_offset[l + 1] - off;
-    const float px = fmaf(x, scale, 0.5f), py = fmaf(y, scale, 0.5f), pz = fmaf(z, scale, 0.5f);
-    const float fx0 = floorf(px), fy0 = floorf(py), fz0 = floorf(pz);
-    const float wx = px - fx0, wy = py - fy0, wz = pz - fz0;
-    const uint32_t gx = (uint32_t)(int)fx0, gy = (uint32_t)(int)fy0, gz = (uint32_t)(int)fz0;
-    float f0 = 0.f, f1 = 0.f;
 #pragma unroll
-    for (int c = 0; c < 8; c++) {
-      const uint32_t dx = c & 1, dy = (c >> 1) & 1, dz = (c >> 2) & 1;
-      const float wgt = (dx ? wx : 1.f - wx) * (dy ? wy : 1.f - wy) * (dz ? wz : 1.f - wz);
-      const uint32_t idx = grid_index(gx + dx, gy + dy, gz + dz, res, size);
-      const float2 v = __ldg(reinterpret_cast<const float2*>(a.table) + off + idx);
-      f0 = fmaf(wgt, v.x, f0);
-      f1 = fmaf(wgt, v.y, f1);
+  for (int l0 = 0; l0 < HG_LEVELS; l0 += HG_GROUP) {
+    float2 v[HG_GROUP][8];
+    float wx[HG_GROUP], wy[HG_GROUP], wz[HG_GROUP];
+#pragma unroll
+    for (int q = 0; q < HG_GROUP; q++) {
+      const int l = l0 + q;
+      const float scale = a.level_scale[l];
+      const uint32_t res = a.level_res[l];
+      const uint32_t off = a.level_offset[l], size = a.level_offset[l + 1] - off;
+      const float px = fmaf(x, scale, 0.5f), py = fmaf(y, scale, 0.5f), pz = fmaf(z, scale, 0.5f);
+      const float fx0 = floorf(px), fy0 = floorf(py), fz0 = floorf(pz);
+      wx[q] = px - fx0; wy[q] = py - fy0; wz[q] = pz - fz0;
+      const uint32_t gx = (uint32_t)(int)fx0, gy = (uint32_t)(int)fy0, gz = (uint32_t)(int)fz0;
+#pragma unroll
+      for (int c = 0; c < 8; c++) {
+        const uint32_t idx = grid_index(gx + (c & 1), gy + ((c >> 1) & 1), gz + ((c >> 2) & 1), res, size);
+        v[q][c] = __ldg(reinterpret_cast<const float2*>(a.table) + off + idx);
+      }
     }
-    feat[2 * l] = f0;
-    feat[2 * l + 1] = f1;
+#pragma unroll
+    for (int q = 0; q < HG_GROUP; q++) {
+      float f0 = 0.f, f1 = 0.f;
+#pragma unroll
+      for (int c = 0; c < 8; c++) {  // same corner order and FMA chain as before: bit-identical features
+        const uint32_t dx = c & 1, dy = (c >> 1) & 1, dz = (c >> 2) & 1;
+        const float wgt = (dx ? wx[q] : 1.f - wx[q]) * (dy ? wy[q] : 1.f - wy[q]) * (dz ? wz[q] : 1.f - wz[q]);
+        f0 = fmaf(wgt, v[q][c].x, f0);
+        f1 = fmaf(wgt, v[q][c].y, f1);
+      }
+      feat[2 * (l0 + q)] = f0;
+      feat[2 * (l0 + q) + 1] = f1;
+    }
   }
 }
 
@@ -176,7 +193,8 @@ __global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs
       const float nz = 2.f * ((z - a.aabb_min[2]) / (a.aabb_max[2] - a.aabb_min[2])) - 1.f;
       hash_encode(a, (nx + 1.f) * 0.5f, (ny + 1.f) * 0.5f, (nz + 1.f) * 0.5f, feat);
       if (a.features)
-        for (int k = 0; k < 2 * a.n_levels; k++) a.features[(size_t)i * 2 * a.n_levels + k] = feat[k];
+#pragma unroll
+        for (int k = 0; k < NR_F; k++) a.features[(size_t)i * NR_F + k] = feat[k];
     }
 #pragma unroll
     for (int k = 0; k < NR_F; k += 8) store_act8(sm.A_hi, sm.A_lo, row, k, feat + k);
@@ -230,8 +248,11 @@ __global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs
   if (live) {
 #pragma unroll
     for (int k = 0; k < 32; k++) d[k] += sm.bias[k];
-    if (a.deltas)
-      for (int k = 0; k < a.n_out; k++) a.deltas[(size_t)i * a.n_out + k] = d[k];
+    if (a.deltas) {
+#pragma unroll
+      for (int k = 0; k < 32; k++)
+        if (k < a.n_out) a.deltas[(size_t)i * a.n_out + k] = d[k];
+    }
     a.xyz_out[3 * (size_t)i] = x + d[0]; a.xyz_out[3 * (size_t)i + 1] = y + d[1]; a.xyz_out[3 * (size_t)i + 2] = z + d[2];
 #pragma unroll
     for (int k = 0; k < 3; k++) a.scaling_out[3 * (size_t)i + k] = a.scaling[3 * (size_t)i + k] + d[3 + k];  // scale_offset: logit
@@ -445,8 +466,11 @@ __global__ void __launch_bounds__(NR_TILE, 1) sk_fwd_kernel(SkinArgs a, SkWs w, 
   if (live) {
 #pragma unroll
     for (int k = 0; k < 32; k++) x[k] += sm.bias[k];
-    if (a.logits)
-      for (int k = 0; k < a.n_out; k++) a.logits[(size_t)i * a.n_out + k] = x[k];
+    if (a.logits) {
+#pragma unroll
+      for (int k = 0; k < 25; k++)
+        if (k < a.n_out) a.logits[(size_t)i * a.n_out + k] = x[k];
+    }
     float p[24];
     if (a.n_out == 25) {
       hierarchical_softmax(x, p);
@@ -532,33 +556,49 @@ __global__ void nr_prep_bwd_kernel(NonRigidArgs a, NrWs w, int npad) {
 __device__ __forceinline__ void hash_backward(const NonRigidArgs& a, float x, float y, float z, const float* dfeat /*[2L]*/,
                                               float* __restrict__ dtable, float* dpos /*[3]*/) {
   dpos[0] = dpos[1] = dpos[2] = 0.f;
-  for (int l = 0; l < a.n_levels; l++) {
-    const float scale = a.level_scale[l];
-    const uint32_t res = a.level_res[l];
-    const uint32_t off = a.level_offset[l], size = a.level_offset[l + 1] - off;
-    const float px = fmaf(x, scale, 0.5f), py = fmaf(y, scale, 0.5f), pz = fmaf(z, scale, 0.5f);
-    const float fx0 = floorf(px), fy0 = floorf(py), fz0 = floorf(pz);
-    const float wx = px - fx0, wy = py - fy0, wz = pz - fz0;
-    const uint32_t gx = (uint32_t)(int)fx0, gy = (uint32_t)(int)fy0, gz = (uint32_t)(int)fz0;
-    const float d0 = dfeat[2 * l], d1 = dfeat[2 * l + 1];
-    float gwx = 0.f, gwy = 0.f, gwz = 0.f;
 #pragma unroll
-    for (int c = 0; c < 8; c++) {
-      const uint32_t dx = c & 1, dy = (c >> 1) & 1, dz = (c >> 2) & 1;
-      const float ax = dx ? wx : 1.f - wx, ay = dy ? wy : 1.f - wy, az = dz ? wz : 1.f - wz;
-      const uint32_t idx = grid_index(gx + dx, gy + dy, gz + dz, res, size);
-      const float2 v = __ldg(reinterpret_cast<const float2*>(a.table) + off + idx);
-      const float wgt = ax * ay * az;
-      float* dst = dtable + 2 * (size_t)(off + idx);
-      asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(dst), "f"(wgt * d0), "f"(wgt * d1) : "memory");
-      const float dv = v.x * d0 + v.y * d1;  // dL/dwgt of this corner
-      gwx += (dx ? dv : -dv) * ay * az;
-      gwy += (dy ? dv : -dv) * ax * az;
-      gwz += (dz ? dv : -dv) * ax * ay;
+  for (int l0 = 0; l0 < HG_LEVELS; l0 += HG_GROUP) {  // four levels at a time: 32 table reads in flight (see hash_encode)
+    float2 v[HG_GROUP][8];
+    uint32_t ix[HG_GROUP][8];
+    float wx[HG_GROUP], wy[HG_GROUP], wz[HG_GROUP];
+#pragma unroll
+    for (int q = 0; q < HG_GROUP; q++) {
+      const int l = l0 + q;
+      const float scale = a.level_scale[l];
+      const uint32_t res = a.level_res[l];
+      const uint32_t off = a.level_offset[l], size = a.level_offset[l + 1] - off;
+      const float px = fmaf(x, scale, 0.5f), py = fmaf(y, scale, 0.5f), pz = fmaf(z, scale, 0.5f);
+      const float fx0 = floorf(px), fy0 = floorf(py), fz0 = floorf(pz);
+      wx[q] = px - fx0; wy[q] = py - fy0; wz[q] = pz - fz0;
+      const uint32_t gx = (uint32_t)(int)fx0, gy = (uint32_t)(int)fy0, gz = (uint32_t)(int)fz0;
+#pragma unroll
+      for (int c = 0; c < 8; c++) {
+        ix[q][c] = off + grid_index(gx + (c & 1), gy + ((c >> 1) & 1), gz + ((c >> 2) & 1), res, size);
+        v[q][c] = __ldg(reinterpret_cast<const float2*>(a.table) + ix[q][c]);
+      }
     }
-    dpos[0] = fmaf(gwx, scale, dpos[0]);
-    dpos[1] = fmaf(gwy, scale, dpos[1]);
-    dpos[2] = fmaf(gwz, scale, dpos[2]);
+#pragma unroll
+    for (int q = 0; q < HG_GROUP; q++) {
+      const int l = l0 + q;
+      const float d0 = dfeat[2 * l], d1 = dfeat[2 * l + 1];
+      float gwx = 0.f, gwy = 0.f, gwz = 0.f;
+#pragma unroll
+      for (int c = 0; c < 8; c++) {
+        const uint32_t dx = c & 1, dy = (c >> 1) & 1, dz = (c >> 2) & 1;
+        const float ax = dx ? wx[q] : 1.f - wx[q], ay = dy ? wy[q] : 1.f - wy[q], az = dz ? wz[q] : 1.f - wz[q];
+        const float wgt = ax * ay * az;
+        float* dst = dtable + 2 * (size_t)ix[q][c];
+        asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(dst), "f"(wgt * d0), "f"(wgt * d1) : "memory");
+        const float dv = v[q][c].x * d0 + v[q][c].y * d1;  // dL/dwgt of this corner
+        gwx += (dx ? dv : -dv) * ay * az;
+        gwy += (dy ? dv : -dv) * ax * az;
+        gwz += (dz ? dv : -dv) * ax * ay;
+      }
+      const float scale = a.level_scale[l];
+      dpos[0] = fmaf(gwx, scale, dpos[0]);
+      dpos[1] = fmaf(gwy, scale, dpos[1]);
+      dpos[2] = fmaf(gwz, scale, dpos[2]);
+    }
   }
 }
 
@@ -602,8 +642,11 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
     for (int k = 0; k < 32; k++) g[k] = 0.f;
     float gx = 0.f, gy = 0.f, gz = 0.f;
     if (live) {
-      if (b.dL_ddeltas)
-        for (int k = 0; k < a.n_out; k++) g[k] = b.dL_ddeltas[(size_t)i * a.n_out + k];
+      if (b.dL_ddeltas) {
+#pragma unroll
+        for (int k = 0; k < 32; k++)
+          if (k < a.n_out) g[k] = b.dL_ddeltas[(size_t)i * a.n_out + k];
+      }
       if (b.dL_dxyz_out) { gx = b.dL_dxyz_out[3 * (size_t)i]; gy = b.dL_dxyz_out[3 * (size_t)i + 1]; gz = b.dL_dxyz_out[3 * (size_t)i + 2]; }
       g[0] += gx; g[1] += gy; g[2] += gz;
       float gs[3] = {0.f, 0.f, 0.f};
@@ -642,7 +685,9 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
     {
       float v[32];
       tmem_ld32(tmem_row + 128, v);
-      for (int n = 0; n < a.n_out; n++) atomicAdd(b.dL_dW3 + (size_t)n * NR_H + row, v[n]);
+#pragma unroll
+      for (int n = 0; n < 32; n++)
+        if (n < a.n_out) atomicAdd(b.dL_dW3 + (size_t)n * NR_H + row, v[n]);
     }
     const float* const dWh[2] = {b.dL_dW2, b.dL_dW1};
 #pragma unroll 1
@@ -899,7 +944,8 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
     for (int k = 0; k < 32; k++) g[k] = 0.f;
     if (live) {
       float x[25], gp[24];
-      for (int k = 0; k < a.n_out; k++) x[k] = a.logits[(size_t)i * a.n_out + k];
+#pragma unroll
+      for (int k = 0; k < 25; k++) x[k] = k < a.n_out ? a.logits[(size_t)i * a.n_out + k] : 0.f;
       const float4* gw = reinterpret_cast<const float4*>(b.dL_dweights + (size_t)i * 24);
 #pragma unroll
       for (int k = 0; k < 6; k++) { const float4 t = gw[k]; gp[4 * k] = t.x; gp[4 * k + 1] = t.y; gp[4 * k + 2] = t.z; gp[4 * k + 3] = t.w; }
@@ -931,7 +977,9 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
     {
       float v[32];
       tmem_ld32(tmem_row + 128, v);
-      for (int n = 0; n < a.n_out; n++) atomicAdd(b.dL_dW[4] + (size_t)n * NR_H + row, v[n]);
+#pragma unroll
+      for (int n = 0; n < 25; n++)
+        if (n < a.n_out) atomicAdd(b.dL_dW[4] + (size_t)n * NR_H + row, v[n]);
     }
 #pragma unroll 1
     for (int hl = 0; hl < 4; hl++) {  // hl = 0..2: layers 3..1 (inputs A2..A0), hl = 3: layer 0 (input = normalised xyz)
