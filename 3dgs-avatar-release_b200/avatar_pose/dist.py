@@ -73,6 +73,9 @@ class SymmetricGradSlab:
         if not self.multicast:
             raise RuntimeError("SymmetricGradSlab: no NVLS multicast support for this group (use allreduce_gradients = NCCL)")
         self.byte_offset = int(self.buf.data_ptr()) - int(self.hdl.buffer_ptrs[self.rank])
+        pad = int(getattr(self.hdl, "signal_pad_size", 0) or 0)
+        if pad and pad < (256 + self.world) * 4:  # the kernel keeps its barrier epochs in words [256, 256 + world) of the pad
+            raise RuntimeError(f"SymmetricGradSlab: signal pad of {pad} bytes is too small for the in-kernel barrier")
         self.blocks = max(1, int(blocks))
         self.error_flag = torch.zeros(16, dtype=torch.int32, device=dev)  # [0] error code, [2:10] phase timestamps of block 0
         self._err_host = torch.zeros(1, dtype=torch.int32).pin_memory()  # error word as of the previous call (async copy)

@@ -5,7 +5,8 @@
 // the switch, `multimem.st` writes the result into every replica: each GPU moves 2/N of the slab instead of NCCL's ring
 // traffic, and there is no staging copy.  (A peer-to-peer variant without the multicast object existed in round 1; it never
 // ran on hardware -- this pool always offers multicast -- and was removed; without multicast the caller uses NCCL.)
-// Ranks meet at in-kernel barriers over the symmetric signal pads (one flag per (block, peer)), so the launch sits inside the
+// Ranks meet at in-kernel barriers over the symmetric signal pads (one epoch word per peer, written with a single release store:
+// no remote atomics, nothing to reset), so the launch sits inside the
 // step's CUDA graph right behind pose_bwd_kernel and overlaps its tail through programmatic dependent launch.  Sums are
 // identical on every rank (each slice is reduced once, then broadcast).
 #include "gs_common.cuh"
@@ -16,12 +17,6 @@ namespace {
 #define AR_SPIN_LIMIT (1u << 25)  // a stuck barrier gives up after tens of seconds (error word set) instead of hanging the GPU:
                                   // a rank may legitimately arrive seconds late (graph re-capture after an overflow, data stall)
 #define AR_UNROLL 8
-
-__device__ __forceinline__ uint32_t cas_sys_acq_rel(uint32_t* addr, uint32_t cmp, uint32_t val) {
-  uint32_t old;
-  asm volatile("atom.global.acq_rel.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
-  return old;
-}
 
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
@@ -37,30 +32,29 @@ __device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-// Cross-rank barrier executed by ONE block per rank: thread t < world raises flag [rank] on peer t's signal pad and waits for
-// flag [t] on its own pad (load-spin, so that the waiting side does not flood its own memory with atomics while the peers'
-// remote atomics are trying to land); every flag returns to 0.
-// Returns false when a peer never arrived (error word set): the caller then leaves the slab untouched.  This rank's own flags
-// are cleared either way, so a later call starts from a clean pad.
-__device__ __forceinline__ bool barrier_ranks(uint32_t* const* pads, int rank, int world, uint32_t* error_flag) {
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Cross-rank barrier executed by ONE block per rank, EPOCH based: the k-th barrier of this slab's life writes the number k into
+// word [AR_PAD_BASE + rank] of every peer's signal pad (one release store per peer: a one-way trip through the switch, no
+// remote atomic and no reset traffic) and waits until its own words [AR_PAD_BASE + peer] have all reached k.  Every rank runs
+// the same sequence of calls, so the counters agree; they only ever grow (compared with wrap-around arithmetic).  The words
+// sit 1 KB into the pad, clear of the channels torch's own symmetric-memory barriers use.
+// Returns false when a peer never arrived (error word set): the caller then leaves the slab untouched.
+#define AR_PAD_BASE 256
+__device__ __forceinline__ bool barrier_ranks(uint32_t* const* pads, int rank, int world, uint32_t epoch, uint32_t* error_flag) {
   __shared__ uint32_t s_fail;
   if (threadIdx.x == 0) s_fail = 0u;
   __syncthreads();
   if ((int)threadIdx.x < world) {
-    __threadfence_system();
+    __threadfence_system();  // this rank's earlier writes (its slab / its share of the result) are visible before the signal
     const int peer = (int)threadIdx.x;
-    uint32_t* put = pads[peer] + rank;
-    uint32_t* wait = pads[rank] + peer;
+    st_release_sys(pads[peer] + AR_PAD_BASE + rank, epoch);
+    const uint32_t* wait = pads[rank] + AR_PAD_BASE + peer;
     uint32_t spins = 0;
-    bool ok = true;
-    while (cas_sys_acq_rel(put, 0u, 1u) != 0u)
-      if (++spins > AR_SPIN_LIMIT) { *error_flag = 1u; ok = false; break; }
-    spins = 0;
-    while (ok && ld_acquire_sys(wait) != 1u)
-      if (++spins > AR_SPIN_LIMIT) { *error_flag = 2u; ok = false; break; }
-    *wait = 0u;
-    if (!ok) s_fail = 1u;
-    __threadfence_system();
+    while ((int32_t)(ld_acquire_sys(wait) - epoch) < 0)
+      if (++spins > AR_SPIN_LIMIT) { *error_flag = 2u; s_fail = 1u; break; }
   }
   __syncthreads();
   return s_fail == 0u;
@@ -99,14 +93,16 @@ slab_allreduce_kernel(long long n4, int rank, int world, void* const* peers, uin
   const long long per = (n4 + world - 1) / world;
   const long long begin = min(n4, per * rank), end = min(n4, begin + per);
   const long long stride = (long long)gridDim.x * AR_THREADS, t0 = (long long)blockIdx.x * AR_THREADS + threadIdx.x;
-  // local control words behind the stamps: [12] go flag, [13] blocks done
+  // local control words behind the stamps: [12] go flag, [13] blocks done, [14] barriers completed so far (the epoch)
   uint32_t* const go = error_flag + 12;
   uint32_t* const done = error_flag + 13;
+  uint32_t* const epoch = error_flag + 14;
   __shared__ bool s_last;
   auto open_gate = [&]() {   // every rank's slab is complete: block 0 meets the peers, the other blocks wait for block 0
     if (blockIdx.x == 0) {
-      const bool ok = barrier_ranks(pads, rank, world, error_flag);
+      const bool ok = barrier_ranks(pads, rank, world, *epoch + 1u, error_flag);
       if (threadIdx.x == 0) st_release_gpu(go, ok ? 1u : 2u);  // 2 = a peer is missing: nobody touches the slab
+      __syncthreads();  // the other threads of THIS block read the gate too
     } else {
       if (threadIdx.x == 0) {
         uint32_t spins = 0;
@@ -143,8 +139,8 @@ slab_allreduce_kernel(long long n4, int rank, int world, void* const* peers, uin
     }
     stamp(2);
     if (last_block()) {  // every block's stores are out: meet the peers, then leave the control words clean
-      if (healthy) barrier_ranks(pads, rank, world, error_flag);  // every slice has reached every replica
-      if (threadIdx.x == 0) { *go = 0u; *done = 0u; }
+      if (healthy) barrier_ranks(pads, rank, world, *epoch + 2u, error_flag);  // every slice has reached every replica
+      if (threadIdx.x == 0) { *go = 0u; *done = 0u; if (healthy) *epoch += 2u; }
       if (threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); stamps[3] = t; }
     }
     return;

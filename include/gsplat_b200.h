@@ -445,12 +445,14 @@ int pose_encoder_backward(const PoseEncoderBackwardArgs* args, void* stream);
  * The reference has no multi-GPU path; this is the one collective the data-parallel step needs, as one kernel
  * behind pose_backward instead of an NCCL call.  The slab must live in symmetric memory (same allocation on every rank,
  * peers' addresses exchanged once): `peer_ptrs[world]` / `signal_pads[world]` are DEVICE arrays of the peers' buffer and
- * signal-pad addresses (zero-initialised pads, >= blocks * world * 4 bytes), `multicast_ptr` the NVLS multicast address of
+ * signal-pad addresses (zero-initialised pads of >= (256 + world) * 4 bytes; words [256, 256 + world) belong to this kernel and
+ * hold barrier epochs that only grow -- the first 1 KB is left to torch's own symmetric-memory barriers), `multicast_ptr` the NVLS multicast address of
  * the buffer (required: without NVLS multicast support the caller uses NCCL).  Every rank must call it with the same
  * n / blocks; ranks meet at in-kernel barriers.  `error_flag`: 16 device u32; [0] is set if a barrier gives up after tens of
  * seconds (a peer never arrived): the slab is then left UNTOUCHED, this rank's flags are cleared, and every later call is a
- * no-op until the caller resets [0]; [2:10] receive four 64-bit %globaltimer stamps of block 0 (start, after the first
- * barrier, after the data phase, end). */
+ * no-op until the caller resets [0] (after a timeout the ranks' epoch counters may disagree: re-create the slab); [2:10] receive
+ * four 64-bit %globaltimer stamps of block 0 (start, after the first barrier, after the data phase, end); [12:15] are the kernel's
+ * own control words (gate, block counter, barrier epoch) and must start at zero. */
 typedef struct SlabAllReduceArgs {
   int64_t n;               /* floats, multiple of 4 */
   int32_t rank, world;
