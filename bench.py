@@ -439,7 +439,8 @@ def ncu_traffic(stage):
     import glob
     import re
     natural = lambda p: [int(t) if t.isdigit() else t for t in re.split(r"(\d+)", os.path.basename(p))]  # r1_v13 after r1_v7
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_kernels.json")), key=natural, reverse=True)
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_kernels.json")) + glob.glob(os.path.join(ROOT, "profiles", "*", "*_kernels.json")),
+                   key=natural, reverse=True)
     mult = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0}
     names = (stage + "_kernel", stage.replace("_fwd", "") + "_kernel")
     for path in files:
@@ -948,6 +949,10 @@ def ours_main(args):
                 ent.update(achieved=amount / (ms * 1e-3) / 1e12, peak=fp32_peak, unit="TFLOP/s")
             ent["frac"] = ent["achieved"] / ent["peak"]
         stages[k] = ent
+    # SURVEY 8(d), end to end: the time the step's algorithmic work would take with every stage at ITS roofline, over the step
+    ideal_ms = sum(1e3 * work[k][1] / ((hbm_peak * G) if work[k][0] == "hbm" else (fp32_peak * 1e12)) for k in st if work[k][1] is not None)
+    roof_step = {"ideal_ms": ideal_ms, "measured_ms": ms_train, "frac": ideal_ms / ms_train,
+                 "what": "sum over the seven stages of (algorithmic bytes or flops / the stage's measured peak) divided by the measured step"}
     dom = max(st, key=lambda k: st[k])
     roof = dict(stages[dom])
     roof.update(kernel=dom, traffic=ncu_traffic(dom), peak_source=(f"{peak_kind} MEASURED_PEAKS.json hbm_gbs" if roof["bound"] == "hbm" else
@@ -997,7 +1002,7 @@ def ours_main(args):
             "render_e2e": {"value": world * 1e3 / ms_render_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d - 3 * H * W * 4,
                            "d2h_bytes_per_step": 3 * H * W * 4},
             "eager_ms_per_step": ms_eager, "ms_per_step_hot_l2": float(np.mean(hot)), "ms_per_step_p10_p90": [float(np.percentile(ts_train, 10)), float(np.percentile(ts_train, 90))],
-            "gpu_launches": launches, "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": fp32_peak,
+            "gpu_launches": launches, "roofline": roof, "roofline_step": roof_step, "stages": stages, "fp32_peak_tflops_measured": fp32_peak,
             "cpu_baseline": cpu, "ref_cuda": ref_cuda, "return_opacity_step": mask_pass, "full_iteration": full_iter, "default_config_step": default_step, "render_seq64": render_seq, "stress_1m": stress, "allreduce_check": ar_check, "clocks": sampler.summary(), "regrows": _C.stats["capacity_regrows"]}
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)

@@ -2,6 +2,7 @@
 git-ignored baseline/_ref/) on the seeded scenes of tests/scenes.py.  Run on a GPU box:
 
     gpurun -- 'python tests/golden/make_ref_cuda_golden.py gpurun_out/golden'   # then copy the .npz files to tests/golden/
+    gpurun -- 'python tests/golden/make_ref_cuda_golden.py gpurun_out/golden cfgA'   # the two bench-size scenes, compact form
 
 The fixtures pin the CPU oracle (tests/test_oracle_golden.py, CPU-only): integer artefacts (radii, sorted keys, point
 list, tile ranges, n_contrib) must match the reference build bit for bit, images <= 1e-5, gradients <= 1e-4 relative.
@@ -110,5 +111,49 @@ def main(outdir):
         print(name, "N", int(out["N"]), "visible", int(vis.sum()), "img mean", float(out["color"].mean()))
 
 
+CFGA = {"cfgA_random_init_50k_512": lambda: scenes.avatar_scene(P=50000, W=512, H=512, random_init=True),
+        "cfgA_trained_like_50k_512": lambda: scenes.avatar_scene(P=50000, W=512, H=512, random_init=False)}
+CROP = (slice(192, 320), slice(192, 320))  # full-resolution window over the torso
+
+
+def sha(a):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def compact(out, H, W):
+    """The bench-size fixture (BASELINE.json configs[1]/[2]: 50 000 Gaussians, 512x512) in a few hundred KB: SHA-256 of the
+    integer artefacts (bit-exactness needs no more), the contributor counts themselves (uint16, compresses well), a full
+    resolution window + 16x16 block means of the image and of final_T, and per-tensor sums + the first rows of every gradient."""
+    nc = out["n_contrib"].reshape(H, W)
+    assert int(nc.max()) < 65536
+    col, fT = out["color"], out["final_T"].reshape(H, W)
+    c = dict(N=out["N"], sha_keys=sha(out["keys"]), sha_point_list=sha(out["point_list"]), sha_ranges=sha(out["ranges"]),
+             sha_radii=sha(out["radii"].astype(np.int32)), sha_tiles_touched=sha(out["tiles_touched"]), sha_n_contrib=sha(nc.astype(np.uint32)),
+             n_contrib=nc.astype(np.uint16), color_crop=col[:, CROP[0], CROP[1]].copy(), final_T_crop=fT[CROP[0], CROP[1]].copy(),
+             color_block_mean=col.astype(np.float64).reshape(3, H // 16, 16, W // 16, 16).mean((2, 4)),
+             final_T_block_mean=fT.astype(np.float64).reshape(H // 16, 16, W // 16, 16).mean((1, 3)))
+    for k, v in out.items():
+        if k.startswith("grad_"):
+            v64 = v.astype(np.float64)
+            c[k + "_sum"], c[k + "_abs_sum"], c[k + "_max_abs"] = v64.sum(), np.abs(v64).sum(), np.abs(v64).max()
+            c[k + "_head"] = v.reshape(v.shape[0], -1)[:2048].copy()
+    return c
+
+
+def main_cfgA(outdir):
+    os.makedirs(outdir, exist_ok=True)
+    ref = load_ref()
+    for name, mk in CFGA.items():
+        sc = mk()
+        out = run(ref, sc, 3, 1.0)
+        np.savez_compressed(os.path.join(outdir, f"ref_cuda_{name}.npz"), **compact(out, sc["H"], sc["W"]))
+        print(name, "N", int(out["N"]), "E_fwd", int(out["n_contrib"].astype(np.int64).sum()))
+
+
 if __name__ == "__main__":
-    main(sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "golden"))
+    d = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "golden")
+    if len(sys.argv) > 2 and sys.argv[2] == "cfgA":
+        main_cfgA(d)
+    else:
+        main(d)

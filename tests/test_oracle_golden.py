@@ -52,3 +52,44 @@ def test_oracle_matches_reference_cuda(name):
             ref = G["grad_" + k].astype(np.float64)
             err = np.abs(bw[v].astype(np.float64) - ref).max() / max(np.abs(ref).max(), 1e-30)
             assert err <= 1e-4, (k, err)
+
+
+CFGA = {"cfgA_random_init_50k_512": lambda: scenes.avatar_scene(P=50000, W=512, H=512, random_init=True),
+        "cfgA_trained_like_50k_512": lambda: scenes.avatar_scene(P=50000, W=512, H=512, random_init=False)}
+
+
+@pytest.mark.parametrize("name", sorted(CFGA))
+def test_oracle_matches_reference_cuda_at_bench_size(name):
+    """The oracle pinned AT SCALE: BASELINE.json configs[1]/[2] (50 000 Gaussians, 512x512), random-init and trained-like, against
+    the reference's CUDA build (compact fixtures of tests/golden/make_ref_cuda_golden.py `cfgA`: SHA-256 of the integer artefacts,
+    the contributor counts, an image window + 16x16 block means, gradient sums + leading rows)."""
+    import hashlib
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+    sc = CFGA[name]()
+    G = np.load(os.path.join(GOLD, f"ref_cuda_{name}.npz"))
+    fw = scenes.oracle_forward(sc, 3, 1.0)
+    H, W = sc["H"], sc["W"]
+    assert fw["N"] == int(G["N"])
+    assert sha(fw["radii"].astype(np.int32)) == str(G["sha_radii"])
+    assert sha(fw["tiles_touched"].astype(np.uint32)) == str(G["sha_tiles_touched"])
+    assert sha(fw["keys"].astype(np.uint64)) == str(G["sha_keys"])
+    assert sha(fw["point_list"].astype(np.uint32)) == str(G["sha_point_list"])
+    assert sha(fw["ranges"].astype(np.uint32)) == str(G["sha_ranges"])
+    nc = fw["n_contrib"].reshape(H, W)
+    assert int((nc != G["n_contrib"]).sum()) == 0, "per-pixel contributor counts differ from the reference build"
+    assert sha(nc.astype(np.uint32)) == str(G["sha_n_contrib"])
+    crop = (slice(192, 320), slice(192, 320))
+    assert np.abs(fw["color"][:, crop[0], crop[1]] - G["color_crop"]).max() <= 1e-5
+    assert np.abs(fw["final_T"].reshape(H, W)[crop] - G["final_T_crop"]).max() <= 1e-5
+    blk = fw["color"].astype(np.float64).reshape(3, H // 16, 16, W // 16, 16).mean((2, 4))
+    assert np.abs(blk - G["color_block_mean"]).max() <= 1e-5
+    blkT = fw["final_T"].astype(np.float64).reshape(H // 16, 16, W // 16, 16).mean((1, 3))
+    assert np.abs(blkT - G["final_T_block_mean"]).max() <= 1e-5
+    bw = gs_oracle.backward(fw, scenes.l1_grad(fw["color"]))
+    for k, v in GRADS.items():
+        if "grad_" + k + "_head" in G:
+            ours = bw[v].astype(np.float64)
+            scale = max(float(G["grad_" + k + "_max_abs"]), 1e-30)
+            head = G["grad_" + k + "_head"].astype(np.float64)
+            assert np.abs(ours.reshape(ours.shape[0], -1)[:head.shape[0]] - head).max() / scale <= 1e-4, k
+            assert abs(np.abs(ours).sum() - float(G["grad_" + k + "_abs_sum"])) <= 1e-4 * float(G["grad_" + k + "_abs_sum"]) + 1e-12, k
