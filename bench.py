@@ -355,12 +355,12 @@ def render_sequence(hp, args, rank, world, dev, GraphedStep, eager, n_frames=64)
 
 def stress_step(dev, GraphedStep, eager, flush, n_steps, P=1_000_000, W=1920, H=1080):
     """BASELINE.json configs[3]: 1M Gaussians at 1080p, fwd+bwd of posing + rasterizer.  The 50k avatar proxy is densified to
-    1M points in the same capsules (scales shrunk by the cube root of the density ratio, times 6 so that the screen footprint
-    stays a few pixels at 1080p from 3.5 m)."""
+    1M points in the same capsules (scales shrunk by the cube root of the density ratio, times 14 so that a splat still covers
+    a few tiles at 1080p from 3.5 m: N is of the order of 1e7 pairs, SURVEY 8's assumption for this configuration)."""
     import synth
     g = synth.canonical_gaussians(P, seed=5, random_init=True)
     g = dict(g)
-    g["scaling"] = (g["scaling"] + np.log(6.0) - np.log(P / 50_000.0) / 3.0).astype(np.float32)
+    g["scaling"] = (g["scaling"] + np.log(14.0) - np.log(P / 50_000.0) / 3.0).astype(np.float32)
     wts = synth.skinning_weights(g["xyz"])
     hp = HotPath(dev, g, wts, W, H)
     fr = dict(cam=synth.camera(W=W, H=H, fx=537.0 * H / 512.0, fy=537.0 * H / 512.0), pose=synth.pose(1), target=synth.l1_target(H, W, seed=2))
