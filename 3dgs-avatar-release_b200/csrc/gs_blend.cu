@@ -493,21 +493,15 @@ static_assert(GS_SEG == 128, "the backward blend unrolls four 32-entry batches p
 // channel (colour 1, no colour gradient) is one more term of the same sum and every geometry gradient comes out as the
 // sum of the reference's two backward calls.
 template <bool OP, bool POLY>
-__global__ void __launch_bounds__(kWarps * 32, GS_BWD_MINBLOCKS)
-blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H, int grid_x,
-                 const uint32_t* __restrict__ seg_off, int tiles, const uint2* __restrict__ items,
-                 const float4* __restrict__ ckpt,
-                 const float* __restrict__ bg, const GsRec* __restrict__ rec, const float* __restrict__ final_Ts,
-                 const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
-                 float* __restrict__ acc /*[P,GS_ACC]*/,
-                 const float* __restrict__ ckpt_op, const float* __restrict__ dL_dop_pix,
-                 const uint32_t* __restrict__ rowmask, GsHeader* __restrict__ hdr) {
-  GS_PDL_PROLOGUE();
-  extern __shared__ __align__(16) unsigned char bwd_smem[];
-  if (blockIdx.x >= seg_off[tiles]) return;
+__device__ __forceinline__ void
+blend_bwd_item(const uint32_t item_index, BwdSlab& sl, const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H,
+               int grid_x, const uint32_t* __restrict__ seg_off, const uint2* __restrict__ items, const float4* __restrict__ ckpt,
+               const float* __restrict__ bg, const GsRec* __restrict__ rec, const float* __restrict__ final_Ts,
+               const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels, float* __restrict__ acc /*[P,GS_ACC]*/,
+               const float* __restrict__ ckpt_op, const float* __restrict__ dL_dop_pix, const uint32_t* __restrict__ rowmask,
+               GsHeader* __restrict__ hdr) {
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  BwdSlab& sl = reinterpret_cast<BwdSlab*>(bwd_smem)[w];
-  const uint2 item = items[blockIdx.x];
+  const uint2 item = items[item_index];
   const int tile = (int)item.x;
   const uint2 range = ranges[tile];
   const int len = (int)(range.y - range.x);
@@ -659,6 +653,31 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   if (lane == 0 && nblend) atomicAdd(&hdr->evals_blended, (unsigned long long)nblend);
 }
 
+// The grid is sized from the pair CAPACITY (the host does not know N), capped at GS_BWD_MAX_GRID CTAs that walk the frame's
+// items with a grid stride: a capacity left large by an earlier, bigger frame then costs nothing (it used to launch one CTA
+// per possible item -- 69 000 mostly empty CTAs, 130 us instead of 62, after a 1M-Gaussian frame had raised the capacity).
+#define GS_BWD_MAX_GRID (148 * GS_BWD_MINBLOCKS * 8)
+template <bool OP, bool POLY>
+__global__ void __launch_bounds__(kWarps * 32, GS_BWD_MINBLOCKS)
+blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H, int grid_x,
+                 const uint32_t* __restrict__ seg_off, int tiles, const uint2* __restrict__ items,
+                 const float4* __restrict__ ckpt,
+                 const float* __restrict__ bg, const GsRec* __restrict__ rec, const float* __restrict__ final_Ts,
+                 const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
+                 float* __restrict__ acc /*[P,GS_ACC]*/,
+                 const float* __restrict__ ckpt_op, const float* __restrict__ dL_dop_pix,
+                 const uint32_t* __restrict__ rowmask, GsHeader* __restrict__ hdr) {
+  GS_PDL_PROLOGUE();
+  extern __shared__ __align__(16) unsigned char bwd_smem[];
+  BwdSlab& sl = reinterpret_cast<BwdSlab*>(bwd_smem)[threadIdx.x >> 5];
+  const uint32_t n_items = seg_off[tiles];
+  for (uint32_t it = blockIdx.x; it < n_items; it += gridDim.x) {
+    blend_bwd_item<OP, POLY>(it, sl, ranges, list, W, H, grid_x, seg_off, items, ckpt, bg, rec, final_Ts, n_contrib, dL_dpixels, acc,
+                             ckpt_op, dL_dop_pix, rowmask, hdr);
+    __syncwarp();  // the warp's slab is reused by its next item
+  }
+}
+
 }  // namespace
 
 int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, const GsScratch& s,
@@ -693,7 +712,8 @@ int gs_launch_blend_bwd(const GsBackwardArgs& a, const GsGeom& g, const GsImage&
                  : (poly ? blend_bwd_kernel<false, true> : blend_bwd_kernel<false, false>);
   const size_t smem = kWarps * sizeof(BwdSlab);
   if (gs_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != GS_OK) return GS_ERR_CUDA;
-  gs_launch(kern, dim3((unsigned)l.max_items), dim3(kWarps * 32), smem, st,
+  const unsigned grid = (unsigned)(l.max_items < (size_t)GS_BWD_MAX_GRID ? l.max_items : (size_t)GS_BWD_MAX_GRID);
+  gs_launch(kern, dim3(grid), dim3(kWarps * 32), smem, st,
       im.ranges, l.point_list, a.width, a.height, gx, im.seg_off, gx * gy, l.items, l.ckpt, a.background, g.rec,
       im.final_T, im.n_contrib, a.dL_dpix, g.acc,
       (const float*)l.ckpt_op, a.dL_dopacity_pix, (const uint32_t*)l.rowmask, g.hdr);

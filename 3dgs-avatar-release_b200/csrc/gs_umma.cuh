@@ -61,7 +61,7 @@ __device__ __forceinline__ void nr_mbar_wait(unsigned long long* bar, uint32_t p
 }
 // ---- bulk asynchronous copy global -> shared (TMA, 1-D): one thread moves a whole operand; the bytes land on an mbarrier ----
 // (the per-thread LDG -> STS loops these replace kept ONE load in flight per thread: with 4 warps per SM the operand loads were
-// a chain of L2 round trips and ~60 % of the MLP kernels' time, profiles/r2/r2_v2_mlp_kernels.json)
+// a chain of L2 round trips and ~60 % of the MLP kernels' time, profiles/r2/r2_v2_mlp_before_tma.json)
 __device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
