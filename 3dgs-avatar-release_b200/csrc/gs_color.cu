@@ -395,12 +395,13 @@ __device__ __forceinline__ void sh_bases_1_bwd(int deg, float x, float y, float 
   d[0] = dx; d[1] = dy; d[2] = dz;
 }
 
-__global__ void __launch_bounds__(NR_TILE, 1)
+__global__ void __launch_bounds__(BW_THREADS, 1)
 color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ saved, int ntiles) {
   extern __shared__ __align__(1024) unsigned char bw_smem_raw[];
   BwSmem& sm = *reinterpret_cast<BwSmem*>(bw_smem_raw);
   const ColorArgs& a = b.fwd;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, row = tid;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int row = tid & (NR_TILE - 1), half = tid >> 7;  // two threads per Gaussian: half 0 / 1 split the columns (BW_THREADS)
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)), "r"(256u) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -410,16 +411,16 @@ color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ 
     nr_mbar_init(&sm.ld_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  for (int k = tid; k < 5 * BW_H; k += NR_TILE) (&sm.dbias[0][0])[k] = 0.f;
+  for (int k = tid; k < 5 * BW_H; k += BW_THREADS) (&sm.dbias[0][0])[k] = 0.f;
   {  // units 64..127 of G and A are never written afterwards: zero the buffers once
     uint4* z = reinterpret_cast<uint4*>(sm.G_hi);  // G_hi, G_lo, A_hi, A_lo are contiguous
-    for (int q = tid; q < 4 * BW_H * BW_H * 2 / 16; q += NR_TILE) z[q] = make_uint4(0u, 0u, 0u, 0u);
+    for (int q = tid; q < 4 * BW_H * BW_H * 2 / 16; q += BW_THREADS) z[q] = make_uint4(0u, 0u, 0u, 0u);
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = sm.tmem_base;
-  const uint32_t tmem_row = tmem + ((uint32_t)(warp * 32) << 16);
+  const uint32_t tmem_row = tmem + ((uint32_t)((warp & 3) * 32) << 16);
   const int F = a.feature_dim, S = cl_n_sh(a.sh_degree), R = a.non_rigid_dim, n_in = F + S + R, d_in = n_in + a.latent_dim;
   uint32_t phase = 0, ld_phase = 0;
   uint32_t signs[4];  // LeakyReLU branches of this thread's row in the activations loaded last
@@ -435,17 +436,17 @@ color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ 
     float g[32];
 #pragma unroll
     for (int k = 0; k < 32; k++) g[k] = 0.f;
-    if (live) {
+    if (live && half == 0) {
 #pragma unroll
       for (int k = 0; k < 3; k++) {  // sigmoid'
         const float c = a.colors[3 * (size_t)i + k];
         g[k] = b.dL_dcolors[3 * (size_t)i + k] * c * (1.f - c);
       }
     }
-    store_grad32(sm, row, 0, g, sm.dbias[2], lane);
+    if (half == 0) store_grad32(sm, row, 0, g, sm.dbias[2], lane);
     // ---- lin2: Z2 = A1 . W2^T ----
     bw_wait_loads(sm, ld_phase);
-    bw_row_signs(sm, row, CL_H, signs);  // of A1
+    bw_row_signs(sm, row, 32 * half, 32 * half + 32, signs);  // of A1 (this thread's 32 columns)
     bw_sync_mma_inputs();
     if (tid == 0) {
       issue_dw(tmem + 128, sm.A_hi, sm.A_lo, sm.G_hi, sm.G_lo, CL_NOUT);    // dW2^T [k_in][n_out] (rows >= 64 are zero)
@@ -455,7 +456,7 @@ color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ 
     if (tid == 0)  // A / W are free again: A0 and W1^T
       bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st + CL_SAVE_LAYER, st + CL_SAVE_LAYER + HALF, HALF * 2, sm.W_hi, sm.W_lo, w.w1t_hi,
                          w.w1t_lo, CL_H * CL_H * 2);
-    {
+    if (half == 0) {  // warp-uniform
       float v[32];
       tmem_ld32(tmem_row + 128, v);
       if (row < CL_H)
@@ -463,8 +464,8 @@ color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ 
     }
 #pragma unroll 1
     for (int hl = 0; hl < 2; hl++) {  // hl = 0: lin1 (input A0), hl = 1: lin0 (input = composed per-Gaussian row)
-#pragma unroll 1
-      for (int c = 0; c < CL_H / 32; c++) {
+      {
+        const int c = half;  // this thread's 32 of the 64 columns
         float v[32];
         tmem_ld32(tmem_row + c * 32, v);
 #pragma unroll
@@ -472,7 +473,7 @@ color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ 
         store_grad32(sm, row, c * 32, v, sm.dbias[1 - hl], lane);
       }
       bw_wait_loads(sm, ld_phase);                          // this layer's A_in and W^T
-      if (hl == 0) bw_row_signs(sm, row, CL_H, signs);      // of A0, for the next epilogue
+      if (hl == 0) bw_row_signs(sm, row, 32 * half, 32 * half + 32, signs);  // of A0, for the next epilogue
       bw_sync_mma_inputs();                                 // G complete; every row has read its dA from TMEM and its signs
       if (tid == 0) {
         issue_dw(tmem + 128, sm.G_hi, sm.G_lo, sm.A_hi, sm.A_lo, CL_H);     // dW [n_out][k_in] (rows >= 64 are zero)
@@ -483,9 +484,10 @@ color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ 
         bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st, st + HALF, HALF * 2, sm.W_hi, sm.W_lo, w.w0t_hi, w.w0t_lo, CL_H * CL_H * 2);
       if (row < CL_H) {
         if (hl == 0) {
-          flush_dw_rows(tmem_row + 128, CL_H, b.dL_dW1 + (size_t)row * CL_H);
+          flush_dw_rows(tmem_row + 128, 32 * half, 32 * half + 32, b.dL_dW1 + (size_t)row * CL_H);
         } else {  // rows of W0 are d_in floats apart (not 16-byte aligned in general): scalar reductions
-          for (int c = 0; c < CL_K0; c += 32) {
+          {
+            const int c = 32 * half;
             float v[32];
             tmem_ld32(tmem_row + 128 + c, v);
 #pragma unroll
@@ -496,7 +498,7 @@ color_bwd_kernel(ColorBackwardArgs b, ClWs w, const __nv_bfloat16* __restrict__ 
       }
     }
     // ---- dL/d(composed input) of this thread's Gaussian: features | SH basis of the view direction | non-rigid feature ----
-    {
+    if (half == 0) {  // warp-uniform: one thread per Gaussian composes the input adjoint
       float din[CL_K0];
       tmem_ld32(tmem_row, din);
       tmem_ld32(tmem_row + 32, din + 32);
@@ -619,7 +621,7 @@ extern "C" int color_backward(const ColorBackwardArgs* args, void* workspace, si
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  color_bwd_kernel<<<ntiles < sms ? ntiles : sms, NR_TILE, smem, st>>>(b, w, (const __nv_bfloat16*)saved, ntiles);
+  color_bwd_kernel<<<ntiles < sms ? ntiles : sms, BW_THREADS, smem, st>>>(b, w, (const __nv_bfloat16*)saved, ntiles);
   if (a.latent_dim > 0) color_bwd_finish_kernel<<<4, 256, 0, st>>>(b);
   return gs_check(cudaGetLastError());
 }

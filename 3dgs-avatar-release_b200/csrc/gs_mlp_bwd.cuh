@@ -18,6 +18,10 @@
 namespace {
 
 constexpr int BW_H = 128;  // hidden width = rows of a tile
+// Two threads per row: warps w and w + 4 own the same TMEM lane quadrant (a warp reaches lanes 32 * (warp % 4) ...) and split
+// the COLUMNS of every epilogue / flush between them.  With one thread per row (4 warps per SM, one per scheduler) every
+// kernel of this family was bound by the latency of its own instruction chains.
+constexpr int BW_THREADS = 256;
 
 struct BwSmem {
   __nv_bfloat16 G_hi[BW_H * BW_H], G_lo[BW_H * BW_H];  // dL/dZ of the current layer, [point][unit]
@@ -37,9 +41,9 @@ __device__ __forceinline__ void bw_wait_loads(BwSmem& sm, uint32_t& ld_phase) {
 
 // Signs of this thread's row of the saved activations in sm.A (bit k of the 128-bit mask = activation (row, k) > 0), taken right
 // after the load so that the buffer can be refilled while the epilogue that needs the signs still runs.
-__device__ __forceinline__ void bw_row_signs(const BwSmem& sm, int row, int units, uint32_t* signs /*[4]*/) {
+__device__ __forceinline__ void bw_row_signs(const BwSmem& sm, int row, int unit_begin, int unit_end, uint32_t* signs /*[4]*/) {
   signs[0] = signs[1] = signs[2] = signs[3] = 0u;
-  for (int s8 = 0; s8 < units / 8; s8++) {
+  for (int s8 = unit_begin / 8; s8 < unit_end / 8; s8++) {
     const uint4 h = *reinterpret_cast<const uint4*>(sm.A_hi + core_idx(row, s8 * 8, BW_H));
     const uint32_t w[4] = {h.x, h.y, h.z, h.w};
     uint32_t bits = 0u;
@@ -153,8 +157,8 @@ __device__ __forceinline__ void bw_commit_wait(BwSmem& sm, bool issuer, uint32_t
 }
 
 // dW partial [128 rows (this thread = row) x ncols] in TMEM -> global, row-major destination with `ld` floats per row
-__device__ __forceinline__ void flush_dw_rows(uint32_t tmem_row, int ncols, float* dst_row) {
-  for (int c = 0; c < ncols; c += 32) {
+__device__ __forceinline__ void flush_dw_rows(uint32_t tmem_row, int col_begin, int ncols, float* dst_row) {
+  for (int c = col_begin; c < ncols; c += 32) {
     float v[32];
     tmem_ld32(tmem_row + c, v);
 #pragma unroll

@@ -90,9 +90,10 @@ __device__ __forceinline__ uint32_t grid_index(uint32_t x, uint32_t y, uint32_t 
 // scheduler nothing else hides the latency, and level by level the encode was 16 dependent L2 round trips per Gaussian.
 constexpr int HG_GROUP = 4;
 constexpr int HG_LEVELS = NR_F / 2;  // n_levels is fixed by the MLP's input width (nr_inputs_ok): loops unroll, features stay in registers
+template <int L_BEGIN, int L_END>  // levels [L_BEGIN, L_END): the two threads of a Gaussian take half of the levels each
 __device__ __forceinline__ void hash_encode(const NonRigidArgs& a, float x, float y, float z, float* feat /*[2L]*/) {
 #pragma unroll
-  for (int l0 = 0; l0 < HG_LEVELS; l0 += HG_GROUP) {
+  for (int l0 = L_BEGIN; l0 < L_END; l0 += HG_GROUP) {
     float2 v[HG_GROUP][8];
     float wx[HG_GROUP], wy[HG_GROUP], wz[HG_GROUP];
 #pragma unroll
@@ -145,9 +146,9 @@ struct NrSmem {
 };
 
 // bias + LeakyReLU(0.01) epilogue of a hidden layer: TMEM accumulators of this thread's row -> next layer's A operand
-__device__ __forceinline__ void hidden_epilogue(NrSmem& sm, uint32_t tmem_row, int row) {
+__device__ __forceinline__ void hidden_epilogue(NrSmem& sm, uint32_t tmem_row, int row, int half) {
 #pragma unroll 1
-  for (int c = 0; c < NR_H / 32; c++) {
+  for (int c = 2 * half; c < 2 * half + 2; c++) {  // this thread's 64 of the 128 columns (two threads per row)
     float v[32];
     tmem_ld32(tmem_row + c * 32, v);
 #pragma unroll
@@ -160,11 +161,13 @@ __device__ __forceinline__ void hidden_epilogue(NrSmem& sm, uint32_t tmem_row, i
   }
 }
 
-__global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs w, int npad, __nv_bfloat16* __restrict__ saved) {
+__global__ void __launch_bounds__(BW_THREADS, 1) nr_fwd_kernel(NonRigidArgs a, NrWs w, int npad, __nv_bfloat16* __restrict__ saved) {
   extern __shared__ __align__(1024) unsigned char nr_smem_raw[];
   NrSmem& sm = *reinterpret_cast<NrSmem*>(nr_smem_raw);
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int row = tid;                         // one Gaussian per thread = one row of the 128-row MMA tile
+  // one Gaussian = one row of the 128-row MMA tile, TWO threads per row (warps w and w + 4 share a TMEM lane quadrant): they
+  // split the hash-grid levels and the columns of every epilogue (gs_mlp_bwd.cuh: BW_THREADS)
+  const int row = tid & (NR_TILE - 1), half = tid >> 7;
   const int i = blockIdx.x * NR_TILE + row;
   const bool live = i < a.P;
 
@@ -191,15 +194,19 @@ __global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs
       const float nx = 2.f * ((x - a.aabb_min[0]) / (a.aabb_max[0] - a.aabb_min[0])) - 1.f;
       const float ny = 2.f * ((y - a.aabb_min[1]) / (a.aabb_max[1] - a.aabb_min[1])) - 1.f;
       const float nz = 2.f * ((z - a.aabb_min[2]) / (a.aabb_max[2] - a.aabb_min[2])) - 1.f;
-      hash_encode(a, (nx + 1.f) * 0.5f, (ny + 1.f) * 0.5f, (nz + 1.f) * 0.5f, feat);
-      if (a.features)
+      if (half == 0) hash_encode<0, HG_LEVELS / 2>(a, (nx + 1.f) * 0.5f, (ny + 1.f) * 0.5f, (nz + 1.f) * 0.5f, feat);
+      else hash_encode<HG_LEVELS / 2, HG_LEVELS>(a, (nx + 1.f) * 0.5f, (ny + 1.f) * 0.5f, (nz + 1.f) * 0.5f, feat);
+      if (a.features) {
 #pragma unroll
-        for (int k = 0; k < NR_F; k++) a.features[(size_t)i * NR_F + k] = feat[k];
+        for (int k = 0; k < NR_F; k++)
+          if ((k >= NR_F / 2) == (half == 1)) a.features[(size_t)i * NR_F + k] = feat[k];
+      }
     }
 #pragma unroll
-    for (int k = 0; k < NR_F; k += 8) store_act8(sm.A_hi, sm.A_lo, row, k, feat + k);
+    for (int k = 0; k < NR_F; k += 8)
+      if ((k >= NR_F / 2) == (half == 1)) store_act8(sm.A_hi, sm.A_lo, row, k, feat + k);
   }
-  sm.bias[tid] = w.bias0[tid];
+  if (tid < NR_H) sm.bias[tid] = w.bias0[tid];
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to the tensor core
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -211,7 +218,7 @@ __global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs
     copy16(save_tile + 128 * 32, sm.A_lo, 128 * 32 * 2);
   }
   const uint32_t tmem = sm.tmem_base;
-  const uint32_t tmem_row = tmem + ((uint32_t)(warp * 32) << 16);  // this warp's 32-lane quadrant
+  const uint32_t tmem_row = tmem + ((uint32_t)((warp & 3) * 32) << 16);  // this warp's 32-lane quadrant
 
   const __nv_bfloat16* next_hi[3] = {w.w1_hi, w.w2_hi, w.w3_hi};
   const __nv_bfloat16* next_lo[3] = {w.w1_lo, w.w2_lo, w.w3_lo};
@@ -225,14 +232,16 @@ __global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs
     if (tid == 0)
       bulk_load_operands(&sm.ld_bar, nullptr, nullptr, nullptr, nullptr, 0u, sm.W_hi, sm.W_lo, next_hi[layer], next_lo[layer],
                          (uint32_t)((layer == 2 ? npad : NR_H) * NR_H * 2));
-    hidden_epilogue(sm, tmem_row, row);
-    __syncthreads();  // everyone has read the old bias (and written its row of the new activations)
+    hidden_epilogue(sm, tmem_row, row, half);
+    __syncthreads();  // everyone has read the old bias (and written its part of the new activations)
     if (save_tile) {
       copy16(save_tile + NR_SAVE_IN + (size_t)layer * NR_SAVE_LAYER, sm.A_hi, 128 * 128 * 2);
       copy16(save_tile + NR_SAVE_IN + (size_t)layer * NR_SAVE_LAYER + 128 * 128, sm.A_lo, 128 * 128 * 2);
     }
-    if (layer < 2) sm.bias[tid] = next_b[layer][tid];
-    else sm.bias[tid] = tid < a.n_out ? a.b3[tid] : 0.f;
+    if (tid < NR_H) {
+      if (layer < 2) sm.bias[tid] = next_b[layer][tid];
+      else sm.bias[tid] = tid < a.n_out ? a.b3[tid] : 0.f;
+    }
     nr_mbar_wait(&sm.ld_bar, (uint32_t)(layer + 1) & 1u);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -244,8 +253,8 @@ __global__ void __launch_bounds__(NR_TILE, 1) nr_fwd_kernel(NonRigidArgs a, NrWs
   nr_mbar_wait(&sm.bar, 1u);
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   float d[32];
-  tmem_ld32(tmem_row, d);  // columns >= npad hold stale values of the previous layer: never used
-  if (live) {
+  if (half == 0) tmem_ld32(tmem_row, d);  // (warp-uniform) columns >= npad hold stale values of the previous layer: never used
+  if (live && half == 0) {
 #pragma unroll
     for (int k = 0; k < 32; k++) d[k] += sm.bias[k];
     if (a.deltas) {
@@ -310,7 +319,7 @@ static int nonrigid_forward_impl(const NonRigidArgs* args, void* workspace, size
   // per call: function attributes are per DEVICE, and one process may drive several
   if (gs_check(cudaFuncSetAttribute(nr_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NrSmem) + 1024)) != GS_OK)
     return GS_ERR_CUDA;
-  nr_fwd_kernel<<<(a.P + NR_TILE - 1) / NR_TILE, NR_TILE, sizeof(NrSmem) + 1024, st>>>(a, w, npad, (__nv_bfloat16*)saved);
+  nr_fwd_kernel<<<(a.P + NR_TILE - 1) / NR_TILE, BW_THREADS, sizeof(NrSmem) + 1024, st>>>(a, w, npad, (__nv_bfloat16*)saved);
   return gs_check(cudaGetLastError());
 }
 
@@ -392,10 +401,11 @@ __device__ __forceinline__ void hierarchical_softmax(const float* x, float* p) {
   for (int k = 0; k < 2; k++) { p[22 + k] = p[20 + k] * s[22 + k]; p[20 + k] = p[20 + k] * (1.f - s[22 + k]); }
 }
 
-__global__ void __launch_bounds__(NR_TILE, 1) sk_fwd_kernel(SkinArgs a, SkWs w, __nv_bfloat16* __restrict__ saved) {
+__global__ void __launch_bounds__(BW_THREADS, 1) sk_fwd_kernel(SkinArgs a, SkWs w, __nv_bfloat16* __restrict__ saved) {
   extern __shared__ __align__(1024) unsigned char nr_smem_raw[];
   NrSmem& sm = *reinterpret_cast<NrSmem*>(nr_smem_raw);
-  const int tid = threadIdx.x, warp = tid >> 5, row = tid;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int row = tid & (NR_TILE - 1), half = tid >> 7;  // two threads per Gaussian (see nr_fwd_kernel)
   const int i = blockIdx.x * NR_TILE + row;
   const bool live = i < a.P;
   if (warp == 0) {
@@ -417,10 +427,10 @@ __global__ void __launch_bounds__(NR_TILE, 1) sk_fwd_kernel(SkinArgs a, SkWs w, 
       for (int k = 0; k < 3; k++)  // AABB.normalize(sym=True), dataset_utils.py:66-71
         in[k] = 2.f * ((a.xyz[3 * (size_t)i + k] - a.aabb_min[k]) / (a.aabb_max[k] - a.aabb_min[k])) - 1.f;
     }
-    store_act8(sm.A_hi, sm.A_lo, row, 0, in);
-    store_act8(sm.A_hi, sm.A_lo, row, 8, in + 8);
+    if (half == 0) store_act8(sm.A_hi, sm.A_lo, row, 0, in);
+    else store_act8(sm.A_hi, sm.A_lo, row, 8, in + 8);
   }
-  sm.bias[tid] = a.b[0][tid];
+  if (tid < NR_H) sm.bias[tid] = a.b[0][tid];
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -432,7 +442,7 @@ __global__ void __launch_bounds__(NR_TILE, 1) sk_fwd_kernel(SkinArgs a, SkWs w, 
     copy16(save_tile + 128 * SK_K0, sm.A_lo, 128 * SK_K0 * 2);
   }
   const uint32_t tmem = sm.tmem_base;
-  const uint32_t tmem_row = tmem + ((uint32_t)(warp * 32) << 16);
+  const uint32_t tmem_row = tmem + ((uint32_t)((warp & 3) * 32) << 16);
 #pragma unroll 1
   for (int layer = 0; layer < 4; layer++) {  // four hidden layers
     if (tid == 0) issue_layer(tmem, sm.A_hi, sm.A_lo, sm.W_hi, sm.W_lo, layer == 0 ? SK_K0 : NR_H, NR_H, &sm.bar);
@@ -444,14 +454,16 @@ __global__ void __launch_bounds__(NR_TILE, 1) sk_fwd_kernel(SkinArgs a, SkWs w, 
       else
         bulk_load_operands(&sm.ld_bar, nullptr, nullptr, nullptr, nullptr, 0u, sm.W_hi, sm.W_lo, w.w4_hi, w.w4_lo, SK_NOUT * NR_H * 2);
     }
-    hidden_epilogue(sm, tmem_row, row);
+    hidden_epilogue(sm, tmem_row, row, half);
     __syncthreads();
     if (save_tile) {
       copy16(save_tile + SK_SAVE_IN + (size_t)layer * NR_SAVE_LAYER, sm.A_hi, 128 * 128 * 2);
       copy16(save_tile + SK_SAVE_IN + (size_t)layer * NR_SAVE_LAYER + 128 * 128, sm.A_lo, 128 * 128 * 2);
     }
-    if (layer < 3) sm.bias[tid] = a.b[layer + 1][tid];
-    else sm.bias[tid] = tid < a.n_out ? a.b[4][tid] : 0.f;
+    if (tid < NR_H) {
+      if (layer < 3) sm.bias[tid] = a.b[layer + 1][tid];
+      else sm.bias[tid] = tid < a.n_out ? a.b[4][tid] : 0.f;
+    }
     nr_mbar_wait(&sm.ld_bar, (uint32_t)(layer + 1) & 1u);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -462,8 +474,8 @@ __global__ void __launch_bounds__(NR_TILE, 1) sk_fwd_kernel(SkinArgs a, SkWs w, 
   nr_mbar_wait(&sm.bar, 0u);  // fifth commit
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   float x[32];
-  tmem_ld32(tmem_row, x);
-  if (live) {
+  if (half == 0) tmem_ld32(tmem_row, x);  // warp-uniform
+  if (live && half == 0) {
 #pragma unroll
     for (int k = 0; k < 32; k++) x[k] += sm.bias[k];
     if (a.logits) {
@@ -524,7 +536,7 @@ static int skinning_forward_impl(const SkinArgs* args, void* workspace, size_t w
   // per call: function attributes are per DEVICE, and one process may drive several
   if (gs_check(cudaFuncSetAttribute(sk_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NrSmem) + 1024)) != GS_OK)
     return GS_ERR_CUDA;
-  sk_fwd_kernel<<<(a.P + NR_TILE - 1) / NR_TILE, NR_TILE, sizeof(NrSmem) + 1024, st>>>(a, w, (__nv_bfloat16*)saved);
+  sk_fwd_kernel<<<(a.P + NR_TILE - 1) / NR_TILE, BW_THREADS, sizeof(NrSmem) + 1024, st>>>(a, w, (__nv_bfloat16*)saved);
   return gs_check(cudaGetLastError());
 }
 
@@ -553,11 +565,12 @@ __global__ void nr_prep_bwd_kernel(NonRigidArgs a, NrWs w, int npad) {
 
 // Backward of hash_encode for one point: scatters dL/dtable (8 corners x levels) and returns dL/d(x01) through the trilinear
 // weights (tiny-cuda-nn's grid backward + input gradient; same indexing as hash_encode above).
+template <int L_BEGIN, int L_END>  // levels [L_BEGIN, L_END): the two threads of a Gaussian take half of the levels each
 __device__ __forceinline__ void hash_backward(const NonRigidArgs& a, float x, float y, float z, const float* dfeat /*[2L]*/,
                                               float* __restrict__ dtable, float* dpos /*[3]*/) {
   dpos[0] = dpos[1] = dpos[2] = 0.f;
 #pragma unroll
-  for (int l0 = 0; l0 < HG_LEVELS; l0 += HG_GROUP) {  // four levels at a time: 32 table reads in flight (see hash_encode)
+  for (int l0 = L_BEGIN; l0 < L_END; l0 += HG_GROUP) {  // four levels at a time: 32 table reads in flight (see hash_encode)
     float2 v[HG_GROUP][8];
     uint32_t ix[HG_GROUP][8];
     float wx[HG_GROUP], wy[HG_GROUP], wz[HG_GROUP];
@@ -602,12 +615,13 @@ __device__ __forceinline__ void hash_backward(const NonRigidArgs& a, float x, fl
   }
 }
 
-__global__ void __launch_bounds__(NR_TILE, 1)
+__global__ void __launch_bounds__(BW_THREADS, 1)
 nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __restrict__ saved, int ntiles) {
   extern __shared__ __align__(1024) unsigned char bw_smem_raw[];
   BwSmem& sm = *reinterpret_cast<BwSmem*>(bw_smem_raw);
   const NonRigidArgs& a = b.fwd;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, row = tid;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int row = tid & (NR_TILE - 1), half = tid >> 7;  // two threads per Gaussian: half 0 / 1 split the columns (BW_THREADS)
   if (warp == 0) {  // TMEM: columns [0,128) dA of the current layer, [128,256) the tile's dW partial
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)), "r"(256u) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -617,12 +631,12 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
     nr_mbar_init(&sm.ld_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  for (int k = tid; k < 5 * BW_H; k += NR_TILE) (&sm.dbias[0][0])[k] = 0.f;
+  for (int k = tid; k < 5 * BW_H; k += BW_THREADS) (&sm.dbias[0][0])[k] = 0.f;
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = sm.tmem_base;
-  const uint32_t tmem_row = tmem + ((uint32_t)(warp * 32) << 16);
+  const uint32_t tmem_row = tmem + ((uint32_t)((warp & 3) * 32) << 16);
   const int in0 = NR_F + a.n_cond;
   uint32_t phase = 0, ld_phase = 0;
   uint32_t signs[4];  // LeakyReLU branches of this thread's row in the activations loaded last
@@ -641,7 +655,7 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
 #pragma unroll
     for (int k = 0; k < 32; k++) g[k] = 0.f;
     float gx = 0.f, gy = 0.f, gz = 0.f;
-    if (live) {
+    if (live && half == 0) {
       if (b.dL_ddeltas) {
 #pragma unroll
         for (int k = 0; k < 32; k++)
@@ -669,10 +683,10 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
       dq.w = -az * gr.x + ay * gr.y - ax * gr.z + gr.w;
       *reinterpret_cast<float4*>(b.dL_drotation + 4 * (size_t)i) = dq;
     }
-    store_grad32(sm, row, 0, g, sm.dbias[3], lane);
+    if (half == 0) store_grad32(sm, row, 0, g, sm.dbias[3], lane);
     // ---- layer 3: Z3 = A2 . W3^T ----
     bw_wait_loads(sm, ld_phase);
-    bw_row_signs(sm, row, NR_H, signs);  // of A2: used by the epilogue that forms G2
+    bw_row_signs(sm, row, 64 * half, 64 * half + 64, signs);  // of A2 (this thread's columns): used by the epilogue that forms G2
     bw_sync_mma_inputs();
     if (tid == 0) {
       issue_dw(tmem + 128, sm.A_hi, sm.A_lo, sm.G_hi, sm.G_lo, npad);   // dW3^T [k_in][n_out]
@@ -682,7 +696,7 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
     if (tid == 0)  // A / W are free again (MMAs done, signs taken before the barrier above): next layer's operands, A1 and W2^T
       bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st + NR_SAVE_IN + NR_SAVE_LAYER, st + NR_SAVE_IN + NR_SAVE_LAYER + 128 * 128,
                          128 * 128 * 2, sm.W_hi, sm.W_lo, w.w2t_hi, w.w2t_lo, NR_H * NR_H * 2);
-    {
+    if (half == 0) {  // warp-uniform
       float v[32];
       tmem_ld32(tmem_row + 128, v);
 #pragma unroll
@@ -694,7 +708,7 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
     for (int hl = 0; hl < 3; hl++) {  // hl = 0: layer 2 (input A1), 1: layer 1 (input A0), 2: layer 0 (input = hash features)
       // G of this layer from dA (TMEM) and the sign of the saved activation still in sm.A
 #pragma unroll 1
-      for (int c = 0; c < NR_H / 32; c++) {
+      for (int c = 2 * half; c < 2 * half + 2; c++) {  // this thread's 64 columns
         float v[32];
         tmem_ld32(tmem_row + c * 32, v);
 #pragma unroll
@@ -703,7 +717,7 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
       }
       const int kin = hl < 2 ? NR_H : NR_F;
       bw_wait_loads(sm, ld_phase);                             // this layer's A_in and W^T (issued after the previous MMAs)
-      if (hl < 2) bw_row_signs(sm, row, NR_H, signs);          // of A1 / A0, for the next epilogue
+      if (hl < 2) bw_row_signs(sm, row, 64 * half, 64 * half + 64, signs);  // of A1 / A0, for the next epilogue
       bw_sync_mma_inputs();                                    // G complete; every row has read its dA from TMEM and its signs
       if (tid == 0) {
         issue_dw(tmem + 128, sm.G_hi, sm.G_lo, sm.A_hi, sm.A_lo, kin);      // dW [n_out][k_in]
@@ -718,24 +732,31 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
           bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st, st + 128 * NR_F, 128 * NR_F * 2, sm.W_hi, sm.W_lo, w.w0t_hi, w.w0t_lo,
                              NR_F * NR_H * 2);
       }
-      if (hl < 2) flush_dw_rows(tmem_row + 128, NR_H, const_cast<float*>(dWh[hl]) + (size_t)row * NR_H);
-      else flush_dw_rows(tmem_row + 128, NR_F, b.dL_dW0 + (size_t)row * in0);
+      if (hl < 2) flush_dw_rows(tmem_row + 128, 64 * half, 64 * half + 64, const_cast<float*>(dWh[hl]) + (size_t)row * NR_H);
+      else if (half == 0) flush_dw_rows(tmem_row + 128, 0, NR_F, b.dL_dW0 + (size_t)row * in0);
     }
-    // ---- hash grid: dL/dfeatures of this thread's Gaussian -> table scatter + dL/dxyz ----
+    // ---- hash grid: dL/dfeatures of this Gaussian -> table scatter + dL/dxyz; the two threads of a row take eight levels each,
+    // the second one passes its share of dL/dx through shared memory (sm.G is free: its last readers, the MMAs, are done) ----
     {
       float df[32];
       tmem_ld32(tmem_row, df);
+      float dpos[3] = {0.f, 0.f, 0.f};
+      float ex = 1.f, ey = 1.f, ez = 1.f;
       if (live) {
         const float x = a.xyz[3 * (size_t)i], y = a.xyz[3 * (size_t)i + 1], z = a.xyz[3 * (size_t)i + 2];
-        const float ex = a.aabb_max[0] - a.aabb_min[0], ey = a.aabb_max[1] - a.aabb_min[1], ez = a.aabb_max[2] - a.aabb_min[2];
+        ex = a.aabb_max[0] - a.aabb_min[0]; ey = a.aabb_max[1] - a.aabb_min[1]; ez = a.aabb_max[2] - a.aabb_min[2];
         const float nx = 2.f * ((x - a.aabb_min[0]) / ex) - 1.f, ny = 2.f * ((y - a.aabb_min[1]) / ey) - 1.f;
         const float nz = 2.f * ((z - a.aabb_min[2]) / ez) - 1.f;
-        float dpos[3];
-        hash_backward(a, (nx + 1.f) * 0.5f, (ny + 1.f) * 0.5f, (nz + 1.f) * 0.5f, df, b.dL_dtable, dpos);
-        // x01 = (x - min) / extent
-        b.dL_dxyz[3 * (size_t)i] = gx + dpos[0] / ex;
-        b.dL_dxyz[3 * (size_t)i + 1] = gy + dpos[1] / ey;
-        b.dL_dxyz[3 * (size_t)i + 2] = gz + dpos[2] / ez;
+        if (half == 0) hash_backward<0, HG_LEVELS / 2>(a, (nx + 1.f) * 0.5f, (ny + 1.f) * 0.5f, (nz + 1.f) * 0.5f, df, b.dL_dtable, dpos);
+        else hash_backward<HG_LEVELS / 2, HG_LEVELS>(a, (nx + 1.f) * 0.5f, (ny + 1.f) * 0.5f, (nz + 1.f) * 0.5f, df, b.dL_dtable, dpos);
+      }
+      float* const xch = reinterpret_cast<float*>(sm.G_hi);
+      if (half == 1) { xch[3 * row] = dpos[0]; xch[3 * row + 1] = dpos[1]; xch[3 * row + 2] = dpos[2]; }
+      __syncthreads();
+      if (live && half == 0) {  // x01 = (x - min) / extent
+        b.dL_dxyz[3 * (size_t)i] = gx + (dpos[0] + xch[3 * row]) / ex;
+        b.dL_dxyz[3 * (size_t)i + 1] = gy + (dpos[1] + xch[3 * row + 1]) / ey;
+        b.dL_dxyz[3 * (size_t)i + 2] = gz + (dpos[2] + xch[3 * row + 2]) / ez;
       }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -745,7 +766,7 @@ nr_bwd_kernel(NonRigidBackwardArgs b, NrWs w, int npad, const __nv_bfloat16* __r
   __syncthreads();
   {
     float* const dbg[4] = {b.dL_db0, b.dL_db1, b.dL_db2, b.dL_db3};
-    for (int l = 0; l < 4; l++) {
+    for (int l = 0; l < 4 && tid < BW_H; l++) {
       const float v = sm.dbias[l][tid];
       if (v != 0.f && (l < 3 || tid < a.n_out)) atomicAdd(dbg[l] + tid, v);
     }
@@ -806,7 +827,7 @@ extern "C" int nonrigid_backward(const NonRigidBackwardArgs* args, void* workspa
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  nr_bwd_kernel<<<ntiles < sms ? ntiles : sms, NR_TILE, smem, st>>>(b, w, npad, (const __nv_bfloat16*)saved, ntiles);
+  nr_bwd_kernel<<<ntiles < sms ? ntiles : sms, BW_THREADS, smem, st>>>(b, w, npad, (const __nv_bfloat16*)saved, ntiles);
   nr_bwd_finish_kernel<<<32, 256, 0, st>>>(b);
   return gs_check(cudaGetLastError());
 }
@@ -907,12 +928,13 @@ __device__ __forceinline__ void hierarchical_softmax_bwd(const float* x, const f
   }
 }
 
-__global__ void __launch_bounds__(NR_TILE, 1)
+__global__ void __launch_bounds__(BW_THREADS, 1)
 sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ saved, int ntiles) {
   extern __shared__ __align__(1024) unsigned char bw_smem_raw[];
   BwSmem& sm = *reinterpret_cast<BwSmem*>(bw_smem_raw);
   const SkinArgs& a = b.fwd;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, row = tid;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int row = tid & (NR_TILE - 1), half = tid >> 7;  // two threads per Gaussian: half 0 / 1 split the columns (BW_THREADS)
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tmem_base)), "r"(256u) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -922,12 +944,12 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
     nr_mbar_init(&sm.ld_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  for (int k = tid; k < 5 * BW_H; k += NR_TILE) (&sm.dbias[0][0])[k] = 0.f;
+  for (int k = tid; k < 5 * BW_H; k += BW_THREADS) (&sm.dbias[0][0])[k] = 0.f;
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = sm.tmem_base;
-  const uint32_t tmem_row = tmem + ((uint32_t)(warp * 32) << 16);
+  const uint32_t tmem_row = tmem + ((uint32_t)((warp & 3) * 32) << 16);
   uint32_t phase = 0, ld_phase = 0;
   uint32_t signs[4];  // LeakyReLU branches of this thread's row in the activations loaded last
 
@@ -942,7 +964,7 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
     float g[32];
 #pragma unroll
     for (int k = 0; k < 32; k++) g[k] = 0.f;
-    if (live) {
+    if (live && half == 0) {
       float x[25], gp[24];
 #pragma unroll
       for (int k = 0; k < 25; k++) x[k] = k < a.n_out ? a.logits[(size_t)i * a.n_out + k] : 0.f;
@@ -961,10 +983,10 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
         for (int k = 0; k < 24; k++) g[k] = p[k] * (gp[k] - dot);
       }
     }
-    store_grad32(sm, row, 0, g, sm.dbias[4], lane);
+    if (half == 0) store_grad32(sm, row, 0, g, sm.dbias[4], lane);
     // ---- output layer: Z4 = A3 . W4^T ----
     bw_wait_loads(sm, ld_phase);
-    bw_row_signs(sm, row, NR_H, signs);  // of A3
+    bw_row_signs(sm, row, 64 * half, 64 * half + 64, signs);  // of A3 (this thread's columns)
     bw_sync_mma_inputs();
     if (tid == 0) {
       issue_dw(tmem + 128, sm.A_hi, sm.A_lo, sm.G_hi, sm.G_lo, SK_NOUT);   // dW4^T [k_in][n_out]
@@ -974,7 +996,7 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
     if (tid == 0)  // A / W are free again: A2 and W3^T
       bulk_load_operands(&sm.ld_bar, sm.A_hi, sm.A_lo, st + SK_SAVE_IN + 2 * NR_SAVE_LAYER, st + SK_SAVE_IN + 2 * NR_SAVE_LAYER + 128 * 128,
                          128 * 128 * 2, sm.W_hi, sm.W_lo, w.wht_hi[2], w.wht_lo[2], NR_H * NR_H * 2);
-    {
+    if (half == 0) {  // warp-uniform
       float v[32];
       tmem_ld32(tmem_row + 128, v);
 #pragma unroll
@@ -984,7 +1006,7 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
 #pragma unroll 1
     for (int hl = 0; hl < 4; hl++) {  // hl = 0..2: layers 3..1 (inputs A2..A0), hl = 3: layer 0 (input = normalised xyz)
 #pragma unroll 1
-      for (int c = 0; c < NR_H / 32; c++) {
+      for (int c = 2 * half; c < 2 * half + 2; c++) {  // this thread's 64 columns
         float v[32];
         tmem_ld32(tmem_row + c * 32, v);
 #pragma unroll
@@ -993,7 +1015,7 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
       }
       const int kin = hl < 3 ? NR_H : SK_K0;
       bw_wait_loads(sm, ld_phase);                             // this layer's A_in and W^T
-      if (hl < 3) bw_row_signs(sm, row, NR_H, signs);          // for the next epilogue
+      if (hl < 3) bw_row_signs(sm, row, 64 * half, 64 * half + 64, signs);  // for the next epilogue
       bw_sync_mma_inputs();                                    // G complete; every row has read its dA from TMEM and its signs
       if (tid == 0) {
         issue_dw(tmem + 128, sm.G_hi, sm.G_lo, sm.A_hi, sm.A_lo, kin);
@@ -1010,14 +1032,14 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
                              SK_K0 * NR_H * 2);
       }
       if (hl < 3) {
-        flush_dw_rows(tmem_row + 128, NR_H, b.dL_dW[3 - hl] + (size_t)row * NR_H);
-      } else {
+        flush_dw_rows(tmem_row + 128, 64 * half, 64 * half + 64, b.dL_dW[3 - hl] + (size_t)row * NR_H);
+      } else if (half == 0) {
         float v[32];
         tmem_ld32(tmem_row + 128, v);
         for (int k = 0; k < 3; k++) atomicAdd(b.dL_dW[0] + (size_t)row * 3 + k, v[k]);
       }
     }
-    {
+    if (half == 0) {
       float dx[32];
       tmem_ld32(tmem_row, dx);  // dL/d(normalised xyz) in columns 0..2
       if (live)
@@ -1027,7 +1049,7 @@ sk_bwd_kernel(SkinBackwardArgs b, SkWs w, const __nv_bfloat16* __restrict__ save
     __syncthreads();
   }
   __syncthreads();
-  for (int l = 0; l < 5; l++) {
+  for (int l = 0; l < 5 && tid < BW_H; l++) {
     const float v = sm.dbias[l][tid];
     if (v != 0.f && (l < 4 || tid < a.n_out)) atomicAdd(b.dL_db[l] + tid, v);
   }
@@ -1066,6 +1088,6 @@ extern "C" int skinning_backward(const SkinBackwardArgs* args, void* workspace, 
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  sk_bwd_kernel<<<ntiles < sms ? ntiles : sms, NR_TILE, smem, st>>>(b, w, (const __nv_bfloat16*)saved, ntiles);
+  sk_bwd_kernel<<<ntiles < sms ? ntiles : sms, BW_THREADS, smem, st>>>(b, w, (const __nv_bfloat16*)saved, ntiles);
   return gs_check(cudaGetLastError());
 }
