@@ -310,6 +310,119 @@ bin_count_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __re
   }
 }
 
+// Work plans of the two blend kernels.  One CTA.
+//  * backward: every tile list is cut into segments of GS_SEG entries; seg_off = exclusive prefix of the segment counts over
+//    tiles (seg_off[tiles] = number of items), items[] = (tile, segment);
+//  * forward: every non-empty tile list is cut into chunks of GS_FWD_CHUNK entries; fitems[] = (tile, chunk, index of the
+//    successor item, index of the predecessor item), ordered by the number of chunks that REMAIN in the tile's chain
+//    (this one included), longest first -- "longest remaining path first": the deep tiles, whose chains are the critical path
+//    of avatar frames, start at once, every last chunk comes at the end, and an item's predecessor (one more remaining)
+//    always has a smaller index: CTAs are dispatched in index order, which makes the hand-off wait of blend_fwd_kernel
+//    deadlock-free.  With nch(t) = chunks of tile t, pos(t) = rank of t in descending nch order (counting sort),
+//    ge[k] = #tiles with nch > k and base = exclusive prefix of ge, item (t, c) with r = nch - c remaining sits at
+//    n_fitems - base[r] + pos(t).  The empty tiles follow as one item each (their pixels still get the background).
+__device__ __forceinline__ uint32_t block_scan_incl_1024(uint32_t v, uint32_t* s_w, uint32_t* total) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint32_t incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  __syncthreads();  // s_w may still be read from the previous scan
+  if (lane == 31) s_w[w] = incl;
+  __syncthreads();
+  uint32_t wv = s_w[lane], wincl = wv;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xFFFFFFFFu, wincl, o);
+    if (lane >= o) wincl += t;
+  }
+  *total = __shfl_sync(0xFFFFFFFFu, wincl, 31);
+  return incl + __shfl_sync(0xFFFFFFFFu, wincl - wv, w);
+}
+
+// `ranges` may live in global memory (plan_kernel) or in shared memory (the plan block of bin_place_kernel).  1024 threads.
+__device__ __forceinline__ void plan_body(int tiles, const uint2* ranges, uint32_t* __restrict__ seg_off, uint2* __restrict__ items,
+                                          uint32_t max_items, uint4* __restrict__ fitems, uint32_t max_fitems,
+                                          GsHeader* __restrict__ hdr) {
+  __shared__ uint32_t s_w[32];
+  __shared__ uint32_t s_hist[GS_FWD_NCH_BINS];  // tiles per chunk count -> cursor of the counting sort
+  __shared__ uint32_t s_base[GS_FWD_NCH_BINS];  // base[r] = sum over k < r of ge[k]
+  __shared__ uint32_t s_total, s_nonempty;
+  const int tid = threadIdx.x;
+  for (int k = tid; k < GS_FWD_NCH_BINS; k += 1024) s_hist[k] = 0;
+  __syncthreads();
+  uint32_t carry = 0;
+  for (int t0 = 0; t0 < tiles; t0 += 1024) {
+    const int t = t0 + tid;
+    uint32_t nseg = 0;
+    if (t < tiles) {
+      const uint2 r = ranges[t];
+      const uint32_t len = r.y - r.x;
+      nseg = (len + GS_SEG - 1) / GS_SEG;
+      atomicAdd(&s_hist[min((len + GS_FWD_CHUNK - 1) / GS_FWD_CHUNK, (uint32_t)GS_FWD_NCH_BINS - 1)], 1u);
+    }
+    uint32_t total;
+    const uint32_t off = carry + block_scan_incl_1024(nseg, s_w, &total) - nseg;
+    if (t < tiles) {
+      seg_off[t] = off;
+      for (uint32_t k = 0; k < nseg; k++)
+        if (off + k < max_items) items[off + k] = make_uint2((uint32_t)t, k);
+    }
+    carry += total;
+  }
+  if (tid == 0) seg_off[tiles] = carry < max_items ? carry : max_items;
+  __syncthreads();
+  // ge[k] = #tiles with chunk count > k = tiles - inclusive prefix of hist; base = exclusive prefix of ge.
+  // Two elements per thread (GS_FWD_NCH_BINS = 2 * 1024).
+  static_assert(GS_FWD_NCH_BINS == 2048, "two bins per thread");
+  {
+    const uint32_t h0 = s_hist[2 * tid], h1 = s_hist[2 * tid + 1];
+    uint32_t total;
+    const uint32_t incl = block_scan_incl_1024(h0 + h1, s_w, &total);
+    const uint32_t ge0 = (uint32_t)tiles - (incl - h1), ge1 = (uint32_t)tiles - incl;
+    uint32_t total2;
+    const uint32_t incl2 = block_scan_incl_1024(ge0 + ge1, s_w, &total2);
+    __syncthreads();
+    s_hist[2 * tid] = ge0; s_hist[2 * tid + 1] = ge1;                          // cursor: tiles with a larger chunk count come first
+    s_base[2 * tid] = incl2 - ge0 - ge1; s_base[2 * tid + 1] = incl2 - ge1;
+    if (tid == 0) {
+      s_total = total2;                                                        // items of the non-empty tiles
+      hdr->n_fitems = total2 < max_fitems ? total2 : max_fitems;
+      s_nonempty = ge0;                                                        // ge[0]
+      hdr->n_empty_tiles = h0;                                                 // hist[0]
+    }
+  }
+  __syncthreads();
+  const uint32_t n_items = s_total, n_nonempty = s_nonempty;
+  for (int t = tid; t < tiles; t += 1024) {
+    const uint2 r = ranges[t];
+    const uint32_t len = r.y - r.x;
+    const uint32_t nch = min((len + GS_FWD_CHUNK - 1) / GS_FWD_CHUNK, (uint32_t)GS_FWD_NCH_BINS - 1);
+    const uint32_t pos = atomicAdd(&s_hist[nch], 1u);
+    if (nch == 0) {  // empty tile: one item behind everything else
+      const uint32_t fi = n_items + (pos - n_nonempty);
+      if (fi < max_fitems) fitems[fi] = make_uint4((uint32_t)t, 0u, 0xFFFFFFFFu, 0xFFFFFFFFu);
+      continue;
+    }
+    for (uint32_t c = 0; c < nch; c++) {
+      const uint32_t rem = nch - c;  // chunks remaining in this tile's chain, this one included
+      const uint32_t fi = n_items - s_base[rem] + pos;
+      if (fi < max_fitems)
+        fitems[fi] = make_uint4((uint32_t)t, c, rem > 1 ? n_items - s_base[rem - 1] + pos : 0xFFFFFFFFu,
+                                c > 0 ? n_items - s_base[rem + 1] + pos : 0xFFFFFFFFu);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(1024)
+plan_kernel(int tiles, const uint2* __restrict__ ranges, uint32_t* __restrict__ seg_off, uint2* __restrict__ items,
+            uint32_t max_items, uint4* __restrict__ fitems, uint32_t max_fitems, GsHeader* __restrict__ hdr) {
+  GS_PDL_PROLOGUE();
+  plan_body(tiles, ranges, seg_off, items, max_items, fitems, max_fitems, hdr);
+}
+
 // tiles <= 2 * GS_BIN_THREADS.  Block 0 also publishes the tile ranges (identifyTileRanges, rasterizer_impl.cu:116-138:
 // empty tiles stay (0,0)) and the pair count.  FUSED: the grid is small enough to be co-resident (the launcher checks), the
 // kernel does the counting itself and crosses a grid-wide barrier instead of a kernel boundary; otherwise
@@ -320,7 +433,8 @@ bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __re
                  const uint32_t* __restrict__ hist_chain, const uint32_t* __restrict__ tiles_touched,
                  const uint32_t* __restrict__ rect, int grid_x, int tiles, uint32_t* blockcount, uint32_t* tile_total,
                  unsigned long long cap, uint32_t* __restrict__ list, uint2* __restrict__ ranges, GsHeader* __restrict__ hdr,
-                 uint32_t* grid_bar) {
+                 uint32_t* grid_bar, uint32_t* __restrict__ seg_off, uint2* __restrict__ items, uint32_t max_items,
+                 uint4* __restrict__ fitems, uint32_t max_fitems) {
   GS_PDL_PROLOGUE();
   extern __shared__ __align__(16) unsigned char s_raw[];
   uint16_t* s_off = reinterpret_cast<uint16_t*>(s_raw);                                  // [32][tiles]
@@ -328,25 +442,37 @@ bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __re
   __shared__ uint32_t s_wsum[32];
   __shared__ uint4 s_stage[32][32];
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  for (int k = tid; k < 16 * tiles; k += GS_BIN_THREADS) reinterpret_cast<uint32_t*>(s_off)[k] = 0;
-  const uint32_t* sorted_gid = depth_result_buffer(hist_chain, (unsigned long long)P, tid) ? dval1 : dval0;  // + barrier
-  const BinWarp bw = bin_load(P, blockIdx.x * GS_BIN_THREADS + tid, sorted_gid, tiles_touched, rect, s_stage[w], lane);
-  bin_warp_walk<false>(bw, s_stage[w], grid_x, s_off + (size_t)w * tiles, nullptr, nullptr, 0ull, lane);
+  // FUSED: the LAST block of the grid places nothing.  It waits for the counts like everybody else, derives the tile ranges in
+  // shared memory and builds the work plans of the two blend kernels (plan_body) WHILE the other blocks place the pairs: the
+  // separate plan_kernel launch (8 us behind the placement) disappears from the step.
+  const bool plan_block = FUSED && blockIdx.x == gridDim.x - 1;
+  const unsigned nblocks = FUSED ? gridDim.x - 1 : gridDim.x;
+  BinWarp bw;
+  bw.total = 0; bw.excl = 0; bw.nz = false;
+  if (!plan_block) {  // block-uniform
+    for (int k = tid; k < 16 * tiles; k += GS_BIN_THREADS) reinterpret_cast<uint32_t*>(s_off)[k] = 0;
+    const uint32_t* sorted_gid = depth_result_buffer(hist_chain, (unsigned long long)P, tid) ? dval1 : dval0;  // + barrier
+    bw = bin_load(P, blockIdx.x * GS_BIN_THREADS + tid, sorted_gid, tiles_touched, rect, s_stage[w], lane);
+    bin_warp_walk<false>(bw, s_stage[w], grid_x, s_off + (size_t)w * tiles, nullptr, nullptr, 0ull, lane);
+  }
   if (FUSED) {
     __syncthreads();
-    for (int t = tid; t < tiles; t += GS_BIN_THREADS) {
-      uint32_t sum = 0;
+    if (!plan_block)
+      for (int t = tid; t < tiles; t += GS_BIN_THREADS) {
+        uint32_t sum = 0;
 #pragma unroll 8
-      for (int k = 0; k < 32; k++) sum += s_off[(size_t)k * tiles + t];
-      blockcount[(size_t)blockIdx.x * tiles + t] = sum;
-      if (sum) atomicAdd(&tile_total[t], sum);
-    }
+        for (int k = 0; k < 32; k++) sum += s_off[(size_t)k * tiles + t];
+        blockcount[(size_t)blockIdx.x * tiles + t] = sum;
+        if (sum) atomicAdd(&tile_total[t], sum);
+      }
     __syncthreads();
-    if (tid == 0) {  // grid-wide barrier
-      __threadfence();
-      atomicAdd(grid_bar, 1u);
+    if (tid == 0) {  // grid-wide barrier over the counting blocks (the plan block only waits)
+      if (!plan_block) {
+        __threadfence();
+        atomicAdd(grid_bar, 1u);
+      }
       uint32_t spins = 0;
-      while (ld_volatile(grid_bar) < gridDim.x)
+      while (ld_volatile(grid_bar) < nblocks)
         if (++spins > SPIN_LIMIT) { atomicExch(&hdr->error, 3u); break; }
       __threadfence();
     }
@@ -357,11 +483,12 @@ bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __re
   const int ta = 2 * tid, tb = 2 * tid + 1;
   const uint32_t ca = ta < tiles ? __ldcg(tile_total + ta) : 0u, cb = tb < tiles ? __ldcg(tile_total + tb) : 0u;
   uint32_t pa = 0, pb = 0;  // pairs of the earlier blocks
-  for (unsigned b0 = 0; b0 < blockIdx.x; b0 += 16) {  // 32 independent loads in flight per round trip
+  const unsigned earlier = plan_block ? 0u : blockIdx.x;
+  for (unsigned b0 = 0; b0 < earlier; b0 += 16) {  // 32 independent loads in flight per round trip
     uint32_t va[16], vb[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) {
-      const bool in = b0 + k < blockIdx.x;
+      const bool in = b0 + k < earlier;
       va[k] = (in && ta < tiles) ? __ldcg(blockcount + (size_t)(b0 + k) * tiles + ta) : 0u;
       vb[k] = (in && tb < tiles) ? __ldcg(blockcount + (size_t)(b0 + k) * tiles + tb) : 0u;
     }
@@ -380,6 +507,15 @@ bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __re
 #pragma unroll
   for (int k = 0; k < 32; k++) { const uint32_t v = s_wsum[k]; if (k < w) wpre += v; total += v; }
   const uint32_t sa = wpre + incl - (ca + cb), sb = sa + ca;
+  if (plan_block) {  // the ranges block 0 publishes, kept in shared memory (the count area is free here), then the plans
+    const uint32_t lim = (unsigned long long)total > cap ? (uint32_t)cap : total;
+    uint2* const s_range = reinterpret_cast<uint2*>(s_raw);  // [tiles] <= 64 * tiles bytes
+    if (ta < tiles) s_range[ta] = ca ? make_uint2(min(sa, lim), min(sa + ca, lim)) : make_uint2(0u, 0u);
+    if (tb < tiles) s_range[tb] = cb ? make_uint2(min(sb, lim), min(sb + cb, lim)) : make_uint2(0u, 0u);
+    __syncthreads();
+    plan_body(tiles, s_range, seg_off, items, max_items, fitems, max_fitems, hdr);
+    return;
+  }
   if (ta < tiles) s_base[ta] = sa + pa;
   if (tb < tiles) s_base[tb] = sb + pb;
   if (blockIdx.x == 0) {
@@ -518,112 +654,6 @@ __global__ void tile_ranges_kernel(const uint32_t* __restrict__ tkey_sorted, con
   }
 }
 
-// Work plans of the two blend kernels.  One CTA.
-//  * backward: every tile list is cut into segments of GS_SEG entries; seg_off = exclusive prefix of the segment counts over
-//    tiles (seg_off[tiles] = number of items), items[] = (tile, segment);
-//  * forward: every non-empty tile list is cut into chunks of GS_FWD_CHUNK entries; fitems[] = (tile, chunk, index of the
-//    successor item, index of the predecessor item), ordered by the number of chunks that REMAIN in the tile's chain
-//    (this one included), longest first -- "longest remaining path first": the deep tiles, whose chains are the critical path
-//    of avatar frames, start at once, every last chunk comes at the end, and an item's predecessor (one more remaining)
-//    always has a smaller index: CTAs are dispatched in index order, which makes the hand-off wait of blend_fwd_kernel
-//    deadlock-free.  With nch(t) = chunks of tile t, pos(t) = rank of t in descending nch order (counting sort),
-//    ge[k] = #tiles with nch > k and base = exclusive prefix of ge, item (t, c) with r = nch - c remaining sits at
-//    n_fitems - base[r] + pos(t).  The empty tiles follow as one item each (their pixels still get the background).
-__device__ __forceinline__ uint32_t block_scan_incl_1024(uint32_t v, uint32_t* s_w, uint32_t* total) {
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  uint32_t incl = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-    if (lane >= o) incl += t;
-  }
-  __syncthreads();  // s_w may still be read from the previous scan
-  if (lane == 31) s_w[w] = incl;
-  __syncthreads();
-  uint32_t wv = s_w[lane], wincl = wv;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t t = __shfl_up_sync(0xFFFFFFFFu, wincl, o);
-    if (lane >= o) wincl += t;
-  }
-  *total = __shfl_sync(0xFFFFFFFFu, wincl, 31);
-  return incl + __shfl_sync(0xFFFFFFFFu, wincl - wv, w);
-}
-
-__global__ void __launch_bounds__(1024)
-plan_kernel(int tiles, const uint2* __restrict__ ranges, uint32_t* __restrict__ seg_off, uint2* __restrict__ items,
-            uint32_t max_items, uint4* __restrict__ fitems, uint32_t max_fitems, GsHeader* __restrict__ hdr) {
-  GS_PDL_PROLOGUE();
-  __shared__ uint32_t s_w[32];
-  __shared__ uint32_t s_hist[GS_FWD_NCH_BINS];  // tiles per chunk count -> cursor of the counting sort
-  __shared__ uint32_t s_base[GS_FWD_NCH_BINS];  // base[r] = sum over k < r of ge[k]
-  __shared__ uint32_t s_total, s_nonempty;
-  const int tid = threadIdx.x;
-  for (int k = tid; k < GS_FWD_NCH_BINS; k += 1024) s_hist[k] = 0;
-  __syncthreads();
-  uint32_t carry = 0;
-  for (int t0 = 0; t0 < tiles; t0 += 1024) {
-    const int t = t0 + tid;
-    uint32_t nseg = 0;
-    if (t < tiles) {
-      const uint2 r = ranges[t];
-      const uint32_t len = r.y - r.x;
-      nseg = (len + GS_SEG - 1) / GS_SEG;
-      atomicAdd(&s_hist[min((len + GS_FWD_CHUNK - 1) / GS_FWD_CHUNK, (uint32_t)GS_FWD_NCH_BINS - 1)], 1u);
-    }
-    uint32_t total;
-    const uint32_t off = carry + block_scan_incl_1024(nseg, s_w, &total) - nseg;
-    if (t < tiles) {
-      seg_off[t] = off;
-      for (uint32_t k = 0; k < nseg; k++)
-        if (off + k < max_items) items[off + k] = make_uint2((uint32_t)t, k);
-    }
-    carry += total;
-  }
-  if (tid == 0) seg_off[tiles] = carry < max_items ? carry : max_items;
-  __syncthreads();
-  // ge[k] = #tiles with chunk count > k = tiles - inclusive prefix of hist; base = exclusive prefix of ge.
-  // Two elements per thread (GS_FWD_NCH_BINS = 2 * 1024).
-  static_assert(GS_FWD_NCH_BINS == 2048, "two bins per thread");
-  {
-    const uint32_t h0 = s_hist[2 * tid], h1 = s_hist[2 * tid + 1];
-    uint32_t total;
-    const uint32_t incl = block_scan_incl_1024(h0 + h1, s_w, &total);
-    const uint32_t ge0 = (uint32_t)tiles - (incl - h1), ge1 = (uint32_t)tiles - incl;
-    uint32_t total2;
-    const uint32_t incl2 = block_scan_incl_1024(ge0 + ge1, s_w, &total2);
-    __syncthreads();
-    s_hist[2 * tid] = ge0; s_hist[2 * tid + 1] = ge1;                          // cursor: tiles with a larger chunk count come first
-    s_base[2 * tid] = incl2 - ge0 - ge1; s_base[2 * tid + 1] = incl2 - ge1;
-    if (tid == 0) {
-      s_total = total2;                                                        // items of the non-empty tiles
-      hdr->n_fitems = total2 < max_fitems ? total2 : max_fitems;
-      s_nonempty = ge0;                                                        // ge[0]
-      hdr->n_empty_tiles = h0;                                                 // hist[0]
-    }
-  }
-  __syncthreads();
-  const uint32_t n_items = s_total, n_nonempty = s_nonempty;
-  for (int t = tid; t < tiles; t += 1024) {
-    const uint2 r = ranges[t];
-    const uint32_t len = r.y - r.x;
-    const uint32_t nch = min((len + GS_FWD_CHUNK - 1) / GS_FWD_CHUNK, (uint32_t)GS_FWD_NCH_BINS - 1);
-    const uint32_t pos = atomicAdd(&s_hist[nch], 1u);
-    if (nch == 0) {  // empty tile: one item behind everything else
-      const uint32_t fi = n_items + (pos - n_nonempty);
-      if (fi < max_fitems) fitems[fi] = make_uint4((uint32_t)t, 0u, 0xFFFFFFFFu, 0xFFFFFFFFu);
-      continue;
-    }
-    for (uint32_t c = 0; c < nch; c++) {
-      const uint32_t rem = nch - c;  // chunks remaining in this tile's chain, this one included
-      const uint32_t fi = n_items - s_base[rem] + pos;
-      if (fi < max_fitems)
-        fitems[fi] = make_uint4((uint32_t)t, c, rem > 1 ? n_items - s_base[rem - 1] + pos : 0xFFFFFFFFu,
-                                c > 0 ? n_items - s_base[rem + 1] + pos : 0xFFFFFFFFu);
-    }
-  }
-}
-
 uint32_t higher_msb(uint32_t n) {  // rasterizer_impl.cu:35-50
   uint32_t msb = sizeof(n) * 4, step = msb;
   while (step > 1) {
@@ -672,10 +702,11 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
       gs_launch(bin_count_kernel, dim3(blocks_c), dim3(GS_BIN_THREADS), smem_c, st, P, (const uint32_t*)s.dval[0],
                 (const uint32_t*)s.dval[1], (const uint32_t*)s.hist, (const uint32_t*)g.tiles_touched, (const uint32_t*)g.rect,
                 gx, tiles, blockcount, s.tile_total);
-    gs_launch(fused ? bin_place_kernel<true> : bin_place_kernel<false>, dim3(blocks_c), dim3(GS_BIN_THREADS), smem_p, st, P,
-              (const uint32_t*)s.dval[0], (const uint32_t*)s.dval[1], (const uint32_t*)s.hist, (const uint32_t*)g.tiles_touched,
+    gs_launch(fused ? bin_place_kernel<true> : bin_place_kernel<false>, dim3(blocks_c + (fused ? 1 : 0)), dim3(GS_BIN_THREADS), smem_p,
+              st, P, (const uint32_t*)s.dval[0], (const uint32_t*)s.dval[1], (const uint32_t*)s.hist, (const uint32_t*)g.tiles_touched,
               (const uint32_t*)g.rect, gx, tiles, blockcount, s.tile_total, (unsigned long long)cap, list, im.ranges, g.hdr,
-              s.counters + 16);
+              s.counters + 16, im.seg_off, l.items, (uint32_t)l.max_items, (uint4*)l.fitems, (uint32_t)l.max_fitems);
+    if (fused) return gs_check(cudaGetLastError());  // the plans came from the placement grid's last block
   } else {
     // 2. chained scan + pair emission in depth order
     int bits = (int)higher_msb((uint32_t)tiles);

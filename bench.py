@@ -979,7 +979,7 @@ def ours_main(args):
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     blocks_c = (P + 1023) // 1024
     if tiles <= 2048:  # direct placement (gs_sort.cu): count+place fused into one grid up to 120 blocks, else two kernels
-        binning = 4 + (1 if blocks_c <= 120 else 2) + 1            # depth passes, placement, plan
+        binning = 4 + (1 if blocks_c <= 120 else 3)                # depth passes, placement (its last block plans) | count, place, plan
     else:
         tile_passes = (max(tiles.bit_length(), 1) + 7) // 8
         binning = 4 + 1 + tile_passes + 1 + 1                       # depth passes, emit, tile passes, ranges, plan
