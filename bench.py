@@ -317,6 +317,8 @@ def render_sequence(hp, args, rank, world, dev, GraphedStep, eager, n_frames=64)
     copy_stream = torch.cuda.Stream(dev)
     main = torch.cuda.current_stream(dev)
     done = [None, None]
+    rendered = [torch.cuda.Event(), torch.cuda.Event()]
+    copied = [torch.cuda.Event(), torch.cuda.Event()]
     checksum = 0.0
 
     def run(timed):
@@ -327,12 +329,12 @@ def render_sequence(hp, args, rank, world, dev, GraphedStep, eager, n_frames=64)
                 main.wait_event(done[slot])          # this slot's previous image has left the device
             statics[slot]["small"].copy_(smalls[i], non_blocking=True)
             img = fns[slot]()
-            ev = torch.cuda.Event()
+            ev = rendered[slot]
             ev.record(main)
             with torch.cuda.stream(copy_stream):
                 copy_stream.wait_event(ev)
                 pins[slot].copy_(img, non_blocking=True)
-                d = torch.cuda.Event()
+                d = copied[slot]
                 d.record(copy_stream)
             done[slot] = d
             if i and done[slot ^ 1] is not None:
@@ -687,10 +689,19 @@ def ours_main(args):
     # target image, from pinned host memory) runs on a copy stream while step k computes, and step k+1 waits for it.
     e2e = {"k": 0, "ready": [None, None], "read": [None, None]}
     copy_stream = torch.cuda.Stream(dev)
+    loss_pins = [torch.empty(1).pin_memory(), torch.empty(1).pin_memory()]
     if not eager:
         f_static2 = hp.static_frame(frames[rank])
-        g_train2 = GraphedStep(lambda: step_with_allreduce(f_static2))
-        e2e_frames, e2e_graphs = [f_static, f_static2], [g_train, g_train2]
+        e2e_frames = [f_static, f_static2]
+
+        def e2e_graph_fn(slot):
+            # the D2H copy of the loss is a node of the step's graph (pinned destination): no separate stream operation per step
+            loss = step_with_allreduce(e2e_frames[slot])
+            loss_pins[slot].copy_(loss.detach().reshape(1), non_blocking=True)
+            return loss
+        e2e_graphs = [GraphedStep(lambda: e2e_graph_fn(0)), GraphedStep(lambda: e2e_graph_fn(1))]
+
+        ready_evs = [torch.cuda.Event(), torch.cuda.Event()]
 
         def prefetch(slot):
             # overwrite the slot only after its previous reader (the graph of step k-1) has finished -- NOT after the step
@@ -699,12 +710,13 @@ def ours_main(args):
                 copy_stream.wait_event(e2e["read"][slot])
             with torch.cuda.stream(copy_stream):
                 hp.load_static(e2e_frames[slot], f_pin)
-                ev = torch.cuda.Event()
+                ev = ready_evs[slot]
                 ev.record(copy_stream)
             e2e["ready"][slot] = ev
 
-    loss_pins = [torch.empty(1).pin_memory(), torch.empty(1).pin_memory()]
     e2e.update(loss_ev=[None, None], last_loss=None)
+
+    e2e_evs = [torch.cuda.Event(), torch.cuda.Event()]
 
     def train_e2e():
         """One end-to-end step.  Software-pipelined by one step, like a training loop that logs the previous iteration's
@@ -720,12 +732,10 @@ def ours_main(args):
         if e2e["ready"][slot] is None:
             prefetch(slot)  # very first step: nothing was prefetched yet
         main.wait_event(e2e["ready"][slot])
-        loss = e2e_graphs[slot].replay()
-        e2e["read"][slot] = torch.cuda.Event()
-        e2e["read"][slot].record(main)
-        loss_pins[slot].copy_(loss.detach().reshape(1), non_blocking=True)
-        ev = torch.cuda.Event()
+        e2e_graphs[slot].replay()                      # step + D2H of its loss into loss_pins[slot]
+        ev = e2e_evs[slot]                             # one event: the slot's inputs have been read AND its loss is on the host
         ev.record(main)
+        e2e["read"][slot] = ev
         e2e["loss_ev"][slot] = ev
         prefetch(slot ^ 1)  # inputs of the NEXT step: the copy runs while this step's kernels do
         if e2e["loss_ev"][slot ^ 1] is not None:
@@ -996,8 +1006,8 @@ def ours_main(args):
             "e2e": {"value": world * 1e3 / ms_train_e2e, "unit": "iter/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": ms_train_e2e,
                     "pipeline": "per step: H2D of the NEXT step's pose+camera+target from pinned memory on a copy stream (double-buffered "
-                                "static inputs), graph replay, D2H of the loss; the host blocks on the PREVIOUS step's loss (one-step "
-                                "software pipeline, every loss is read)"},
+                                "static inputs), graph replay whose last node is the D2H copy of the loss into pinned memory; the host "
+                                "blocks on the PREVIOUS step's loss (one-step software pipeline, every loss is read)"},
             "render_fps": world * 1e3 / ms_render,
             "render_e2e": {"value": world * 1e3 / ms_render_e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d - 3 * H * W * 4,
                            "d2h_bytes_per_step": 3 * H * W * 4},
