@@ -161,6 +161,16 @@ __global__ void __launch_bounds__(PE_J * 32) pose_encoder_bwd_kernel(PoseEncoder
     }
   }
   // ---- backward: leaves first ----
+  // the transposed weight columns this lane needs (lane k < 19: Wb[j][i][k], Wa[j][i][k]) go to registers up front: every
+  // load is in flight at once instead of two L2 round trips per tree level on the serial path
+  float wbT[PE_D], waT[PE_F];
+  {
+    const int kk = lane < PE_F ? lane : 0;
+#pragma unroll
+    for (int i = 0; i < PE_D; i++) wbT[i] = __ldg(a.Wb + ((size_t)j * PE_D + i) * PE_F + kk);
+#pragma unroll
+    for (int i = 0; i < PE_F; i++) waT[i] = __ldg(a.Wa + ((size_t)j * PE_F + i) * PE_F + kk);
+  }
   for (int level = max_depth; level >= 0; level--) {
     if (depth == level) {
       float go = 0.f;  // lane i < 6: dL/dout[j][i], own upstream + what the children left for their parent feature
@@ -181,7 +191,7 @@ __global__ void __launch_bounds__(PE_J * 32) pose_encoder_bwd_kernel(PoseEncoder
 #pragma unroll
         for (int i = 0; i < PE_D; i++) {
           const float g = __shfl_sync(0xFFFFFFFFu, go, i);
-          if (lane < PE_F) dh = fmaf(__ldg(a.Wb + ((size_t)j * PE_D + i) * PE_F + lane), g, dh);
+          if (lane < PE_F) dh = fmaf(wbT[i], g, dh);
         }
         if (lane < PE_F) {
           dz = s_h[j][lane] > 0.f ? dh : 0.f;
@@ -192,7 +202,7 @@ __global__ void __launch_bounds__(PE_J * 32) pose_encoder_bwd_kernel(PoseEncoder
 #pragma unroll
       for (int i = 0; i < PE_F; i++) {
         const float g = __shfl_sync(0xFFFFFFFFu, dz, i);
-        if (lane < PE_F) din = fmaf(__ldg(a.Wa + ((size_t)j * PE_F + i) * PE_F + lane), g, din);
+        if (lane < PE_F) din = fmaf(waT[i], g, din);
       }
       for (int e0 = 0; e0 < PE_F * PE_F; e0 += 32) {  // dWa[j][i][k] = dz_i * in_k (all lanes take part in the shuffle)
         const int e = e0 + lane, ec = e < PE_F * PE_F ? e : 0, i = ec / PE_F, k = ec - i * PE_F;

@@ -67,10 +67,15 @@ __global__ void nr_prep_kernel(NonRigidArgs a, NrWs w, int npad) {
     const float v = n < a.n_out ? a.W3[(size_t)n * NR_H + k] : 0.f;
     split_bf16(v, w.w3_hi[core_idx(n, k, npad)], w.w3_lo[core_idx(n, k, npad)]);
   }
-  for (int n = tid; n < NR_H; n += nth) {
-    float acc = a.b0[n];
-    for (int c = 0; c < a.n_cond; c++) acc = fmaf(a.W0[(size_t)n * in0 + NR_F + c], a.cond[c], acc);
-    w.bias0[n] = acc;
+  // bias0[n] = b0[n] + W0[n, F:] . cond -- one WARP per output (coalesced row reads, shuffle reduction); one thread per output
+  // walked 144 strided loads in a row and was most of this kernel's 15 us
+  const int lane = threadIdx.x & 31;
+  for (int n = tid >> 5; n < NR_H; n += nth >> 5) {
+    float acc = 0.f;
+    for (int c = lane; c < a.n_cond; c += 32) acc = fmaf(a.W0[(size_t)n * in0 + NR_F + c], a.cond[c], acc);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+    if (lane == 0) w.bias0[n] = a.b0[n] + acc;
   }
 }
 
@@ -785,12 +790,16 @@ __global__ void nr_bwd_finish_kernel(NonRigidBackwardArgs b) {
     const int n = e / a.n_cond, c = e % a.n_cond;
     b.dL_dW0[(size_t)n * in0 + NR_F + c] = b.dL_db0[n] * a.cond[c];
   }
-  if (b.dL_dcond && blockIdx.x == 0)
-    for (int c = threadIdx.x; c < a.n_cond; c += blockDim.x) {
+  if (b.dL_dcond) {  // dcond[c] = sum_n W0[n][F + c] db0[n]: a warp per output, lanes over n
+    const int lane = threadIdx.x & 31, gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+    for (int c = gw; c < a.n_cond; c += nw) {
       float acc = 0.f;
-      for (int n = 0; n < NR_H; n++) acc = fmaf(a.W0[(size_t)n * in0 + NR_F + c], b.dL_db0[n], acc);
-      b.dL_dcond[c] = acc;
+      for (int n = lane; n < NR_H; n += 32) acc = fmaf(a.W0[(size_t)n * in0 + NR_F + c], b.dL_db0[n], acc);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+      if (lane == 0) b.dL_dcond[c] = acc;
     }
+  }
 }
 
 }  // namespace
