@@ -53,7 +53,11 @@ class FlatGaussianParams:
     the gradient-slab layout) and re-binds the attributes as views of it, so one kernel can update all of them."""
 
     def __init__(self, gaussians):
-        tensors = [getattr(gaussians, _ATTR[k]) for k in SLAB_ORDER]
+        self.gaussians = gaussians
+        self._bind([getattr(gaussians, _ATTR[k]) for k in SLAB_ORDER])
+
+    def _bind(self, tensors):
+        gaussians = self.gaussians
         dev = tensors[0].device
         if not tensors[0].is_cuda:
             raise _gs.GsError("FlatGaussianParams needs CUDA tensors (there is no CPU path)")
@@ -123,6 +127,33 @@ class FusedAdam:
         a.exp_avg, a.exp_avg_sq, a.state = self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.state.data_ptr()
         with torch.cuda.device(dev):
             _gs._check(L.adam_step(ctypes.byref(a), torch.cuda.current_stream(dev).cuda_stream), "adam_step")
+
+    @torch.no_grad()
+    def resize(self, keep_mask=None, new_tensors=None):
+        """The optimiser surgery of densify-and-prune with the reference's semantics (scene/gaussian_model.py: `_prune_optimizer`
+        :251-270 keeps the rows of `keep_mask` in every parameter AND in exp_avg / exp_avg_sq; `cat_tensors_to_optimizer` :290-312
+        appends `new_tensors` = {"xyz": [n,3], "f_dc": [n,1,3], "f_rest": [n,15,3], "opacity": [n,1], "scaling": [n,3],
+        "rotation": [n,4]} with ZERO moments); the step counter and the learning rates are kept.  Re-homes the parameters in a new
+        slab and re-binds the GaussianModel attributes; returns {name: new parameter tensor} like the reference's helpers."""
+        flat = self.flat
+        dev = flat.slab.device
+        params, m1, m2, off = {}, {}, {}, 0
+        for k, n in zip(SLAB_ORDER, flat.sizes):
+            shape = flat.views[k].shape
+            parts = [flat.views[k].detach(), self.exp_avg[off:off + n].view(shape), self.exp_avg_sq[off:off + n].view(shape)]
+            if keep_mask is not None:
+                parts = [t[keep_mask] for t in parts]
+            if new_tensors is not None:
+                ext = new_tensors[k].detach().to(dev, torch.float32)
+                parts = [torch.cat([parts[0], ext]), torch.cat([parts[1], torch.zeros_like(ext)]), torch.cat([parts[2], torch.zeros_like(ext)])]
+            params[k], m1[k], m2[k] = parts
+            off += n
+        flat._bind([params[k] for k in SLAB_ORDER])
+        self.exp_avg = torch.cat([m1[k].reshape(-1) for k in SLAB_ORDER])
+        self.exp_avg_sq = torch.cat([m2[k].reshape(-1) for k in SLAB_ORDER])
+        for grp in self.param_groups:
+            grp["params"] = [flat.views[grp["name"]]]
+        return dict(flat.views)
 
     def zero_grad(self, set_to_none=True):
         for v in self.flat.views.values():

@@ -19,6 +19,8 @@
 // of 9 per (pixel, entry).
 #include <stdlib.h>
 
+#include <cstdlib>
+
 #include "gs_common.cuh"
 
 namespace {
@@ -147,7 +149,7 @@ blend_fwd_work(FwdSmem& sm, const uint32_t work, const uint32_t n_items,
                uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                const uint32_t* __restrict__ seg_off, float4* __restrict__ ckpt, const uint4* __restrict__ fitems,
                GsHeader* __restrict__ hdr, int grid_x, float* __restrict__ out_opacity,
-               float* __restrict__ ckpt_op, uint32_t* __restrict__ rowmask, uint32_t* __restrict__ hand) {
+               float* __restrict__ ckpt_op, uint32_t* __restrict__ rowmask, uint32_t* __restrict__ hand, int poll_ns) {
   if (work >= n_items * 8) {
     // ---- empty tiles: one work unit each, thread = pixel (forward.cu:363-372 with T = 1, C = 0, no contributor) ----
     const uint32_t e = work - n_items * 8;
@@ -350,7 +352,7 @@ blend_fwd_work(FwdSmem& sm, const uint32_t work, const uint32_t n_items,
             v1 = make_uint2(GS_HAND_VALID, 0u);
             break;
           }
-          __nanosleep(32);
+          if (poll_ns > 0) __nanosleep(poll_ns);
         }
         decode(v0, v1);
         have_state = true;
@@ -436,7 +438,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                  const uint32_t* __restrict__ seg_off, float4* __restrict__ ckpt, const uint4* __restrict__ fitems,
                  GsHeader* __restrict__ hdr, int grid_x, float* __restrict__ out_opacity,
-                 float* __restrict__ ckpt_op, uint32_t* __restrict__ rowmask, uint32_t* __restrict__ hand) {
+                 float* __restrict__ ckpt_op, uint32_t* __restrict__ rowmask, uint32_t* __restrict__ hand, int poll_ns) {
   GS_PDL_PROLOGUE();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FwdSmem& sm = *reinterpret_cast<FwdSmem*>(smem_raw);
@@ -449,7 +451,7 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
     const uint32_t work = sm.ticket;
     if (work >= n_work) break;
     blend_fwd_work<OP, POLY>(sm, work, n_items, ranges, list, W, H, rec, bg, final_T, n_contrib, out_color, seg_off, ckpt, fitems,
-                             hdr, grid_x, out_opacity, ckpt_op, rowmask, hand);
+                             hdr, grid_x, out_opacity, ckpt_op, rowmask, hand, poll_ns);
   }
 }
 
@@ -697,11 +699,12 @@ int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& 
     if (!sm_count[dev]) cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
     sms = sm_count[dev] ? sm_count[dev] : sms;
   }
+  static const int poll_ns = [] { const char* e = getenv("GS_FWD_POLL_NS"); return e ? atoi(e) : 32; }();  // pause between hand-off polls
   const size_t work_max = l.max_fitems * 8;  // upper bound of the frame's work units
   const unsigned grid = (unsigned)(work_max < (size_t)sms * GS_FWD_CTAS ? work_max : (size_t)sms * GS_FWD_CTAS);
   gs_launch(kern, dim3(grid), dim3(kFwdWarps * 32), smem, st, im.ranges, l.point_list, a.width,
             a.height, g.rec, a.background, im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt, (const uint4*)l.fitems,
-            g.hdr, gx, a.out_opacity, l.ckpt_op, l.rowmask, s.hand);
+            g.hdr, gx, a.out_opacity, l.ckpt_op, l.rowmask, s.hand, poll_ns);
   return gs_check(cudaGetLastError());
 }
 

@@ -117,3 +117,51 @@ def test_densification_stats(built_lib):
     assert torch.equal(mr_d.cpu(), mr_ref) and torch.equal(den_d.cpu(), den_ref)
     assert float((acc_d.cpu() - acc_ref).abs().max()) <= 1e-7
     assert torch.equal(acc_d.cpu()[~vis], acc[~vis])
+
+
+def test_fused_adam_resize_keeps_moments_like_the_reference(built_lib):
+    """Densify-and-prune surgery (scene/gaussian_model.py:251-312): pruning keeps the surviving rows of every parameter and of
+    both Adam moments, densification appends rows with zero moments, the step count goes on.  FusedAdam.resize against
+    torch.optim.Adam on the CPU with the reference's state surgery done by hand, stepped before and after."""
+    from avatar_pose.optim import FlatGaussianParams, FusedAdam, SLAB_ORDER
+    dev = torch.device("cuda:0")
+    P, n_new = 3000, 700
+    g, gm = _model(P, dev, seed=4)
+    flat = FlatGaussianParams(gm)
+    opt = FusedAdam(flat, LRS, eps=1e-15)
+    cpu = {k: torch.from_numpy(g[KEY[k]]).clone().requires_grad_(True) for k in ATTR}
+    order = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
+    ref = torch.optim.Adam([{"params": [cpu[k]], "lr": LRS[k], "name": k} for k in order], lr=0.0, eps=1e-15)
+    gen = torch.Generator().manual_seed(9)
+
+    def steps(n):
+        for _ in range(n):
+            for k in ATTR:
+                gr = torch.randn(cpu[k].shape, generator=gen) * 1e-3
+                cpu[k].grad = gr.clone()
+                getattr(gm, ATTR[k]).grad = gr.to(dev)
+            opt.step()
+            ref.step()
+            opt.zero_grad()
+
+    steps(6)
+    keep = torch.rand(P, generator=gen) > 0.25
+    new = {k: torch.randn(n_new, *cpu[k].shape[1:], generator=gen) * 0.1 for k in ATTR}
+    # the reference's surgery on torch.optim.Adam (gaussian_model.py:251-270 then :290-312)
+    for grp in ref.param_groups:
+        k = grp["name"]
+        st = ref.state.pop(grp["params"][0])
+        st["exp_avg"] = torch.cat([st["exp_avg"][keep], torch.zeros_like(new[k])])
+        st["exp_avg_sq"] = torch.cat([st["exp_avg_sq"][keep], torch.zeros_like(new[k])])
+        cpu[k] = torch.cat([grp["params"][0].detach()[keep], new[k]]).requires_grad_(True)
+        grp["params"][0] = cpu[k]
+        ref.state[cpu[k]] = st
+    out = opt.resize(keep.to(dev), {k: v.to(dev) for k, v in new.items()})
+    P2 = int(keep.sum()) + n_new
+    assert gm._xyz.shape == (P2, 3) and out["xyz"] is gm._xyz and flat.slab.numel() == 59 * P2 and opt.step_count() == 6
+    steps(5)
+    assert opt.step_count() == 11
+    for k in SLAB_ORDER:
+        a, b = getattr(gm, ATTR[k]).detach().cpu(), cpu[k].detach()
+        assert a.shape == b.shape
+        assert float((a - b).abs().max() / b.abs().max()) <= 2e-6, k
