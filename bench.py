@@ -347,12 +347,15 @@ def render_sequence(hp, args, rank, world, dev, GraphedStep, eager, n_frames=64)
 
     run(False)
     torch.cuda.synchronize(dev)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(main)
-    run(True)
-    e1.record(main)
-    torch.cuda.synchronize(dev)
-    return len(mine), e0.elapsed_time(e1), checksum
+    best = float("inf")
+    for _ in range(5):  # a shard is 8 frames (~1.5 ms) at N = 8: one host hiccup would decide a single pass; best of five passes
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(main)
+        run(True)
+        e1.record(main)
+        torch.cuda.synchronize(dev)
+        best = min(best, e0.elapsed_time(e1))
+    return len(mine), best, checksum
 
 
 def stress_step(dev, GraphedStep, eager, flush, n_steps, P=1_000_000, W=1920, H=1080):
@@ -903,7 +906,7 @@ def ours_main(args):
                       "pair_capacity_overflow": bool(over),
                       "h2d_bytes_per_frame": 419 * 4, "d2h_bytes_per_frame": 3 * H * W * 4,
                       "what": "render.py's loop: 64-frame slerp animation + ring camera, frame f on rank f mod N, per frame H2D pose+camera -> "
-                              "posing + rasterizer forward -> D2H image (pinned, double-buffered); no collective"}
+                              "posing + rasterizer forward -> D2H image (pinned, double-buffered); no collective; best of five passes per rank, max over ranks"}
     except Exception as ex:  # informational leg
         if world > 1:
             raise
