@@ -80,32 +80,23 @@ def _fill_fwd(xyz, rotation, scaling, opacity, f_dc, f_rest, weights, bones, cam
 
 
 class _FusedPose(torch.autograd.Function):
+    """One forward kernel + one backward kernel, through the C++ extension (csrc/ext/ext.cpp: pose_forward / pose_backward fill
+    PoseArgs / PoseBackwardArgs and call the C ABI; the ctypes route cost ~25 us of Python per call)."""
+
     @staticmethod
     def forward(ctx, xyz, rotation, scaling, opacity, f_dc, f_rest, weights, bones, cam, sh_degree, mod, cano,
                 want_aux, view_noise=None):
-        L = _lib()
-        dev = xyz.device
         if not xyz.is_cuda:
             raise _gs.GsError("fused_pose needs CUDA tensors (there is no CPU path)")
         c = lambda t: t.detach().contiguous()
-        xyz_, rot_, sc_, op_, dc_, rest_, w_, b_, cam_ = map(c, (xyz, rotation, scaling, opacity, f_dc, f_rest, weights, bones, cam))
-        P = xyz_.shape[0]
-        with torch.cuda.device(dev):
-            f32 = dict(dtype=torch.float32, device=dev)
-            out = torch.empty(P, 13, **f32)  # one allocation: means 3 | cov 6 | colour 3 | opacity 1 (SoA slabs)
-            flat = out.view(-1)
-            means, cov = flat[:3 * P].view(P, 3), flat[3 * P:9 * P].view(P, 6)
-            colors, opac = flat[9 * P:12 * P].view(P, 3), flat[12 * P:].view(P, 1)
-            T_fwd = torch.empty(P, 4, 4, **f32) if want_aux else None
-            Rbar = torch.empty(P, 3, 3, **f32) if want_aux else None
-            vn_ = None if view_noise is None else view_noise.detach().contiguous().float().reshape(-1)
-            a = _fill_fwd(xyz_, rot_, sc_, op_, dc_, rest_, w_, b_, cam_, sh_degree, mod, cano, vn_)
-            a.means3D, a.cov3D, a.colors, a.opacity_out = means.data_ptr(), cov.data_ptr(), colors.data_ptr(), opac.data_ptr()
-            a.T_fwd = T_fwd.data_ptr() if want_aux else None
-            a.rotation_bar = Rbar.data_ptr() if want_aux else None
-            if P:
-                _gs._check(L.pose_forward(ctypes.byref(a), torch.cuda.current_stream(dev).cuda_stream), "pose_forward")
-        ctx.save_for_backward(xyz_, rot_, sc_, op_, dc_, rest_, w_, b_, cam_)
+        saved = tuple(map(c, (xyz, rotation, scaling, opacity, f_dc, f_rest, weights, bones, cam)))
+        P = saved[0].shape[0]
+        vn_ = None if view_noise is None else view_noise.detach().contiguous().float().reshape(-1)
+        out, T_fwd, Rbar = _gs._call(_gs._ext.pose_forward, *saved, int(sh_degree), float(mod), bool(cano), bool(want_aux), vn_)
+        flat = out.view(-1)  # one allocation: means 3 | cov 6 | colour 3 | opacity 1 (SoA slabs)
+        means, cov = flat[:3 * P].view(P, 3), flat[3 * P:9 * P].view(P, 6)
+        colors, opac = flat[9 * P:12 * P].view(P, 3), flat[12 * P:].view(P, 1)
+        ctx.save_for_backward(*saved)
         ctx.cfg = (int(sh_degree), float(mod), bool(cano))
         ctx.view_noise = vn_
         ctx.need_w = weights.requires_grad
@@ -117,44 +108,18 @@ class _FusedPose(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_means, g_cov, g_col, g_op, *unused):
-        L = _lib()
         xyz, rot, sc, op, dc, rest, w, b, cam = ctx.saved_tensors
         sh_degree, mod, cano = ctx.cfg
-        dev = xyz.device
         P = xyz.shape[0]
-        with torch.cuda.device(dev):
-            f32 = dict(dtype=torch.float32, device=dev)
-            z = lambda g, shape: (torch.zeros(shape, **f32) if g is None else g.contiguous())
-            g_means, g_cov, g_col, g_op = z(g_means, (P, 3)), z(g_cov, (P, 6)), z(g_col, (P, 3)), z(g_op, (P, 1))
-            nrest = rest.shape[1] if rest.numel() else 0
-            # one flat gradient slab (the buffer a data-parallel all-reduce runs over): xyz 3 | rot 4 | scale 3 |
-            # opacity 1 | dc 3 | rest 3*nrest
-            widths = [3, 4, 3, 1, 3, 3 * nrest]
-            total = P * sum(widths)
-            buf = _slab_buffer[0]
-            flat = buf[:total] if (buf is not None and buf.numel() >= total and buf.device == dev) else torch.empty(total, **f32)
-            parts, off = [], 0
-            for wd in widths:
-                parts.append(flat[off:off + P * wd])
-                off += P * wd
-            gxyz, grot, gsc, gop = parts[0].view(P, 3), parts[1].view(P, 4), parts[2].view(P, 3), parts[3].view(P, 1)
-            gdc, grest = parts[4].view(P, 1, 3), parts[5].view(P, nrest, 3)
-            gw = torch.empty(P, 24, **f32) if ctx.need_w else None
-            ba = PoseBackwardArgs()
-            ba.fwd = _fill_fwd(xyz, rot, sc, op, dc, rest, w, b, cam, sh_degree, mod, cano, ctx.view_noise)
-            ba.dL_dmeans3D, ba.dL_dcov3D, ba.dL_dcolors, ba.dL_dopacity = (g_means.data_ptr(), g_cov.data_ptr(),
-                                                                           g_col.data_ptr(), g_op.data_ptr())
-            ba.dL_dxyz, ba.dL_drotation, ba.dL_dscaling, ba.dL_dopacity_logit = (gxyz.data_ptr(), grot.data_ptr(),
-                                                                                 gsc.data_ptr(), gop.data_ptr())
-            ba.dL_dfeatures_dc = gdc.data_ptr()
-            ba.dL_dfeatures_rest = grest.data_ptr() if nrest else None
-            ba.dL_dweights = gw.data_ptr() if gw is not None else None
-            gb = torch.empty(24, 4, 4, **f32) if ctx.need_b else None
-            ba.dL_dbone_transforms = gb.data_ptr() if gb is not None else None
-            if P:
-                _gs._check(L.pose_backward(ctypes.byref(ba), torch.cuda.current_stream(dev).cuda_stream), "pose_backward")
+        nrest = rest.shape[1] if rest.numel() else 0
+        # one flat gradient slab (the buffer a data-parallel all-reduce runs over): xyz 3 | rot 4 | scale 3 | opacity 1 | dc 3 |
+        # rest 3*nrest, attribute-major; written into the registered slab buffer (set_grad_slab_buffer) when there is one
+        flat, gw, gb = _gs._call(_gs._ext.pose_backward, xyz, rot, sc, op, dc, rest, w, b, cam, sh_degree, mod, cano, ctx.view_noise,
+                                 g_means, g_cov, g_col, g_op, bool(ctx.need_w), bool(ctx.need_b), _slab_buffer[0])
         _last_slab[0] = flat
-        gop = gop.view(op.shape)
+        gxyz, grot, gsc = flat[:3 * P].view(P, 3), flat[3 * P:7 * P].view(P, 4), flat[7 * P:10 * P].view(P, 3)
+        gop, gdc = flat[10 * P:11 * P].view(op.shape), flat[11 * P:14 * P].view(P, 1, 3)
+        grest = flat[14 * P:].view(P, nrest, 3)
         return gxyz, grot, gsc, gop, gdc, grest, gw, (gb.view(b.shape) if gb is not None else None), None, None, None, None, None, None
 
 

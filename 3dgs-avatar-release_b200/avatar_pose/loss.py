@@ -27,37 +27,22 @@ def _lib():
 
 
 class _L1(torch.autograd.Function):
+    """Through the C++ extension (csrc/ext/ext.cpp: l1_forward / l1_backward call l1_loss_forward / l1_loss_backward of the C ABI)."""
+
     @staticmethod
     def forward(ctx, image, target):
         if not image.is_cuda or not target.is_cuda:
             raise _gs.GsError("l1_loss needs CUDA tensors (there is no CPU path)")
         if image.shape != target.shape:
             raise _gs.GsError("l1_loss: image and target shapes differ")
-        L = _lib()
-        dev = image.device
-        img, gt = image.detach().contiguous().float(), target.detach().contiguous().float()
-        with torch.cuda.device(dev):
-            ws = _ws.get(dev)
-            if ws is None:
-                ws = _ws[dev] = torch.zeros(L.l1_loss_workspace_bytes(), dtype=torch.uint8, device=dev)
-            loss = torch.empty((), dtype=torch.float32, device=dev)
-            unit = torch.empty_like(img)
-            _gs._check(L.l1_loss_forward(img.data_ptr(), gt.data_ptr(), img.numel(), loss.data_ptr(), unit.data_ptr(),
-                                         ws.data_ptr(), ws.numel(), torch.cuda.current_stream(dev).cuda_stream), "l1_loss_forward")
+        loss, unit = _gs._call(_gs._ext.l1_forward, image.detach().float(), target.detach().float())
         ctx.save_for_backward(unit)
         return loss
 
     @staticmethod
     def backward(ctx, g):
         (unit,) = ctx.saved_tensors
-        L = _lib()
-        dev = unit.device
-        g = g.detach().contiguous().float()
-        with torch.cuda.device(dev):
-            out = torch.empty_like(unit)
-            _gs._check(L.l1_loss_backward(unit.data_ptr(), g.data_ptr(), unit.numel(), out.data_ptr(),
-                                          torch.cuda.current_stream(dev).cuda_stream), "l1_loss_backward")
-        return out, None
+        return _gs._call(_gs._ext.l1_backward, unit, g.detach().float()), None
 
 
 def l1_loss(network_output, gt):

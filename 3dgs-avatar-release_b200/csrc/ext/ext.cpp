@@ -214,6 +214,117 @@ torch::Tensor mark_visible(const torch::Tensor& means3D_, const torch::Tensor& v
   return present;
 }
 
+// ---- posing (avatar_pose.fused_pose) and the L1 loss (avatar_pose.loss.l1_loss): the same thin glue for the other two ops of the
+// eager training step -- each ctypes call with its argument struct cost ~25 us of Python per call ----
+using OptT = c10::optional<torch::Tensor>;
+
+void fill_pose(PoseArgs& a, const torch::Tensor& xyz, const torch::Tensor& rot, const torch::Tensor& sc, const torch::Tensor& op,
+               const torch::Tensor& dc, const torch::Tensor& rest, const torch::Tensor& w, const torch::Tensor& bones, const torch::Tensor& cam,
+               int64_t sh_degree, double mod, bool cano, const torch::Tensor& vn) {
+  if (w.dim() != 2 || w.size(1) != 24 || bones.numel() != 24 * 16) throw std::runtime_error("weights must be [P,24] and bone_transforms [24,4,4]");
+  a.P = (int32_t)xyz.size(0); a.sh_degree = (int32_t)sh_degree; a.cano_view_dir = cano ? 1 : 0; a.scaling_modifier = (float)mod;
+  a.M = 1 + ((rest.defined() && rest.numel()) ? (int32_t)rest.size(1) : 0);
+  a.xyz = fptr(xyz, "xyz"); a.rotation = fptr(rot, "rotation"); a.scaling = fptr(sc, "scaling"); a.opacity = fptr(op, "opacity");
+  a.features_dc = fptr(dc, "features_dc"); a.features_rest = fptr(rest, "features_rest"); a.weights = fptr(w, "weights");
+  a.bone_transforms = fptr(bones, "bone_transforms"); a.camera_center = fptr(cam, "camera_center"); a.view_noise = fptr(vn, "view_noise");
+}
+
+// -> (out slab [P,13]: means 3 | cov 6 | colour 3 | opacity 1 as SoA slabs, T_fwd or undefined, rotation_bar or undefined)
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor>
+pose_forward_t(const torch::Tensor& xyz, const torch::Tensor& rot, const torch::Tensor& sc, const torch::Tensor& op, const torch::Tensor& dc,
+               const torch::Tensor& rest, const torch::Tensor& w, const torch::Tensor& bones, const torch::Tensor& cam, int64_t sh_degree,
+               double mod, bool cano, bool want_aux, const OptT& view_noise) {
+  TORCH_CHECK(xyz.is_cuda(), "fused_pose needs CUDA tensors (there is no CPU path)");
+  const c10::cuda::CUDAGuard guard(xyz.device());
+  const int64_t P = xyz.size(0);
+  auto f32 = xyz.options().dtype(torch::kFloat32);
+  auto out = torch::empty({P, 13}, f32);
+  torch::Tensor T_fwd, Rbar, vn;
+  if (want_aux) { T_fwd = torch::empty({P, 4, 4}, f32); Rbar = torch::empty({P, 3, 3}, f32); }
+  if (view_noise.has_value() && view_noise->defined()) vn = *view_noise;
+  if (P) {
+    PoseArgs a{};
+    fill_pose(a, xyz, rot, sc, op, dc, rest, w, bones, cam, sh_degree, mod, cano, vn);
+    float* o = out.data_ptr<float>();
+    a.means3D = o; a.cov3D = o + 3 * P; a.colors = o + 9 * P; a.opacity_out = o + 12 * P;
+    a.T_fwd = want_aux ? T_fwd.data_ptr<float>() : nullptr;
+    a.rotation_bar = want_aux ? Rbar.data_ptr<float>() : nullptr;
+    const int status = pose_forward(&a, at::cuda::getCurrentCUDAStream(xyz.device().index()).stream());
+    if (status != GS_OK) fail("pose_forward", status);
+  }
+  return {out, T_fwd, Rbar};
+}
+
+// -> (flat gradient slab, dL_dweights or undefined, dL_dbone_transforms or undefined); slab = xyz 3 | rot 4 | scale 3 | opacity 1 |
+// dc 3 | rest 3 * nrest per Gaussian, attribute-major; `slab_buffer` (optional) is used when it is large enough
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor>
+pose_backward_t(const torch::Tensor& xyz, const torch::Tensor& rot, const torch::Tensor& sc, const torch::Tensor& op, const torch::Tensor& dc,
+                const torch::Tensor& rest, const torch::Tensor& w, const torch::Tensor& bones, const torch::Tensor& cam, int64_t sh_degree,
+                double mod, bool cano, const OptT& view_noise, const OptT& g_means_, const OptT& g_cov_, const OptT& g_col_, const OptT& g_op_,
+                bool need_w, bool need_b, const OptT& slab_buffer) {
+  const c10::cuda::CUDAGuard guard(xyz.device());
+  const int64_t P = xyz.size(0);
+  auto f32 = xyz.options().dtype(torch::kFloat32);
+  auto grad_or_zero = [&](const OptT& g, int64_t width) {
+    if (g.has_value() && g->defined()) return contig(*g);
+    return torch::zeros({P, width}, f32);
+  };
+  auto g_means = grad_or_zero(g_means_, 3), g_cov = grad_or_zero(g_cov_, 6), g_col = grad_or_zero(g_col_, 3), g_op = grad_or_zero(g_op_, 1);
+  const int64_t nrest = (rest.defined() && rest.numel()) ? rest.size(1) : 0;
+  const int64_t total = P * (3 + 4 + 3 + 1 + 3 + 3 * nrest);
+  torch::Tensor flat;
+  if (slab_buffer.has_value() && slab_buffer->defined() && slab_buffer->numel() >= total && slab_buffer->device() == xyz.device())
+    flat = slab_buffer->narrow(0, 0, total);
+  else
+    flat = torch::empty({total}, f32);
+  torch::Tensor gw, gb, vn;
+  if (need_w) gw = torch::empty({P, 24}, f32);
+  if (need_b) gb = torch::empty({24, 4, 4}, f32);
+  if (view_noise.has_value() && view_noise->defined()) vn = *view_noise;
+  if (P) {
+    PoseBackwardArgs b{};
+    fill_pose(b.fwd, xyz, rot, sc, op, dc, rest, w, bones, cam, sh_degree, mod, cano, vn);
+    b.dL_dmeans3D = fptr(g_means, "dL_dmeans3D"); b.dL_dcov3D = fptr(g_cov, "dL_dcov3D"); b.dL_dcolors = fptr(g_col, "dL_dcolors");
+    b.dL_dopacity = fptr(g_op, "dL_dopacity");
+    float* o = flat.data_ptr<float>();
+    b.dL_dxyz = o; b.dL_drotation = o + 3 * P; b.dL_dscaling = o + 7 * P; b.dL_dopacity_logit = o + 10 * P; b.dL_dfeatures_dc = o + 11 * P;
+    b.dL_dfeatures_rest = nrest ? o + 14 * P : nullptr;
+    b.dL_dweights = need_w ? gw.data_ptr<float>() : nullptr;
+    b.dL_dbone_transforms = need_b ? gb.data_ptr<float>() : nullptr;
+    const int status = pose_backward(&b, at::cuda::getCurrentCUDAStream(xyz.device().index()).stream());
+    if (status != GS_OK) fail("pose_backward", status);
+  }
+  return {flat, gw, gb};
+}
+
+std::map<int, torch::Tensor> g_l1_ws;  // per device: partial sums + ticket of the fused L1 loss (zero on first use, self-resetting)
+
+std::tuple<torch::Tensor, torch::Tensor> l1_forward_t(const torch::Tensor& image, const torch::Tensor& target) {
+  TORCH_CHECK(image.is_cuda() && target.is_cuda(), "l1_loss needs CUDA tensors (there is no CPU path)");
+  if (image.sizes() != target.sizes()) throw std::runtime_error("l1_loss: image and target shapes differ");
+  const c10::cuda::CUDAGuard guard(image.device());
+  const int dev = image.device().index();
+  auto img = contig(image), gt = contig(target);
+  auto& ws = g_l1_ws[dev];
+  if (!ws.defined()) ws = torch::zeros({(int64_t)l1_loss_workspace_bytes()}, image.options().dtype(torch::kUInt8));
+  auto loss = torch::empty({}, image.options().dtype(torch::kFloat32));
+  auto unit = torch::empty_like(img);
+  const int status = l1_loss_forward(fptr(img, "image"), fptr(gt, "target"), img.numel(), loss.data_ptr<float>(), unit.data_ptr<float>(),
+                                     ws.data_ptr(), (size_t)ws.numel(), at::cuda::getCurrentCUDAStream(dev).stream());
+  if (status != GS_OK) fail("l1_loss_forward", status);
+  return {loss, unit};
+}
+
+torch::Tensor l1_backward_t(const torch::Tensor& unit, const torch::Tensor& g_) {
+  const c10::cuda::CUDAGuard guard(unit.device());
+  auto g = contig(g_);
+  auto out = torch::empty_like(unit);
+  const int status = l1_loss_backward(fptr(unit, "unit"), fptr(g, "dL_dloss"), unit.numel(), out.data_ptr<float>(),
+                                      at::cuda::getCurrentCUDAStream(unit.device().index()).stream());
+  if (status != GS_OK) fail("l1_loss_backward", status);
+  return out;
+}
+
 // ---- capacity / graph bookkeeping (what the ctypes shim kept in _DeviceState) ----
 int64_t get_capacity(int64_t dev) { return dev_state((int)dev).capacity; }
 void set_capacity(int64_t dev, int64_t cap) { dev_state((int)dev).capacity = cap; }
@@ -226,7 +337,7 @@ std::tuple<int64_t, bool> graph_overflow(int64_t dev) {
   if (over) { st.capacity = (int64_t)(N * kGrow) + 4096; g_regrows++; }
   return {N, over};
 }
-void release_cached() { g_state.clear(); }
+void release_cached() { g_state.clear(); g_l1_ws.clear(); }
 std::tuple<int64_t, int64_t, int64_t> counters() { return {g_forward_calls, g_backward_calls, g_regrows}; }
 
 }  // namespace
@@ -240,6 +351,10 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         py::arg("campos"), py::arg("geomBuffer"), py::arg("R"), py::arg("binningBuffer"), py::arg("imageBuffer"), py::arg("debug"),
         py::arg("dL_dout_opacity") = py::none());
   m.def("mark_visible", &mark_visible);
+  m.def("pose_forward", &pose_forward_t);
+  m.def("pose_backward", &pose_backward_t);
+  m.def("l1_forward", &l1_forward_t);
+  m.def("l1_backward", &l1_backward_t);
   m.def("get_capacity", &get_capacity);
   m.def("set_capacity", &set_capacity);
   m.def("graph_overflow", &graph_overflow);
