@@ -187,9 +187,9 @@ blend_fwd_work(FwdSmem& sm, const uint32_t work, const uint32_t n_items,
   const float X0 = (float)bx, X1 = (float)(bx + 7), Y0 = (float)by, Y1 = (float)(by + 3);
   const uint32_t* const tl = list + range.x;
   uint32_t* const rm = rowmask + ((size_t)seg_off[tile] * 8 + blk) * (2 * GS_SEG / 32);  // + segment * 64 + batch in segment * 2 + strip
-  // hand-off slots are indexed by the SENDING item (items with a successor occupy the first n_items - #non-empty tiles indices)
+  // (item.z / item.w ARE the slot numbers: plan_body numbers the receiving chunks of the frame densely, tile by tile)
   const float* const hin = reinterpret_cast<const float*>(hand + ((size_t)(has_pred ? item.w : 0u) * 8 + blk) * GS_HAND_WORDS);
-  float* const hout = reinterpret_cast<float*>(hand + ((size_t)(has_succ ? fi : 0u) * 8 + blk) * GS_HAND_WORDS);
+  float* const hout = reinterpret_cast<float*>(hand + ((size_t)(has_succ ? item.z : 0u) * 8 + blk) * GS_HAND_WORDS);
 
   // chain state (warp 0).  Tr is the running product of (1 - alpha) over ALL rows; it never increases (0 < 1 - alpha <= 1; a
   // row the pixel skips has alpha = 0 and multiplies by exactly 1), so "the pixel has terminated" (the reference's done flag,

@@ -34,7 +34,9 @@ struct GsHeader {            // first 256 bytes of the geom workspace
   unsigned int n_fitems;            // forward work items (tile, chunk) of the non-empty tiles, written by plan_kernel
   unsigned int n_empty_tiles;       // ... followed by this many single items of the empty tiles
   unsigned int fwd_ticket;          // next work unit of the persistent forward blend
-  unsigned int pad[55];
+  unsigned int fwd_order;           // order of the forward work items (plan_body): 0 longest-remaining-chain first, 1 chunk level by level
+  unsigned int n_nonempty_tiles;    // tiles with a list (level order: hand-off slot of an item = successor's index - this)
+  unsigned int pad[53];
 };
 
 // One packed record per Gaussian, what both blend kernels gather per list entry (3 x LDG.128).

@@ -21,6 +21,8 @@
 // onesweep pass: one kernel per 8-bit digit; warp-level multi-split with __match_any_sync, per-warp digit counters
 // in shared memory, CTA-wide digit offsets, decoupled look-back across CTAs on a (flag|count) status word per
 // (CTA, digit); digit histograms come for free from the producing kernels (preprocess / emit).
+#include <cstdlib>
+
 #include "gs_common.cuh"
 namespace {
 
@@ -345,32 +347,41 @@ __device__ __forceinline__ uint32_t block_scan_incl_1024(uint32_t v, uint32_t* s
 // `ranges` may live in global memory (plan_kernel) or in shared memory (the plan block of bin_place_kernel).  1024 threads.
 __device__ __forceinline__ void plan_body(int tiles, const uint2* ranges, uint32_t* __restrict__ seg_off, uint2* __restrict__ items,
                                           uint32_t max_items, uint4* __restrict__ fitems, uint32_t max_fitems,
-                                          GsHeader* __restrict__ hdr) {
+                                          GsHeader* __restrict__ hdr, int fwd_order) {
   __shared__ uint32_t s_w[32];
   __shared__ uint32_t s_hist[GS_FWD_NCH_BINS];  // tiles per chunk count -> cursor of the counting sort
   __shared__ uint32_t s_base[GS_FWD_NCH_BINS];  // base[r] = sum over k < r of ge[k]
-  __shared__ uint32_t s_total, s_nonempty;
+  __shared__ uint32_t s_total, s_nonempty, s_maxch;
+  constexpr int MIX_D = 32;
+  __shared__ uint32_t s_mix_first[2 * MIX_D], s_mix_off[2 * MIX_D][MIX_D + 1], s_mix_ge[MIX_D + 1];
   const int tid = threadIdx.x;
   for (int k = tid; k < GS_FWD_NCH_BINS; k += 1024) s_hist[k] = 0;
+  if (tid == 0) s_maxch = 0;
   __syncthreads();
-  uint32_t carry = 0;
+  uint32_t carry = 0, rcarry = 0;
+  uint32_t roff_l[64];  // this thread's tiles (t = t0 + tid in both loops): first hand-off slot of the tile; 65535 tiles at most
   for (int t0 = 0; t0 < tiles; t0 += 1024) {
     const int t = t0 + tid;
-    uint32_t nseg = 0;
+    uint32_t nseg = 0, nrecv = 0;
     if (t < tiles) {
       const uint2 r = ranges[t];
       const uint32_t len = r.y - r.x;
       nseg = (len + GS_SEG - 1) / GS_SEG;
-      atomicAdd(&s_hist[min((len + GS_FWD_CHUNK - 1) / GS_FWD_CHUNK, (uint32_t)GS_FWD_NCH_BINS - 1)], 1u);
+      const uint32_t nch = min((len + GS_FWD_CHUNK - 1) / GS_FWD_CHUNK, (uint32_t)GS_FWD_NCH_BINS - 1);
+      atomicAdd(&s_hist[nch], 1u);
+      atomicMax(&s_maxch, nch);
+      nrecv = nch ? nch - 1 : 0;  // chunks that receive a chain state
     }
-    uint32_t total;
+    uint32_t total, rtotal;
     const uint32_t off = carry + block_scan_incl_1024(nseg, s_w, &total) - nseg;
+    roff_l[(t0 >> 10) & 63] = rcarry + block_scan_incl_1024(nrecv, s_w, &rtotal) - nrecv;
     if (t < tiles) {
       seg_off[t] = off;
       for (uint32_t k = 0; k < nseg; k++)
         if (off + k < max_items) items[off + k] = make_uint2((uint32_t)t, k);
     }
     carry += total;
+    rcarry += rtotal;
   }
   if (tid == 0) seg_off[tiles] = carry < max_items ? carry : max_items;
   __syncthreads();
@@ -392,35 +403,68 @@ __device__ __forceinline__ void plan_body(int tiles, const uint2* ranges, uint32
       hdr->n_fitems = total2 < max_fitems ? total2 : max_fitems;
       s_nonempty = ge0;                                                        // ge[0]
       hdr->n_empty_tiles = h0;                                                 // hist[0]
+      hdr->n_nonempty_tiles = ge0;
     }
   }
   __syncthreads();
+  const int D = (int)s_maxch;
+  if (fwd_order >= 2 && D > MIX_D) fwd_order = 0;  // very deep lists (> 8192 entries in a tile): the closed-form order
+  if (tid == 0) hdr->fwd_order = (unsigned)fwd_order;
+  // mixed order (fwd_order 2): bucket K = 2 c + (D - nch) holds chunk c of the tiles with nch chunks -- half-way between level
+  // order (K = c) and longest-remaining-first (K = c + D - nch): the shallow tiles' chunks fill the machine while the deep chains
+  // run, instead of all arriving behind them.  s_mix_off[K][n] = items of bucket K that belong to tiles deeper than n (deeper
+  // tiles come first inside a bucket; [K][0] = the whole bucket), s_mix_first[K] = first item of the bucket.
+  if (fwd_order == 2) {
+    if (tid < 2 * D) {  // one thread per bucket: suffix sums over the chunk counts
+      const int K = tid;
+      uint32_t o = 0;
+      for (int n = D; n >= 0; n--) {
+        s_mix_off[K][n] = o;
+        const int e = K - D + n;  // chunk c = e / 2 of the tiles with n chunks lies in this bucket if it is an integer in [0, n)
+        if (n >= 1 && e >= 0 && !(e & 1) && (e >> 1) < n) o += s_hist[n - 1] - s_hist[n];  // hist[n] = ge[n-1] - ge[n]
+      }
+    }
+    if (tid <= MIX_D) s_mix_ge[tid] = s_hist[tid];  // ge[n] before the cursors below move
+    __syncthreads();
+    if (tid == 0) {
+      uint32_t run = 0;
+      for (int K = 0; K < 2 * D; K++) { s_mix_first[K] = run; run += s_mix_off[K][0]; }
+    }
+    __syncthreads();
+  }
   const uint32_t n_items = s_total, n_nonempty = s_nonempty;
   for (int t = tid; t < tiles; t += 1024) {
     const uint2 r = ranges[t];
     const uint32_t len = r.y - r.x;
     const uint32_t nch = min((len + GS_FWD_CHUNK - 1) / GS_FWD_CHUNK, (uint32_t)GS_FWD_NCH_BINS - 1);
     const uint32_t pos = atomicAdd(&s_hist[nch], 1u);
+    const uint32_t roff = roff_l[(t >> 10) & 63];
     if (nch == 0) {  // empty tile: one item behind everything else
       const uint32_t fi = n_items + (pos - n_nonempty);
       if (fi < max_fitems) fitems[fi] = make_uint4((uint32_t)t, 0u, 0xFFFFFFFFu, 0xFFFFFFFFu);
       continue;
     }
+    // item = (tile, chunk, hand-off slot it SENDS its chain state to or ~0, slot it RECEIVES from or ~0); a predecessor always
+    // has a smaller index in every order, which is what makes the forward's wait deadlock-free
     for (uint32_t c = 0; c < nch; c++) {
       const uint32_t rem = nch - c;  // chunks remaining in this tile's chain, this one included
-      const uint32_t fi = n_items - s_base[rem] + pos;
-      if (fi < max_fitems)
-        fitems[fi] = make_uint4((uint32_t)t, c, rem > 1 ? n_items - s_base[rem - 1] + pos : 0xFFFFFFFFu,
-                                c > 0 ? n_items - s_base[rem + 1] + pos : 0xFFFFFFFFu);
+      uint32_t fi;
+      if (fwd_order == 0) fi = n_items - s_base[rem] + pos;  // longest remaining chain first
+      else if (fwd_order == 1) fi = s_base[c] + pos;         // level by level, deepest tiles first inside a level
+      else {  // mixed
+        const int K = 2 * (int)c + D - (int)nch;
+        fi = s_mix_first[K] + s_mix_off[K][nch] + (pos - s_mix_ge[nch]);  // deeper tiles first, then the rank among equals
+      }
+      if (fi < max_fitems) fitems[fi] = make_uint4((uint32_t)t, c, rem > 1 ? roff + c : 0xFFFFFFFFu, c > 0 ? roff + c - 1 : 0xFFFFFFFFu);
     }
   }
 }
 
 __global__ void __launch_bounds__(1024)
 plan_kernel(int tiles, const uint2* __restrict__ ranges, uint32_t* __restrict__ seg_off, uint2* __restrict__ items,
-            uint32_t max_items, uint4* __restrict__ fitems, uint32_t max_fitems, GsHeader* __restrict__ hdr) {
+            uint32_t max_items, uint4* __restrict__ fitems, uint32_t max_fitems, GsHeader* __restrict__ hdr, int fwd_order) {
   GS_PDL_PROLOGUE();
-  plan_body(tiles, ranges, seg_off, items, max_items, fitems, max_fitems, hdr);
+  plan_body(tiles, ranges, seg_off, items, max_items, fitems, max_fitems, hdr, fwd_order);
 }
 
 // tiles <= 2 * GS_BIN_THREADS.  Block 0 also publishes the tile ranges (identifyTileRanges, rasterizer_impl.cu:116-138:
@@ -434,7 +478,7 @@ bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __re
                  const uint32_t* __restrict__ rect, int grid_x, int tiles, uint32_t* blockcount, uint32_t* tile_total,
                  unsigned long long cap, uint32_t* __restrict__ list, uint2* __restrict__ ranges, GsHeader* __restrict__ hdr,
                  uint32_t* grid_bar, uint32_t* __restrict__ seg_off, uint2* __restrict__ items, uint32_t max_items,
-                 uint4* __restrict__ fitems, uint32_t max_fitems) {
+                 uint4* __restrict__ fitems, uint32_t max_fitems, int fwd_order) {
   GS_PDL_PROLOGUE();
   extern __shared__ __align__(16) unsigned char s_raw[];
   uint16_t* s_off = reinterpret_cast<uint16_t*>(s_raw);                                  // [32][tiles]
@@ -513,7 +557,7 @@ bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __re
     if (ta < tiles) s_range[ta] = ca ? make_uint2(min(sa, lim), min(sa + ca, lim)) : make_uint2(0u, 0u);
     if (tb < tiles) s_range[tb] = cb ? make_uint2(min(sb, lim), min(sb + cb, lim)) : make_uint2(0u, 0u);
     __syncthreads();
-    plan_body(tiles, s_range, seg_off, items, max_items, fitems, max_fitems, hdr);
+    plan_body(tiles, s_range, seg_off, items, max_items, fitems, max_fitems, hdr, fwd_order);
     return;
   }
   if (ta < tiles) s_base[ta] = sa + pa;
@@ -669,6 +713,8 @@ uint32_t higher_msb(uint32_t n) {  // rasterizer_impl.cu:35-50
 int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsScratch& s, const GsList& l,
                       int64_t cap, cudaStream_t st) {
   uint32_t* list = l.point_list;
+  // plan_body's order of the forward work items: 2 (default) mixed, 0 longest remaining chain first, 1 level by level
+  static const int fwd_order = [] { const char* e = getenv("GS_FWD_ORDER"); return e ? atoi(e) : 2; }();
   const int P = a.P;
   const int gx = (a.width + GS_TILE - 1) / GS_TILE, gy = (a.height + GS_TILE - 1) / GS_TILE;
   const int tiles = gx * gy;
@@ -705,7 +751,7 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
     gs_launch(fused ? bin_place_kernel<true> : bin_place_kernel<false>, dim3(blocks_c + (fused ? 1 : 0)), dim3(GS_BIN_THREADS), smem_p,
               st, P, (const uint32_t*)s.dval[0], (const uint32_t*)s.dval[1], (const uint32_t*)s.hist, (const uint32_t*)g.tiles_touched,
               (const uint32_t*)g.rect, gx, tiles, blockcount, s.tile_total, (unsigned long long)cap, list, im.ranges, g.hdr,
-              s.counters + 16, im.seg_off, l.items, (uint32_t)l.max_items, (uint4*)l.fitems, (uint32_t)l.max_fitems);
+              s.counters + 16, im.seg_off, l.items, (uint32_t)l.max_items, (uint4*)l.fitems, (uint32_t)l.max_fitems, fwd_order);
     if (fused) return gs_check(cudaGetLastError());  // the plans came from the placement grid's last block
   } else {
     // 2. chained scan + pair emission in depth order
@@ -739,6 +785,6 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   }
   // 5. backward work plan (segments of GS_SEG entries per tile)
   gs_launch(plan_kernel, dim3(1), dim3(1024), 0, st, tiles, im.ranges, im.seg_off, l.items, (uint32_t)l.max_items, l.fitems,
-            (uint32_t)l.max_fitems, g.hdr);
+            (uint32_t)l.max_fitems, g.hdr, fwd_order);
   return gs_check(cudaGetLastError());
 }
