@@ -6,6 +6,8 @@ because the FP32 operation order is shared by specification, final_T and the ima
 The tests of this file run the blend in ORACLE EXP MODE (gs_set_exp_mode(1): the polynomial exp that oracle/gs_oracle.c
 reproduces bit for bit); the default mode -- CUDA's expf, the reference's instruction sequence -- is compared with the
 reference's own CUDA build in tests/test_gpu_vs_reference_cuda.py and with the oracle in test_default_exp_mode_vs_oracle."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -355,3 +357,17 @@ def test_mark_visible(built_lib):
                                                 d(cam["full_proj_transform"]), 3, d(cam["camera_center"]), False, False)
         rmask = ref.GaussianRasterizer(rrs).markVisible(d(means)).cpu().numpy()
         assert np.array_equal(got, rmask), f"{int((got != rmask).sum())} visibility decisions differ from the reference build"
+
+
+@pytest.mark.parametrize("order", ["0", "1"])
+def test_alternative_forward_item_orders(built_lib, order):
+    """The forward blend's work items can be planned in three orders (GS_FWD_ORDER: 2 = mixed, the default; 0 = longest remaining
+    chain first; 1 = level by level).  The order only schedules: images, n_contrib and gradients must not depend on it.  The
+    variable is read once per process, so the bit-exact tests of the deep-list and bench-size scenes run in a child process."""
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, GS_FWD_ORDER=order)
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_rasterizer.py"), "-q", "-m", "gpu", "-x", "-k",
+                        "deep_lists or bench_config or trained_like or unfused"], env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]
