@@ -186,7 +186,7 @@ blend_fwd_work(FwdSmem& sm, const uint32_t work, const uint32_t n_items,
   const float pfx = (float)px, pfy = (float)py;
   const float X0 = (float)bx, X1 = (float)(bx + 7), Y0 = (float)by, Y1 = (float)(by + 3);
   const uint32_t* const tl = list + range.x;
-  uint32_t* const rm = rowmask + ((size_t)seg_off[tile] * 8 + blk) * (2 * GS_SEG / 32);  // + segment * 64 + batch in segment * 2 + strip
+  uint32_t* const rm = rowmask + ((size_t)seg_off[tile] * 8 + blk) * GS_MASK_WORDS;  // + segment * 8 * GS_MASK_WORDS + batch in segment * 4 + group
   // (item.z / item.w ARE the slot numbers: plan_body numbers the receiving chunks of the frame densely, tile by tile)
   const float* const hin = reinterpret_cast<const float*>(hand + ((size_t)(has_pred ? item.w : 0u) * 8 + blk) * GS_HAND_WORDS);
   float* const hout = reinterpret_cast<float*>(hand + ((size_t)(has_succ ? item.z : 0u) * 8 + blk) * GS_HAND_WORDS);
@@ -264,7 +264,7 @@ blend_fwd_work(FwdSmem& sm, const uint32_t work, const uint32_t n_items,
         sm.row[rowbase + lane] = make_float4(cur.c.x, cur.c.y, cur.c.z, __int_as_float(r0 + rowbase + lane + 1));
       }
       __syncwarp();
-      uint32_t m = __ballot_sync(0xFFFFFFFFu, keep), kept_lo = 0, kept_hi = 0;
+      uint32_t m = __ballot_sync(0xFFFFFFFFu, keep), kept0 = 0, kept1 = 0, kept2 = 0, kept3 = 0;
       while (m) {
         float al[kPChunk];
         bool ok[kPChunk];
@@ -290,16 +290,19 @@ blend_fwd_work(FwdSmem& sm, const uint32_t work, const uint32_t n_items,
           if (jj[u] >= 0) {  // warp-uniform
             sm.alpha[rowbase + jj[u]][lane] = ok[u] ? al[u] : 0.0f;
             const uint32_t who = __ballot_sync(0xFFFFFFFFu, ok[u]);  // rows no pixel of the block blends never reach the chain
-            if (who & 0xFFFFu) kept_lo |= 1u << jj[u];              // per 8x2 strip (lanes 0-15 / 16-31): what the backward visits
-            if (who >> 16) kept_hi |= 1u << jj[u];
+            // per 4x2 pixel group (lane = x + 8 y: x < 4 | x >= 4, y < 2 | y >= 2): what the backward visits
+            if (who & 0x00000F0Fu) kept0 |= 1u << jj[u];
+            if (who & 0x0000F0F0u) kept1 |= 1u << jj[u];
+            if (who & 0x0F0F0000u) kept2 |= 1u << jj[u];
+            if (who & 0xF0F00000u) kept3 |= 1u << jj[u];
           }
         }
         __syncwarp();
       }
       if (lane == 0) {
-        sm.mask[b] = kept_lo | kept_hi;
+        sm.mask[b] = kept0 | kept1 | kept2 | kept3;
         const int bg_ = (r0 >> 5) + b;  // batch index inside the tile list
-        *reinterpret_cast<uint2*>(rm + (size_t)(bg_ >> 2) * 64 + (bg_ & 3) * 2) = make_uint2(kept_lo, kept_hi);
+        *reinterpret_cast<uint4*>(rm + (size_t)(bg_ >> 2) * (8 * GS_MASK_WORDS) + (bg_ & 3) * 4) = make_uint4(kept0, kept1, kept2, kept3);
       }
     }
     __syncthreads();
@@ -473,13 +476,14 @@ __device__ __forceinline__ void xpose_step(float* v, int lane) {
 // T = T(seg end), accumulated colour behind it = (C_final - C(seg end)) / T(seg end); inside the segment the recurrences
 // are the reference's (backward.cu:497-534).  Deep tile lists thus spread over many SMs instead of one.
 //
-// Inside a warp the two 8x2 pixel strips (lanes 0-15 / 16-31) walk their OWN entry sequences -- the forward left one mask per
-// strip and 32-entry batch: the entries at least one pixel of the strip blended -- so one warp instruction evaluates two
-// different entries, and the reductions run over 16 lanes instead of 32 (avatar splats cover ~8 pixels of an 8x4 block: most
-// lanes of a whole-block visit were dead).  Per (pixel, entry) only RAW MOMENTS of g = G * dL/dalpha are formed --
-// sum g, g dx, g dy, g dx^2, g dx dy, g dy^2 and the three colour terms -- reduced with a transposing butterfly (2 entries x 8
-// terms -> 15 shuffles, lane L ends with the total of term L & 15) BEFORE one atomic per lane; preprocess_bwd_kernel turns the
-// moments into dL/dmean2D, dL/dconic (it reads the conic and the opacity of the Gaussian anyway).
+// Inside a warp the four 4x2 pixel GROUPS (eight consecutive lanes each) walk their OWN entry sequences -- the forward left one
+// mask per group and 32-entry batch: the entries at least one pixel of the group blended -- so one warp instruction evaluates
+// four different entries, and the reductions run over 8 lanes instead of 32 (avatar splats cover a handful of pixels of an 8x4
+// block: with whole-block visits most lanes were dead, with 8x2 strips still four of five).  Per (pixel, entry) only RAW MOMENTS
+// of g = G * dL/dalpha are formed -- sum g, g dx, g dy, g dx^2, g dx dy, g dy^2 and the three colour terms -- reduced with a
+// transposing butterfly (2 entries x 8 terms over 8 lanes -> 14 shuffles, a lane ends with two adjacent terms of one entry)
+// BEFORE one 8-byte vector reduction per lane; preprocess_bwd_kernel turns the moments into dL/dmean2D, dL/dconic (it reads
+// the conic and the opacity of the Gaussian anyway).
 #ifndef GS_BWD_MINBLOCKS
 #define GS_BWD_MINBLOCKS 3
 #endif
@@ -510,7 +514,11 @@ blend_bwd_item(const uint32_t item_index, BwdSlab& sl, const uint2* __restrict__
   const int seg_begin = (int)item.y * GS_SEG, seg_end = min(len, seg_begin + GS_SEG);
   const int tx = tile % grid_x, ty = tile / grid_x;
   const int bx = tx * GS_TILE + (w & 1) * 8, by = ty * GS_TILE + (w >> 1) * 4;
-  const int px = bx + (lane & 7), py = by + (lane >> 3);
+  // lane -> pixel of the warp's 8x4 block: the four 4x2 pixel GROUPS are eight consecutive lanes each (the reductions below run
+  // inside a group); `flane` is the same pixel's lane in the forward's x + 8 y numbering (checkpoints are stored by it)
+  const int grp = lane >> 3, gi = lane & 7;
+  const int xl = (grp & 1) * 4 + (gi & 3), yl = (grp >> 1) * 2 + (gi >> 2), flane = xl + 8 * yl;
+  const int px = bx + xl, py = by + yl;
   const bool inside = px < W && py < H;
   const float pfx = (float)px, pfy = (float)py;
   const size_t pix = (size_t)py * W + px, hw = (size_t)H * W;
@@ -521,15 +529,18 @@ blend_bwd_item(const uint32_t item_index, BwdSlab& sl, const uint2* __restrict__
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xFFFFFFFFu, wmax, o));
   if (wmax <= seg_begin) return;
-  // per strip and batch: the entries at least one pixel of the strip blended in the forward pass (written by the forward's
-  // producers for every batch of every chunk it ran, i.e. every batch below wmax): the only ones worth visiting
-  const uint4* const mp = reinterpret_cast<const uint4*>(rowmask + (((size_t)seg_off[tile] + item.y) * 8 + w) * (2 * GS_SEG / 32));
-  const uint4 mA = mp[0], mB = mp[1];  // {batch0 lo, batch0 hi, batch1 lo, batch1 hi}, {batch2 ..., batch3 ...}
+  // per 4x2 pixel group and batch: the entries at least one pixel of the group blended in the forward pass (written by the
+  // forward's producers for every batch of every chunk it ran, i.e. every batch below wmax): the only ones worth visiting
+  const uint4* const mp = reinterpret_cast<const uint4*>(rowmask + (((size_t)seg_off[tile] + item.y) * 8 + w) * GS_MASK_WORDS);
   wmax -= seg_begin;  // positions below are relative to the segment start (a multiple of 32)
   const int hi_rel = hi - seg_begin;
-  const bool upper = lane >= 16;
-  uint32_t mall[4] = {mA.x | mA.y, mA.z | mA.w, mB.x | mB.y, mB.z | mB.w};
-  uint32_t mine[4] = {upper ? mA.y : mA.x, upper ? mA.w : mA.z, upper ? mB.y : mB.x, upper ? mB.w : mB.z};
+  uint32_t mall[4], mine[4];
+#pragma unroll
+  for (int b = 0; b < 4; b++) {  // batch b: {group 0, 1, 2, 3}
+    const uint4 mb = mp[b];
+    mall[b] = mb.x | mb.y | mb.z | mb.w;
+    mine[b] = grp == 0 ? mb.x : grp == 1 ? mb.y : grp == 2 ? mb.z : mb.w;
+  }
 #pragma unroll
   for (int b = 0; b < 4; b++) {  // nothing at or behind wmax
     const int n = wmax - b * 32;
@@ -556,7 +567,7 @@ blend_bwd_item(const uint32_t item_index, BwdSlab& sl, const uint2* __restrict__
   float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_alpha = 0.f;
   float acc3 = 0.f, lc3 = 0.f;  // opacity channel: its colour is 1 once a contributor has been seen
   if (last_contributor > seg_end) {  // restart from the checkpoint at the segment end
-    const size_t ck_base = ((size_t)seg_off[tile] + tile) * 256 + threadIdx.x;
+    const size_t ck_base = ((size_t)seg_off[tile] + tile) * 256 + w * 32 + flane;
     const float4* ck = ckpt + ck_base;
     const float4 c = ck[(size_t)(item.y + 1) * 256];
     const float4 cf = ck[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256];
@@ -574,10 +585,8 @@ blend_bwd_item(const uint32_t item_index, BwdSlab& sl, const uint2* __restrict__
   // the second call's image has the same background; only its channel 0 carries an upstream gradient (`[:1]`)
   const float bg_dot_dpixel = bg[0] * dp0 + bg[1] * dp1 + bg[2] * dp2 + (OP ? bg[0] * dp3 : 0.f);
   const float nTfbg = -T_final * bg_dot_dpixel;
-  // which accumulator this lane feeds after the transposing reduction: entry (lane >> 3) & 1 of its strip's pair, term lane & 7
-  // of the Gaussian's 48-byte record: 0,1 -> sum g dx, g dy; 2,3,4 -> sum g dx^2, g dx dy, g dy^2; 5 -> sum g (= dL_dopacity);
-  // 6,7 (+ the separate ninth term at 8) -> colour gradient
-  const int comp = lane & 7;
+  // terms of the Gaussian's 48-byte accumulator record: 0,1 -> sum g dx, g dy; 2,3,4 -> sum g dx^2, g dx dy, g dy^2; 5 -> sum g
+  // (= dL_dopacity); 6,7 (+ the separate ninth term at 8) -> colour gradient
   uint32_t nblend = 0;  // blended (pixel, entry) pairs = E_bwd of SURVEY.md 8(d), summed into the frame header
   __syncwarp();
 
@@ -635,20 +644,19 @@ blend_bwd_item(const uint32_t item_index, BwdSlab& sl, const uint2* __restrict__
         }
       }
       if (!__any_sync(0xFFFFFFFFu, any_ok)) continue;
-      // strip reduction BEFORE the atomics: lane L ends with the total of v[L & 15] over the 16 lanes of its strip
-      xpose_step<16, 8>(v, lane);
-      xpose_step<8, 4>(v, lane);
-      xpose_step<4, 2>(v, lane);
-      xpose_step<2, 1>(v, lane);
-      xpose_step<2, 8>(v8, lane);
+      // group reduction BEFORE the atomics: 2 entries x 8 terms over the 8 lanes of the group -> lane i ends with the totals of
+      // terms 2 (i & 3), 2 (i & 3) + 1 of entry (i >> 2): one 8-byte vector reduction per lane
+      xpose_step<16, 4>(v, lane);
+      xpose_step<8, 2>(v, lane);
+      xpose_step<4, 1>(v, lane);
+      xpose_step<2, 4>(v8, lane);
       float r8 = v8[0];
-      r8 += __shfl_xor_sync(0xFFFFFFFFu, r8, 4);
       r8 += __shfl_xor_sync(0xFFFFFFFFu, r8, 2);
       r8 += __shfl_xor_sync(0xFFFFFFFFu, r8, 1);
-      const uint32_t my_id = (lane & 8) ? ids[1] : ids[0];
-      const float r = v[0];
-      if (r != 0.f) atomicAdd(acc + (size_t)GS_ACC * my_id + comp, r);
-      if (comp == 0 && r8 != 0.f) atomicAdd(acc + (size_t)GS_ACC * my_id + 8, r8);
+      const uint32_t my_id = (lane & 4) ? ids[1] : ids[0];
+      float* const dst = acc + (size_t)GS_ACC * my_id + 2 * (lane & 3);
+      if (v[0] != 0.f || v[1] != 0.f) asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(dst), "f"(v[0]), "f"(v[1]) : "memory");
+      if ((lane & 3) == 0 && r8 != 0.f) atomicAdd(acc + (size_t)GS_ACC * my_id + 8, r8);
     }
   }
   nblend = __reduce_add_sync(0xFFFFFFFFu, nblend);

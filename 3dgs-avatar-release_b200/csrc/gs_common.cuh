@@ -23,6 +23,7 @@
 #define GS_FWD_CHUNK 256    // list entries per forward work item (tile, pixel block, chunk): a multiple of GS_SEG.  Measured at
 #endif                      // cfg-A: 256 entries / 4 warps / 5 CTAs per SM 78 us, 512 / 8 warps / 3 CTAs 88 us (profiles/r2)
 #define GS_FWD_NCH_BINS 2048  // plan_kernel sorts tiles by chunk count with a counting sort of this many bins
+#define GS_MASK_WORDS (4 * GS_SEG / 32)  // rowmask words per (segment, pixel block): 4 batches x 4 pixel groups of 4x2
 #define GS_HAND_WORDS (32 * 6)  // hand-off slot of one (tile, pixel block, chunk): 32 lanes x {T, C0, C1, C2} + {last|flags, C3}
 
 // ---- workspace layouts (private; reached from outside only through gs_debug_read) ----
@@ -72,7 +73,7 @@ struct GsList {
   uint2* items;             // [max_items] (tile, segment) work items of the backward blend
   float4* ckpt;             // [(max_items + tiles) * 256] per-pixel (T, C.rgb) at every segment start + final state
   float* ckpt_op;           // same slots: accumulated opacity channel (written only by the fused opacity pass)
-  uint32_t* rowmask;        // [max_items][8 pixel blocks][GS_SEG / 32][2 strips] per 32-entry batch and 8x2 pixel strip: entries at
+  uint32_t* rowmask;        // [max_items][8 pixel blocks][GS_SEG / 32][4 groups] per 32-entry batch and 4x2 pixel group: entries at
                             // least one pixel of the strip blended in the forward pass (what the backward blend visits)
   uint4* fitems;            // [max_fitems] forward work items (tile, chunk, index of the successor item or ~0, index of the
                             // predecessor item or ~0), longest remaining chain first: a predecessor always has a smaller index
@@ -142,7 +143,7 @@ static inline __host__ size_t gs_carve_list(char* base, int64_t cap, int W, int 
   gs_carve(p, t.items, t.max_items);
   gs_carve(p, t.ckpt, (t.max_items + tiles) * 256);
   gs_carve(p, t.ckpt_op, (t.max_items + tiles) * 256);
-  gs_carve(p, t.rowmask, t.max_items * 8 * (2 * GS_SEG / 32));
+  gs_carve(p, t.rowmask, t.max_items * 8 * GS_MASK_WORDS);
   gs_carve(p, t.fitems, t.max_fitems);
   if (l) *l = t;
   return (size_t)(p - base);
