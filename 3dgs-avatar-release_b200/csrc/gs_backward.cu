@@ -101,7 +101,7 @@ __device__ void cov3d_backward(const float* __restrict__ s3, float mod, const fl
   dL_drot[3] = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
 }
 
-__global__ void __launch_bounds__(256) preprocess_bwd_kernel(GsBackwardArgs a, const float* __restrict__ cov3Ds,
+__global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(GsBackwardArgs a, const float* __restrict__ cov3Ds,
                                                              const uint8_t* __restrict__ clamped, const GsRec* __restrict__ recs,
                                                              float* __restrict__ accs) {
   GS_PDL_PROLOGUE();
@@ -117,8 +117,16 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(GsBackwardArgs a, c
     // the blend's accumulators: consumed here and zeroed again (a second backward over the same forward starts clean)
     float4* const ac = reinterpret_cast<float4*>(accs + (size_t)GS_ACC * idx);
     const float4 ac0 = ac[0], ac1 = ac[1], ac2 = ac[2];
+    // every load of this Gaussian is issued BEFORE the visibility branch (all of them are in bounds for a culled Gaussian too):
+    // one memory round trip per thread instead of two -- at 1M Gaussians the kernel sat on long-scoreboard stalls
+    const int radius = a.radii[idx];
+    const float mx = a.means3D[3 * (size_t)idx], my = a.means3D[3 * (size_t)idx + 1], mz = a.means3D[3 * (size_t)idx + 2];
+    float c6[6];
+#pragma unroll
+    for (int k = 0; k < 6; k++) c6[k] = cov3Ds[6 * (size_t)idx + k];
+    const float4 rb = reinterpret_cast<const float4*>(recs + idx)[1];  // conic a, b, c, opacity
     ac[0] = ac[1] = ac[2] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (!(a.radii[idx] > 0)) {  // culled: every gradient is zero (the outputs need no initialisation by the caller)
+    if (!(radius > 0)) {  // culled: every gradient is zero (the outputs need no initialisation by the caller)
       a.dL_dmean2D[3 * (size_t)idx] = a.dL_dmean2D[3 * (size_t)idx + 1] = a.dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
       a.dL_dopacity[idx] = 0.f;
       if (a.dL_dconic) *reinterpret_cast<float4*>(a.dL_dconic + 4 * (size_t)idx) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -135,14 +143,9 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(GsBackwardArgs a, c
       }
       continue;
     }
-    const float mx = a.means3D[3 * (size_t)idx], my = a.means3D[3 * (size_t)idx + 1], mz = a.means3D[3 * (size_t)idx + 2];
-    float c6[6];
-#pragma unroll
-    for (int k = 0; k < 6; k++) c6[k] = cov3Ds[6 * (size_t)idx + k];
     // blend_bwd_kernel left RAW MOMENTS of g = G * dL/dalpha over the blended (pixel, Gaussian) pairs: sum g dx, g dy, g dx^2,
     // g dx dy, g dy^2, g and the colour gradient.  With the Gaussian's conic and opacity they become the sums of
     // backward.cu:536-549: dL_dmean2D = -ddel * o * (conic * m1), dL_dconic = -0.5 * o * m2, dL_dopacity = sum g.
-    const float4 rb = reinterpret_cast<const float4*>(recs + idx)[1];  // conic a, b, c, opacity
     const float m1x = ac0.x, m1y = ac0.y;
     const float g2x = -(0.5f * a.width) * rb.w * (rb.x * m1x + rb.y * m1y);
     const float g2y = -(0.5f * a.height) * rb.w * (rb.z * m1y + rb.y * m1x);
