@@ -458,6 +458,246 @@ blend_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
   }
 }
 
+// ---- forward, per-block variant: one CTA per (tile, 8x4 pixel block) walks the WHOLE list ------------------------------
+// Seven producer warps take the list's 32-entry batches round-robin (records software-pipelined one batch ahead, list indices
+// two ahead), cull, evaluate and leave rows alpha[row][pixel] in their own shared-memory buffer; ONE consumer warp applies the
+// rows in list order (the same chain as above); full / empty mbarriers per producer buffer.  Producers and consumer overlap
+// inside the CTA, so all eight warps stay busy -- the right shape when a frame has thousands of SHALLOW tiles (1M Gaussians at
+// 1080p: 8160 tiles of one or two chunks): nothing is gained from cutting chains there, and the chunked kernel's rows-then-chain
+// units leave three of four warps idle during the chain (757 us against 531 us for this kernel).  With few deep tiles (avatar
+// frames at 512^2) the consumer of the deepest block is the critical path and the chunked kernel wins.  The launcher picks by
+// the size of the tile grid.  Same operations in the same order per pixel: both kernels produce identical bits.
+constexpr int kBkProducers = 7;
+struct BkBuf {             // one per producer warp
+  float4 q0[32], q1[32];   // staged records: x, y, conic a, b | conic c, opacity, r, g
+  float q2[32];            // b
+  float alpha[32][32];     // [row][pixel lane]; 0 = the reference's skip tests failed
+  float4 row[32];          // [row] r, g, b, 1-based list position (int bits)
+  uint32_t cnt;            // rows in this batch
+  uint32_t pad[3];
+};
+struct BkCtl {
+  unsigned long long full[kBkProducers];   // producer -> consumer: rows of the buffer are ready
+  unsigned long long empty[kBkProducers];  // consumer -> producer: buffer may be overwritten
+  uint32_t done;                           // every pixel of the block has terminated
+  uint32_t pad[3];
+};
+__device__ __forceinline__ uint32_t bk_ld_acquire(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"((uint32_t)__cvta_generic_to_shared(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void bk_st_release(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ void bk_mbar_init(unsigned long long* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void bk_mbar_arrive(unsigned long long* bar) {  // release: prior shared-memory writes are visible
+  asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void bk_mbar_arrive_relaxed(unsigned long long* bar) {  // WAR hand-back: the reads were consumed
+  asm volatile("mbarrier.arrive.relaxed.cta.shared::cta.b64 _, [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void bk_mbar_wait(unsigned long long* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "BKW_%=:\n"
+      "mbarrier.try_wait.parity.acquire.cta.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra BKD_%=;\n"
+      "bra BKW_%=;\n"
+      "BKD_%=:\n"
+      "}\n" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ bool bk_mbar_try_wait(unsigned long long* bar, uint32_t parity) {  // bounded suspend, then returns
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.acquire.cta.shared::cta.b64 p, [%1], %2, %3;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n" : "=r"(ok) : "r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(parity), "r"(1000u) : "memory");
+  return ok != 0;
+}
+
+template <bool OP, bool POLY>
+__global__ void __launch_bounds__((kBkProducers + 1) * 32)
+blend_fwd_block_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ list, int W, int H, const GsRec* __restrict__ rec,
+                       const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+                       float* __restrict__ out_color, const uint32_t* __restrict__ seg_off, float4* __restrict__ ckpt,
+                       const uint32_t* __restrict__ order, int grid_x, float* __restrict__ out_opacity, float* __restrict__ ckpt_op,
+                       uint32_t* __restrict__ rowmask) {
+  GS_PDL_PROLOGUE();
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  BkCtl& ctl = *reinterpret_cast<BkCtl*>(smem_raw);
+  BkBuf* const bufs = reinterpret_cast<BkBuf*>(smem_raw + sizeof(BkCtl));
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;  // warp 0 = consumer, 1..kBkProducers = producers
+  const int blk = blockIdx.x & 7;                              // pixel block of the tile
+  const int tile = (int)order[blockIdx.x >> 3];                // longest lists first
+  const int tile_x = tile % grid_x, tile_y = tile / grid_x;
+  const uint2 range = ranges[tile];
+  const int len = (int)(range.y - range.x);
+  const int nb = (len + 31) >> 5;
+  const int bx = tile_x * GS_TILE + (blk & 1) * 8, by = tile_y * GS_TILE + (blk >> 1) * 4;
+  const int px = bx + (lane & 7), py = by + (lane >> 3);
+  const bool inside = px < W && py < H;
+  if (threadIdx.x == 0) {
+    ctl.done = 0;
+    for (int i = 0; i < kBkProducers; i++) { bk_mbar_init(&ctl.full[i], 1); bk_mbar_init(&ctl.empty[i], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  if (wid > 0) {
+    // ------------------------------------------------ producer ------------------------------------------------
+    const int p = wid - 1;
+    BkBuf& ws = bufs[p];
+    const float pfx = (float)px, pfy = (float)py;
+    const float X0 = (float)bx, X1 = (float)(bx + 7), Y0 = (float)by, Y1 = (float)(by + 3);
+    const uint32_t* const tl = list + range.x;
+    uint32_t* const rm = rowmask + ((size_t)seg_off[tile] * 8 + blk) * GS_MASK_WORDS;  // + segment * 8 * GS_MASK_WORDS + batch * 4 + group
+    Rec3 cur;
+    cur.a = cur.b = cur.c = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint32_t id_next = 0;
+    {
+      const int e = p * 32 + lane;
+      if (e < len) cur = load_rec(rec, tl[e]);
+      if (e + kBkProducers * 32 < len) id_next = tl[e + kBkProducers * 32];
+    }
+    uint32_t it = 0;
+    for (int b = p; b < nb; b += kBkProducers, it++) {
+      // software pipeline: records of this warp's next batch, list indices of the one after
+      const int e = b * 32 + lane;
+      Rec3 nxt = cur;
+      if (e + kBkProducers * 32 < len) nxt = load_rec(rec, id_next);
+      uint32_t id_nn = 0;
+      if (e + 2 * kBkProducers * 32 < len) id_nn = tl[e + 2 * kBkProducers * 32];
+      const bool keep = (e < len) && may_contribute(cur.a.x, cur.a.y, cur.b.x, cur.b.y, cur.b.z, cur.a.z, X0, X1, Y0, Y1);
+      // the consumer has finished with the previous rows -- or every pixel has terminated: the flag is polled inside the wait
+      // because the consumer's wake-up arrivals at termination can put the barrier two phases ahead (parity alias)
+      if (it > 0) {
+        while (!bk_mbar_try_wait(&ctl.empty[p], (it - 1) & 1u)) {
+          if (bk_ld_acquire(&ctl.done)) break;
+        }
+      }
+      __syncwarp();
+      {
+        uint32_t t = 0;
+        if (lane == 0) t = bk_ld_acquire(&ctl.done);
+        if (__shfl_sync(0xFFFFFFFFu, t, 0)) break;
+      }
+      if (e < len) {
+        ws.q0[lane] = make_float4(cur.a.x, cur.a.y, cur.b.x, cur.b.y);
+        ws.q1[lane] = make_float4(cur.b.z, cur.b.w, cur.c.x, cur.c.y);
+        ws.q2[lane] = cur.c.z;
+      }
+      __syncwarp();
+      uint32_t m = __ballot_sync(0xFFFFFFFFu, keep), kept0 = 0, kept1 = 0, kept2 = 0, kept3 = 0;
+      int k = 0;
+      while (m) {
+#pragma unroll
+        for (int u = 0; u < kPChunk; u++) {
+          const bool valid = m != 0;
+          const int j = valid ? (__ffs(m) - 1) : 0;
+          m &= m - 1;
+          const float4 q0 = ws.q0[j], q1 = ws.q1[j];
+          const float dx = __fsub_rn(q0.x, pfx), dy = __fsub_rn(q0.y, pfy);
+          const float power = __fmaf_rn(__fmaf_rn(dx, __fmul_rn(dx, q0.z), __fmul_rn(dy, __fmul_rn(dy, q1.x))), -0.5f,
+                                        -__fmul_rn(dy, __fmul_rn(dx, q0.w)));  // SASS: FFMA q*-0.5 - cross
+          const float alpha = fminf(0.99f, __fmul_rn(q1.y, blend_exp<POLY>(power)));
+          const bool ok = valid && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+          const uint32_t who = __ballot_sync(0xFFFFFFFFu, ok);
+          if (who) {  // rows no pixel of the block blends are dropped here, off the serial chain
+            ws.alpha[k][lane] = ok ? alpha : 0.0f;
+            if (lane == 0) ws.row[k] = make_float4(q1.z, q1.w, ws.q2[j], __int_as_float(b * 32 + j + 1));
+            // per 4x2 pixel group (lane = x + 8 y: x < 4 | x >= 4, y < 2 | y >= 2): what the backward visits
+            if (who & 0x00000F0Fu) kept0 |= 1u << j;
+            if (who & 0x0000F0F0u) kept1 |= 1u << j;
+            if (who & 0x0F0F0000u) kept2 |= 1u << j;
+            if (who & 0xF0F00000u) kept3 |= 1u << j;
+            k++;
+          }
+        }
+      }
+      for (int kk = k; kk & (kChunk - 1); kk++) {  // the consumer reads whole groups of rows, branch-free: pad rows must be 0 * finite
+        ws.alpha[kk][lane] = 0.0f;
+        if (lane == 0) ws.row[kk] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      if (lane == 0) {
+        ws.cnt = (uint32_t)k;
+        *reinterpret_cast<uint4*>(rm + (size_t)(b >> 2) * (8 * GS_MASK_WORDS) + (b & 3) * 4) = make_uint4(kept0, kept1, kept2, kept3);
+      }
+      __syncwarp();
+      if (lane == 0) bk_mbar_arrive(&ctl.full[p]);
+      cur = nxt;
+      id_next = id_nn;
+    }
+    return;
+  }
+
+  // -------------------------------------------------- consumer --------------------------------------------------
+  // checkpoint slots of this tile: one per segment start + one final (the backward's work items restart from them)
+  const size_t ck_base = ((size_t)seg_off[tile] + tile) * 256 + blk * 32 + lane;
+  float4* const ck = ckpt + ck_base;
+  float* const ck3 = OP ? ckpt_op + ck_base : nullptr;
+  float T = 1.0f, Tr = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, C3 = 0.f;  // see blend_fwd_work for the chain's state
+  uint32_t last = 0;
+  for (int b = 0; b < nb; b++) {
+    const int p = b % kBkProducers;
+    BkBuf& ws = bufs[p];
+    bk_mbar_wait(&ctl.full[p], (uint32_t)(b / kBkProducers) & 1u);
+    if ((b & (GS_SEG / 32 - 1)) == 0) {
+      ck[(size_t)(b / (GS_SEG / 32)) * 256] = make_float4(T, C0, C1, C2);
+      if (OP) ck3[(size_t)(b / (GS_SEG / 32)) * 256] = C3;
+    }
+    const int cnt = (int)ws.cnt;  // rows up to the next multiple of kChunk are zero-padded by the producer
+    for (int k0 = 0; k0 < cnt; k0 += kChunk) {
+      float al[kChunk];
+      float4 rw[kChunk];
+#pragma unroll
+      for (int u = 0; u < kChunk; u++) {
+        al[u] = ws.alpha[k0 + u][lane];
+        rw[u] = ws.row[k0 + u];
+      }
+#pragma unroll
+      for (int u = 0; u < kChunk; u++) {  // forward.cu:335-361 without carried control state, same values in the same order
+        const float test_T = __fmul_rn(Tr, __fsub_rn(1.0f, al[u]));
+        const bool ok = !(test_T < 0.0001f);
+        const float Tw = ok ? Tr : 0.0f;
+        C0 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].x), C0);
+        C1 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].y), C1);
+        C2 = __fmaf_rn(Tw, __fmul_rn(al[u], rw[u].z), C2);
+        if (OP) C3 = __fmaf_rn(Tw, al[u], C3);
+        T = ok ? test_T : T;
+        last = (ok && al[u] != 0.0f) ? (uint32_t)__float_as_int(rw[u].w) : last;
+        Tr = test_T;
+      }
+    }
+    const bool all_done = __all_sync(0xFFFFFFFFu, !inside || Tr < 0.0001f);
+    if (lane == 0) {
+      if (all_done) {  // stop the producers: whoever waits on an empty barrier wakes and sees the flag
+        bk_st_release(&ctl.done, 1u);
+        for (int i = 0; i < kBkProducers; i++) bk_mbar_arrive(&ctl.empty[i]);
+      } else {
+        bk_mbar_arrive_relaxed(&ctl.empty[p]);
+      }
+    }
+    if (all_done) break;
+  }
+  ck[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256] = make_float4(T, C0, C1, C2);
+  if (OP) ck3[(size_t)((len + GS_SEG - 1) / GS_SEG) * 256] = C3;
+  if (inside) {
+    const size_t pix = (size_t)py * W + px, hw = (size_t)H * W;
+    final_T[pix] = T;
+    n_contrib[pix] = last;
+    out_color[pix] = __fmaf_rn(T, bg[0], C0);
+    out_color[hw + pix] = __fmaf_rn(T, bg[1], C1);
+    out_color[2 * hw + pix] = __fmaf_rn(T, bg[2], C2);
+    if (OP) out_opacity[pix] = __fmaf_rn(T, bg[0], C3);  // channel 0 of the second call: same background
+  }
+}
+
 // Transposing butterfly step: N values per lane -> N/2, exchanging with lane ^ XOR.  After the steps for XOR = 16, 8, 4, 2, 1
 // on 32 values, lane L holds the warp total of value L: 31 shuffles for 32 sums instead of 160.
 template <int N, int XOR>
@@ -693,8 +933,22 @@ blend_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 int gs_launch_blend_fwd(const GsForwardArgs& a, const GsGeom& g, const GsImage& im, const GsList& l, const GsScratch& s,
                         cudaStream_t st) {
   const int gx = (a.width + GS_TILE - 1) / GS_TILE, gy = (a.height + GS_TILE - 1) / GS_TILE;
-  const size_t smem = sizeof(FwdSmem);
   const bool op = a.out_opacity != nullptr, poly = gs_exp_mode() != 0;
+  // Which forward blend: the chunked kernel for small tile grids (avatar frames: few deep tiles, the chain is the critical path),
+  // the per-block kernel for large ones (thousands of shallow tiles: throughput).  GS_FWD_KERNEL=chunk|block overrides.
+  static const int forced = [] { const char* e = getenv("GS_FWD_KERNEL"); return !e ? 0 : (e[0] == 'b' ? 2 : 1); }();
+  const bool block_kernel = forced ? forced == 2 : gx * gy > GS_BIN_MAX_TILES;
+  if (block_kernel) {
+    const size_t smem = sizeof(BkCtl) + kBkProducers * sizeof(BkBuf);
+    auto kern = op ? (poly ? blend_fwd_block_kernel<true, true> : blend_fwd_block_kernel<true, false>)
+                   : (poly ? blend_fwd_block_kernel<false, true> : blend_fwd_block_kernel<false, false>);
+    if (gs_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != GS_OK) return GS_ERR_CUDA;
+    gs_launch(kern, dim3((unsigned)(gx * gy) * 8u), dim3((kBkProducers + 1) * 32), smem, st, im.ranges, l.point_list, a.width, a.height,
+              g.rec, a.background, im.final_T, im.n_contrib, a.out_color, im.seg_off, l.ckpt, (const uint32_t*)l.order, gx, a.out_opacity,
+              l.ckpt_op, l.rowmask);
+    return gs_check(cudaGetLastError());
+  }
+  const size_t smem = sizeof(FwdSmem);
   auto kern = op ? (poly ? blend_fwd_kernel<true, true> : blend_fwd_kernel<true, false>)
                  : (poly ? blend_fwd_kernel<false, true> : blend_fwd_kernel<false, false>);
   // per device and per instantiation; cheap enough to set on every launch (a process may drive several GPUs)

@@ -75,8 +75,9 @@ struct GsList {
   float* ckpt_op;           // same slots: accumulated opacity channel (written only by the fused opacity pass)
   uint32_t* rowmask;        // [max_items][8 pixel blocks][GS_SEG / 32][4 groups] per 32-entry batch and 4x2 pixel group: entries at
                             // least one pixel of the strip blended in the forward pass (what the backward blend visits)
-  uint4* fitems;            // [max_fitems] forward work items (tile, chunk, index of the successor item or ~0, index of the
-                            // predecessor item or ~0), longest remaining chain first: a predecessor always has a smaller index
+  uint4* fitems;            // [max_fitems] forward work items (tile, chunk, hand-off slot it sends its chain state to or ~0, slot
+                            // it receives from or ~0); a predecessor always has a smaller index
+  uint32_t* order;          // [tiles] tiles by descending list length (chunk count): launch order of the per-block forward blend
   size_t max_items, max_fitems;
 };
 
@@ -145,6 +146,7 @@ static inline __host__ size_t gs_carve_list(char* base, int64_t cap, int W, int 
   gs_carve(p, t.ckpt_op, (t.max_items + tiles) * 256);
   gs_carve(p, t.rowmask, t.max_items * 8 * GS_MASK_WORDS);
   gs_carve(p, t.fitems, t.max_fitems);
+  gs_carve(p, t.order, tiles);
   if (l) *l = t;
   return (size_t)(p - base);
 }

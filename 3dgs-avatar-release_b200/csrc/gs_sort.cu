@@ -347,7 +347,7 @@ __device__ __forceinline__ uint32_t block_scan_incl_1024(uint32_t v, uint32_t* s
 // `ranges` may live in global memory (plan_kernel) or in shared memory (the plan block of bin_place_kernel).  1024 threads.
 __device__ __forceinline__ void plan_body(int tiles, const uint2* ranges, uint32_t* __restrict__ seg_off, uint2* __restrict__ items,
                                           uint32_t max_items, uint4* __restrict__ fitems, uint32_t max_fitems,
-                                          GsHeader* __restrict__ hdr, int fwd_order) {
+                                          GsHeader* __restrict__ hdr, int fwd_order, uint32_t* __restrict__ order) {
   __shared__ uint32_t s_w[32];
   __shared__ uint32_t s_hist[GS_FWD_NCH_BINS];  // tiles per chunk count -> cursor of the counting sort
   __shared__ uint32_t s_base[GS_FWD_NCH_BINS];  // base[r] = sum over k < r of ge[k]
@@ -437,7 +437,8 @@ __device__ __forceinline__ void plan_body(int tiles, const uint2* ranges, uint32
     const uint2 r = ranges[t];
     const uint32_t len = r.y - r.x;
     const uint32_t nch = min((len + GS_FWD_CHUNK - 1) / GS_FWD_CHUNK, (uint32_t)GS_FWD_NCH_BINS - 1);
-    const uint32_t pos = atomicAdd(&s_hist[nch], 1u);
+    const uint32_t pos = atomicAdd(&s_hist[nch], 1u);  // rank of the tile by descending chunk count (empty tiles last)
+    order[pos] = (uint32_t)t;
     const uint32_t roff = roff_l[(t >> 10) & 63];
     if (nch == 0) {  // empty tile: one item behind everything else
       const uint32_t fi = n_items + (pos - n_nonempty);
@@ -462,9 +463,10 @@ __device__ __forceinline__ void plan_body(int tiles, const uint2* ranges, uint32
 
 __global__ void __launch_bounds__(1024)
 plan_kernel(int tiles, const uint2* __restrict__ ranges, uint32_t* __restrict__ seg_off, uint2* __restrict__ items,
-            uint32_t max_items, uint4* __restrict__ fitems, uint32_t max_fitems, GsHeader* __restrict__ hdr, int fwd_order) {
+            uint32_t max_items, uint4* __restrict__ fitems, uint32_t max_fitems, GsHeader* __restrict__ hdr, int fwd_order,
+            uint32_t* __restrict__ order) {
   GS_PDL_PROLOGUE();
-  plan_body(tiles, ranges, seg_off, items, max_items, fitems, max_fitems, hdr, fwd_order);
+  plan_body(tiles, ranges, seg_off, items, max_items, fitems, max_fitems, hdr, fwd_order, order);
 }
 
 // tiles <= 2 * GS_BIN_THREADS.  Block 0 also publishes the tile ranges (identifyTileRanges, rasterizer_impl.cu:116-138:
@@ -478,7 +480,7 @@ bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __re
                  const uint32_t* __restrict__ rect, int grid_x, int tiles, uint32_t* blockcount, uint32_t* tile_total,
                  unsigned long long cap, uint32_t* __restrict__ list, uint2* __restrict__ ranges, GsHeader* __restrict__ hdr,
                  uint32_t* grid_bar, uint32_t* __restrict__ seg_off, uint2* __restrict__ items, uint32_t max_items,
-                 uint4* __restrict__ fitems, uint32_t max_fitems, int fwd_order) {
+                 uint4* __restrict__ fitems, uint32_t max_fitems, int fwd_order, uint32_t* __restrict__ order) {
   GS_PDL_PROLOGUE();
   extern __shared__ __align__(16) unsigned char s_raw[];
   uint16_t* s_off = reinterpret_cast<uint16_t*>(s_raw);                                  // [32][tiles]
@@ -557,7 +559,7 @@ bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __re
     if (ta < tiles) s_range[ta] = ca ? make_uint2(min(sa, lim), min(sa + ca, lim)) : make_uint2(0u, 0u);
     if (tb < tiles) s_range[tb] = cb ? make_uint2(min(sb, lim), min(sb + cb, lim)) : make_uint2(0u, 0u);
     __syncthreads();
-    plan_body(tiles, s_range, seg_off, items, max_items, fitems, max_fitems, hdr, fwd_order);
+    plan_body(tiles, s_range, seg_off, items, max_items, fitems, max_fitems, hdr, fwd_order, order);
     return;
   }
   if (ta < tiles) s_base[ta] = sa + pa;
@@ -751,7 +753,7 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
     gs_launch(fused ? bin_place_kernel<true> : bin_place_kernel<false>, dim3(blocks_c + (fused ? 1 : 0)), dim3(GS_BIN_THREADS), smem_p,
               st, P, (const uint32_t*)s.dval[0], (const uint32_t*)s.dval[1], (const uint32_t*)s.hist, (const uint32_t*)g.tiles_touched,
               (const uint32_t*)g.rect, gx, tiles, blockcount, s.tile_total, (unsigned long long)cap, list, im.ranges, g.hdr,
-              s.counters + 16, im.seg_off, l.items, (uint32_t)l.max_items, (uint4*)l.fitems, (uint32_t)l.max_fitems, fwd_order);
+              s.counters + 16, im.seg_off, l.items, (uint32_t)l.max_items, (uint4*)l.fitems, (uint32_t)l.max_fitems, fwd_order, l.order);
     if (fused) return gs_check(cudaGetLastError());  // the plans came from the placement grid's last block
   } else {
     // 2. chained scan + pair emission in depth order
@@ -785,6 +787,6 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   }
   // 5. backward work plan (segments of GS_SEG entries per tile)
   gs_launch(plan_kernel, dim3(1), dim3(1024), 0, st, tiles, im.ranges, im.seg_off, l.items, (uint32_t)l.max_items, l.fitems,
-            (uint32_t)l.max_fitems, g.hdr, fwd_order);
+            (uint32_t)l.max_fitems, g.hdr, fwd_order, l.order);
   return gs_check(cudaGetLastError());
 }

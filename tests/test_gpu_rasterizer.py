@@ -359,15 +359,19 @@ def test_mark_visible(built_lib):
         assert np.array_equal(got, rmask), f"{int((got != rmask).sum())} visibility decisions differ from the reference build"
 
 
-@pytest.mark.parametrize("order", ["0", "1"])
-def test_alternative_forward_item_orders(built_lib, order):
-    """The forward blend's work items can be planned in three orders (GS_FWD_ORDER: 2 = mixed, the default; 0 = longest remaining
-    chain first; 1 = level by level).  The order only schedules: images, n_contrib and gradients must not depend on it.  The
-    variable is read once per process, so the bit-exact tests of the deep-list and bench-size scenes run in a child process."""
+@pytest.mark.parametrize("env", [{"GS_FWD_ORDER": "0"}, {"GS_FWD_ORDER": "1"}, {"GS_FWD_KERNEL": "block"}], ids=["order0", "order1", "block_kernel"])
+def test_alternative_forward_variants(built_lib, env):
+    """The forward blend has two kernels (chunked, the default for tile grids <= 2048 tiles; per-block with producer / consumer
+    warps, the default above: GS_FWD_KERNEL=chunk|block forces one) and the chunked kernel three orders of its work items
+    (GS_FWD_ORDER: 2 = mixed, the default; 0 = longest remaining chain first; 1 = level by level).  All of them only SCHEDULE the
+    same per-pixel operation sequence: images, n_contrib and gradients must not depend on the choice.  The variables are read once
+    per process, so the bit-exact tests of the deep-list, bench-size, trained-like and A/B-against-the-reference scenes run in
+    a child process."""
     import subprocess
     import sys
     here = os.path.dirname(os.path.abspath(__file__))
-    env = dict(os.environ, GS_FWD_ORDER=order)
-    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_rasterizer.py"), "-q", "-m", "gpu", "-x", "-k",
-                        "deep_lists or bench_config or trained_like or unfused"], env=env, capture_output=True, text=True, timeout=900)
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_rasterizer.py"), os.path.join(here, "test_gpu_vs_reference_cuda.py"),
+                        os.path.join(here, "test_gpu_opacity_pass.py"), "-q", "-m", "gpu", "-x", "-k",
+                        "deep_lists or bench_config or trained_like or unfused or reference_cuda_build or opacity"],
+                       env=dict(os.environ, **env), capture_output=True, text=True, timeout=1200)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]
