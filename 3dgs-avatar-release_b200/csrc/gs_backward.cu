@@ -101,30 +101,42 @@ __device__ void cov3d_backward(const float* __restrict__ s3, float mod, const fl
   dL_drot[3] = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
 }
 
-__global__ void __launch_bounds__(256, 4) preprocess_bwd_kernel(GsBackwardArgs a, const float* __restrict__ cov3Ds,
+template <bool PRE>
+__global__ void __launch_bounds__(256, PRE ? 3 : 4) preprocess_bwd_kernel(GsBackwardArgs a, const float* __restrict__ cov3Ds,
                                                              const uint8_t* __restrict__ clamped, const GsRec* __restrict__ recs,
                                                              float* __restrict__ accs) {
-  GS_PDL_PROLOGUE();
+  if (!PRE) GS_PDL_PROLOGUE();
+  // The direct predecessor of this grid is always blend_bwd_kernel of the same call, which waited for everything before it:
+  // whatever blend_bwd does not write (camera, the first Gaussian's forward-time state) is fetched BEFORE the wait, under the
+  // tail of the blend; only the accumulators come after it.
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   if (threadIdx.x < 16) { s_view[threadIdx.x] = a.viewmatrix[threadIdx.x]; s_proj[threadIdx.x] = a.projmatrix[threadIdx.x]; }
   if (threadIdx.x < 3 && a.campos) s_cam[threadIdx.x] = a.campos[threadIdx.x];
-  __syncthreads();
   const float* view = s_view;
   const float* proj = s_proj;
   const float h_y = a.height / (2.0f * a.tan_fovy), h_x = a.width / (2.0f * a.tan_fovx);
   const float limx = 1.3f * a.tan_fovx, limy = 1.3f * a.tan_fovy;
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < a.P; idx += gridDim.x * blockDim.x) {
+  const int idx0 = blockIdx.x * blockDim.x + threadIdx.x;
+  int radius = 0;
+  float mx = 0.f, my = 0.f, mz = 0.f, c6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  float4 rb = make_float4(0.f, 0.f, 0.f, 0.f);
+  // every load of a Gaussian is issued BEFORE the visibility branch (all of them are in bounds for a culled Gaussian too):
+  // one memory round trip per thread instead of two -- at 1M Gaussians the kernel sat on long-scoreboard stalls
+  auto load_state = [&](int idx) {
+    radius = a.radii[idx];
+    mx = a.means3D[3 * (size_t)idx]; my = a.means3D[3 * (size_t)idx + 1]; mz = a.means3D[3 * (size_t)idx + 2];
+#pragma unroll
+    for (int k = 0; k < 6; k++) c6[k] = cov3Ds[6 * (size_t)idx + k];
+    rb = reinterpret_cast<const float4*>(recs + idx)[1];  // conic a, b, c, opacity
+  };
+  if (idx0 < a.P) load_state(idx0);
+  __syncthreads();
+  if (PRE) GS_PDL_PROLOGUE();
+  for (int idx = idx0; idx < a.P; idx += gridDim.x * blockDim.x) {
     // the blend's accumulators: consumed here and zeroed again (a second backward over the same forward starts clean)
     float4* const ac = reinterpret_cast<float4*>(accs + (size_t)GS_ACC * idx);
     const float4 ac0 = ac[0], ac1 = ac[1], ac2 = ac[2];
-    // every load of this Gaussian is issued BEFORE the visibility branch (all of them are in bounds for a culled Gaussian too):
-    // one memory round trip per thread instead of two -- at 1M Gaussians the kernel sat on long-scoreboard stalls
-    const int radius = a.radii[idx];
-    const float mx = a.means3D[3 * (size_t)idx], my = a.means3D[3 * (size_t)idx + 1], mz = a.means3D[3 * (size_t)idx + 2];
-    float c6[6];
-#pragma unroll
-    for (int k = 0; k < 6; k++) c6[k] = cov3Ds[6 * (size_t)idx + k];
-    const float4 rb = reinterpret_cast<const float4*>(recs + idx)[1];  // conic a, b, c, opacity
+    if (idx != idx0) load_state(idx);
     ac[0] = ac[1] = ac[2] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (!(radius > 0)) {  // culled: every gradient is zero (the outputs need no initialisation by the caller)
       a.dL_dmean2D[3 * (size_t)idx] = a.dL_dmean2D[3 * (size_t)idx + 1] = a.dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
@@ -247,6 +259,7 @@ int gs_launch_preprocess_bwd(const GsBackwardArgs& a, const GsGeom& g, cudaStrea
   int blocks = (a.P + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
   const float* cov = a.cov3D_precomp ? a.cov3D_precomp : g.cov3D;
-  gs_launch(preprocess_bwd_kernel, dim3(blocks), dim3(256), 0, st, a, cov, g.clamped, (const GsRec*)g.rec, g.acc);
+  gs_launch((gs_prewait_mask() & 4) ? preprocess_bwd_kernel<true> : preprocess_bwd_kernel<false>, dim3(blocks), dim3(256), 0, st, a, cov,
+            g.clamped, (const GsRec*)g.rec, g.acc);
   return gs_check(cudaGetLastError());
 }

@@ -11,6 +11,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/gsplat_b200.h"
 
@@ -240,6 +241,12 @@ __device__ __forceinline__ float gs_exp(float x) {
     asm volatile("griddepcontrol.wait;" ::: "memory");             \
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); \
   } while (0)
+// Which kernels run their predecessor-independent prologue BEFORE griddepcontrol.wait (GS_PREWAIT bit mask, default all):
+// 1 depth-sort links 1..3, 2 placement, 4 preprocess backward.
+static inline int gs_prewait_mask() {
+  static const int m = [] { const char* e = getenv("GS_PREWAIT"); return e ? atoi(e) : 7; }();
+  return m;
+}
 template <typename... KArgs, typename... Args>
 static inline cudaError_t gs_launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
   cudaLaunchConfig_t cfg = {};

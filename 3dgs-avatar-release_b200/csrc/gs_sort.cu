@@ -54,13 +54,19 @@ __device__ __forceinline__ void st_volatile(uint32_t* p, uint32_t v) { *reinterp
 // (vals_in, vals_out) = (buffer 0, buffer 1); constant-digit passes are skipped WITHOUT a copy, so a pass reads the buffer
 // selected by the number of effective passes before it (all histograms, `hist_chain`, exist before the first pass) and the
 // consumers locate the result with depth_result_buffer().  chain_pass < 0: fixed buffers, constant digit = plain copy.
-template <int ITEMS>
+template <int ITEMS, bool EARLY>
 __global__ void __launch_bounds__(GS_SORT_THREADS)
 onesweep_pass_kernel(const uint32_t* keys_in, uint32_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
                      const unsigned long long* __restrict__ n_ptr, unsigned long long n_cap, int shift,
                      const uint32_t* __restrict__ hist, uint32_t* __restrict__ status, uint32_t* __restrict__ ticket,
                      unsigned int* __restrict__ error_flag, int chain_pass, const uint32_t* __restrict__ hist_chain) {
-  GS_PDL_PROLOGUE();
+  // Links 1..3 of the depth chain read only what the kernels BEFORE the chain produced up to their key loads (n, the digit
+  // histograms of preprocess, counters zeroed at the start of the call) and their direct predecessor is always link p-1, which
+  // has itself waited for its predecessor before letting this grid start: the prologue below (histogram words, ticket,
+  // shared-memory clear) runs while link p-1 is still scattering, and the wait moves down to the first key load (EARLY).
+  // A template parameter, not a run-time branch: loads through const __restrict__ pointers are invariant loads, which the
+  // compiler hoists above a CONDITIONAL wait -- link 0 then read the histograms while preprocess was still adding to them.
+  if (!EARLY) GS_PDL_PROLOGUE();
   constexpr int LB = ITEMS <= 4 ? 32 : 8;  // look-back width: predecessors fetched per round trip
   constexpr int WARPS = GS_SORT_THREADS / 32;
   __shared__ uint32_t s_warp_hist[WARPS][256];
@@ -79,6 +85,7 @@ onesweep_pass_kernel(const uint32_t* keys_in, uint32_t* keys_out, const uint32_t
 #pragma unroll
   for (int i = 0; i < WARPS; i++) s_warp_hist[i][tid] = 0;
   __syncthreads();
+  if (EARLY) GS_PDL_PROLOGUE();  // before any exit: a grid that returns without waiting would release ITS successor early
   const uint32_t tile = s_ticket;
   const unsigned long long base = (unsigned long long)tile * (ITEMS * GS_SORT_THREADS);
   if (base >= n) return;
@@ -232,7 +239,7 @@ __device__ __forceinline__ BinWarp bin_load(int P, int i, const uint32_t* __rest
   uint32_t gid = 0, cnt = 0;
   uint2 r = make_uint2(0u, 0u);
   if (i < P) {
-    gid = sorted_gid[i];
+    gid = __ldcg(sorted_gid + i);  // NOT an invariant load: it must stay behind the caller's griddepcontrol.wait
     cnt = tiles_touched[gid];
     if (cnt) r = *reinterpret_cast<const uint2*>(rect + 2 * (size_t)gid);
   }
@@ -473,7 +480,7 @@ plan_kernel(int tiles, const uint2* __restrict__ ranges, uint32_t* __restrict__ 
 // empty tiles stay (0,0)) and the pair count.  FUSED: the grid is small enough to be co-resident (the launcher checks), the
 // kernel does the counting itself and crosses a grid-wide barrier instead of a kernel boundary; otherwise
 // bin_count_kernel has run before.
-template <bool FUSED>
+template <bool FUSED, bool PRE>
 __global__ void __launch_bounds__(GS_BIN_THREADS)
 bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __restrict__ dval1,
                  const uint32_t* __restrict__ hist_chain, const uint32_t* __restrict__ tiles_touched,
@@ -481,7 +488,7 @@ bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __re
                  unsigned long long cap, uint32_t* __restrict__ list, uint2* __restrict__ ranges, GsHeader* __restrict__ hdr,
                  uint32_t* grid_bar, uint32_t* __restrict__ seg_off, uint2* __restrict__ items, uint32_t max_items,
                  uint4* __restrict__ fitems, uint32_t max_fitems, int fwd_order, uint32_t* __restrict__ order) {
-  GS_PDL_PROLOGUE();
+  if (!PRE) GS_PDL_PROLOGUE();
   extern __shared__ __align__(16) unsigned char s_raw[];
   uint16_t* s_off = reinterpret_cast<uint16_t*>(s_raw);                                  // [32][tiles]
   uint32_t* s_base = reinterpret_cast<uint32_t*>(s_raw + (size_t)64 * tiles);            // [tiles]
@@ -495,9 +502,15 @@ bin_place_kernel(int P, const uint32_t* __restrict__ dval0, const uint32_t* __re
   const unsigned nblocks = FUSED ? gridDim.x - 1 : gridDim.x;
   BinWarp bw;
   bw.total = 0; bw.excl = 0; bw.nz = false;
+  // Before the wait: the counter clear and the choice of the sorted buffer (digit histograms of preprocess; the direct
+  // predecessor of this grid is always the last link of the depth chain, which waited for everything before it).
+  const uint32_t* sorted_gid = nullptr;
   if (!plan_block) {  // block-uniform
     for (int k = tid; k < 16 * tiles; k += GS_BIN_THREADS) reinterpret_cast<uint32_t*>(s_off)[k] = 0;
-    const uint32_t* sorted_gid = depth_result_buffer(hist_chain, (unsigned long long)P, tid) ? dval1 : dval0;  // + barrier
+    sorted_gid = depth_result_buffer(hist_chain, (unsigned long long)P, tid) ? dval1 : dval0;  // + barrier
+  }
+  if (PRE) GS_PDL_PROLOGUE();
+  if (!plan_block) {
     bw = bin_load(P, blockIdx.x * GS_BIN_THREADS + tid, sorted_gid, tiles_touched, rect, s_stage[w], lane);
     bin_warp_walk<false>(bw, s_stage[w], grid_x, s_off + (size_t)w * tiles, nullptr, nullptr, 0ull, lane);
   }
@@ -726,8 +739,11 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   //    for 50k keys against 26 us for these passes: 8 SMs at ~1 IPC lose to a latency chain spread over 49 SMs.)
   const int blocks_d = (int)gs_sort_blocks((unsigned long long)P);
   const bool small_d = gs_sort_items((unsigned long long)P) == GS_SORT_ITEMS_SMALL;
+  const int prewait = gs_prewait_mask();
   for (int p = 0; p < 4; p++) {
-    auto kern = small_d ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL> : onesweep_pass_kernel<GS_SORT_ITEMS>;
+    const bool early = (prewait & 1) && p >= 1;  // link 0 follows preprocess, the producer of everything it reads
+    auto kern = small_d ? (early ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL, true> : onesweep_pass_kernel<GS_SORT_ITEMS_SMALL, false>)
+                        : (early ? onesweep_pass_kernel<GS_SORT_ITEMS, true> : onesweep_pass_kernel<GS_SORT_ITEMS, false>);
     gs_launch(kern, dim3(blocks_d), dim3(GS_SORT_THREADS), 0, st,
         (const uint32_t*)s.dkey[0], s.dkey[1], (const uint32_t*)s.dval[0], s.dval[1], (const unsigned long long*)nullptr,
         (unsigned long long)P, 8 * p, (const uint32_t*)(s.hist + p * 256), s.status_d + (size_t)p * s.blocks_d * 256,
@@ -740,8 +756,9 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
     {  // per call: function attributes are per DEVICE, and one process may drive several
       const int max_smem = 68 * GS_BIN_MAX_TILES;
       if (cudaFuncSetAttribute(bin_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess ||
-          cudaFuncSetAttribute(bin_place_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess ||
-          cudaFuncSetAttribute(bin_place_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess)
+          cudaFuncSetAttribute(bin_place_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess ||
+          cudaFuncSetAttribute(bin_place_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess ||
+          cudaFuncSetAttribute(bin_place_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem) != cudaSuccess)
         return gs_check(cudaGetLastError());
     }
     uint32_t* blockcount = s.tkey[0];  // [blocks_c][tiles] <= cap words
@@ -750,7 +767,9 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
       gs_launch(bin_count_kernel, dim3(blocks_c), dim3(GS_BIN_THREADS), smem_c, st, P, (const uint32_t*)s.dval[0],
                 (const uint32_t*)s.dval[1], (const uint32_t*)s.hist, (const uint32_t*)g.tiles_touched, (const uint32_t*)g.rect,
                 gx, tiles, blockcount, s.tile_total);
-    gs_launch(fused ? bin_place_kernel<true> : bin_place_kernel<false>, dim3(blocks_c + (fused ? 1 : 0)), dim3(GS_BIN_THREADS), smem_p,
+    const bool pre = fused && (prewait & 2);
+    gs_launch(fused ? (pre ? bin_place_kernel<true, true> : bin_place_kernel<true, false>) : bin_place_kernel<false, false>,
+              dim3(blocks_c + (fused ? 1 : 0)), dim3(GS_BIN_THREADS), smem_p,
               st, P, (const uint32_t*)s.dval[0], (const uint32_t*)s.dval[1], (const uint32_t*)s.hist, (const uint32_t*)g.tiles_touched,
               (const uint32_t*)g.rect, gx, tiles, blockcount, s.tile_total, (unsigned long long)cap, list, im.ranges, g.hdr,
               s.counters + 16, im.seg_off, l.items, (uint32_t)l.max_items, (uint4*)l.fitems, (uint32_t)l.max_fitems, fwd_order, l.order);
@@ -771,7 +790,7 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
     const bool small_t = gs_sort_items((unsigned long long)cap) == GS_SORT_ITEMS_SMALL;
     for (int p = 0; p < tile_passes; p++) {
       uint32_t* vout = (p == tile_passes - 1) ? list : vbuf[(p + 1) & 1];
-      auto kern = small_t ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL> : onesweep_pass_kernel<GS_SORT_ITEMS>;
+      auto kern = small_t ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL, false> : onesweep_pass_kernel<GS_SORT_ITEMS, false>;
       gs_launch(kern, dim3(blocks_t), dim3(GS_SORT_THREADS), 0, st,
           (const uint32_t*)s.tkey[p & 1], s.tkey[(p + 1) & 1], (const uint32_t*)vbuf[p & 1], vout,
           (const unsigned long long*)&g.hdr->num_rendered, (unsigned long long)cap, 8 * p,
