@@ -153,7 +153,9 @@ static inline __host__ size_t gs_carve_list(char* base, int64_t cap, int W, int 
 }
 
 #define GS_SORT_ITEMS 16                                   // keys per thread, large inputs
+#ifndef GS_SORT_ITEMS_SMALL
 #define GS_SORT_ITEMS_SMALL 4                              // small inputs: more, shorter CTAs (latency-bound regime)
+#endif
 #define GS_SORT_SMALL_MAX (1 << 19)                        // inputs up to this size use the small tile
 #define GS_SORT_THREADS 256
 #define GS_SORT_TILE (GS_SORT_ITEMS * GS_SORT_THREADS)   // 4096 keys per CTA

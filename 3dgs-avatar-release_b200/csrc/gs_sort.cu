@@ -67,7 +67,7 @@ onesweep_pass_kernel(const uint32_t* keys_in, uint32_t* keys_out, const uint32_t
   // A template parameter, not a run-time branch: loads through const __restrict__ pointers are invariant loads, which the
   // compiler hoists above a CONDITIONAL wait -- link 0 then read the histograms while preprocess was still adding to them.
   if (!EARLY) GS_PDL_PROLOGUE();
-  constexpr int LB = ITEMS <= 4 ? 32 : 8;  // look-back width: predecessors fetched per round trip
+  constexpr int LB = ITEMS <= 8 ? 32 : 8;  // look-back width: predecessors fetched per round trip
   constexpr int WARPS = GS_SORT_THREADS / 32;
   __shared__ uint32_t s_warp_hist[WARPS][256];
   __shared__ uint32_t s_digit_base[256];
