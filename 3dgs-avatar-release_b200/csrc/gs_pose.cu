@@ -63,6 +63,13 @@ __device__ __forceinline__ void sh_basis_grad(int deg, float x, float y, float z
   }
 }
 
+// All 16 basis values / gradients, unconditionally: the callers' loops over k are fully unrolled and predicated with k < nb, so
+// the arrays live in registers (with run-time bounds they sat in local memory and every use was a long-scoreboard LDL).
+__device__ __forceinline__ void sh_basis16(float x, float y, float z, float (&b)[16]) { sh_basis(3, x, y, z, b); }
+__device__ __forceinline__ void sh_basis_grad16(float x, float y, float z, float (&gx)[16], float (&gy)[16], float (&gz)[16]) {
+  sh_basis_grad(3, x, y, z, gx, gy, gz);
+}
+
 struct PoseCore {
   float A[3][3], t[3];     // blended transform (rows 0..2 of T_fwd)
   float qn[4], inv_norm;   // normalised quaternion
@@ -76,10 +83,13 @@ struct PoseCore {
 // independent coalesced loads in flight per lane instead of 45 dependent-latency strided ones; the rows are then read
 // back lane-private with an odd stride (conflict-free).
 #define POSE_MAXREST 45
-__device__ __forceinline__ void warp_stage_in(float* __restrict__ s, const float* __restrict__ g, int n, int lane) {
-  float v[POSE_MAXREST];
+// Two halves, so that the caller can issue every other global load of the Gaussian between them: one memory round trip per
+// warp instead of two.
+__device__ __forceinline__ void warp_stage_load(float (&v)[POSE_MAXREST], const float* __restrict__ g, int n, int lane) {
 #pragma unroll
   for (int k = 0; k < POSE_MAXREST; k++) { const int e = k * 32 + lane; v[k] = e < n ? __ldg(g + e) : 0.f; }
+}
+__device__ __forceinline__ void warp_stage_commit(float* __restrict__ s, const float (&v)[POSE_MAXREST], int n, int lane) {
 #pragma unroll
   for (int k = 0; k < POSE_MAXREST; k++) { const int e = k * 32 + lane; if (e < n) s[e] = v[k]; }
   __syncwarp();
@@ -91,19 +101,38 @@ __device__ __forceinline__ void warp_stage_out(float* __restrict__ g, const floa
   __syncwarp();
 }
 
-__device__ __forceinline__ void pose_core(const PoseArgs& a, int i, const float* __restrict__ s_bones, PoseCore& c) {
+// The Gaussian's own inputs, loaded before anything is computed (and before the SH rows are committed to shared memory).
+struct PoseRaw {
+  float w[24];
+  float x, y, z;
+  float4 q;
+  float sc[3];
+  float op;
+  float dc[3];
+};
+__device__ __forceinline__ void pose_load(const PoseArgs& a, int i, PoseRaw& r) {
+  const float4* wp = reinterpret_cast<const float4*>(a.weights + (size_t)i * 24);  // 96-byte rows: 16-byte aligned
+#pragma unroll
+  for (int k = 0; k < 6; k++) { const float4 t = __ldg(wp + k); r.w[4 * k] = t.x; r.w[4 * k + 1] = t.y; r.w[4 * k + 2] = t.z; r.w[4 * k + 3] = t.w; }
+  r.x = a.xyz[3 * (size_t)i]; r.y = a.xyz[3 * (size_t)i + 1]; r.z = a.xyz[3 * (size_t)i + 2];
+  if ((reinterpret_cast<uintptr_t>(a.rotation) & 15) == 0) {
+    r.q = *reinterpret_cast<const float4*>(a.rotation + 4 * (size_t)i);
+  } else {  // a view into a flat parameter slab (avatar_pose.optim) starts at float 3P: aligned only when P % 4 == 0
+    const float* qp = a.rotation + 4 * (size_t)i;
+    r.q = make_float4(qp[0], qp[1], qp[2], qp[3]);
+  }
+#pragma unroll
+  for (int k = 0; k < 3; k++) { r.sc[k] = a.scaling[3 * (size_t)i + k]; r.dc[k] = a.features_dc[3 * (size_t)i + k]; }
+  r.op = a.opacity[i];
+}
+
+__device__ __forceinline__ void pose_core(const PoseArgs& a, const PoseRaw& raw, const float* __restrict__ s_bones, PoseCore& c) {
   float T[12];
 #pragma unroll
   for (int k = 0; k < 12; k++) T[k] = 0.f;
-  float w[24];
-  {
-    const float4* wp = reinterpret_cast<const float4*>(a.weights + (size_t)i * 24);  // 96-byte rows: 16-byte aligned
-#pragma unroll
-    for (int k = 0; k < 6; k++) { const float4 t = __ldg(wp + k); w[4 * k] = t.x; w[4 * k + 1] = t.y; w[4 * k + 2] = t.z; w[4 * k + 3] = t.w; }
-  }
 #pragma unroll
   for (int j = 0; j < 24; j++) {
-    const float wj = w[j];
+    const float wj = raw.w[j];
 #pragma unroll
     for (int k = 0; k < 12; k++) T[k] = fmaf(wj, s_bones[j * 16 + k], T[k]);
   }
@@ -111,16 +140,10 @@ __device__ __forceinline__ void pose_core(const PoseArgs& a, int i, const float*
   for (int r = 0; r < 3; r++) {
     c.A[r][0] = T[4 * r]; c.A[r][1] = T[4 * r + 1]; c.A[r][2] = T[4 * r + 2]; c.t[r] = T[4 * r + 3];
   }
-  const float x = a.xyz[3 * (size_t)i], y = a.xyz[3 * (size_t)i + 1], z = a.xyz[3 * (size_t)i + 2];
+  const float x = raw.x, y = raw.y, z = raw.z;
 #pragma unroll
   for (int r = 0; r < 3; r++) c.xb[r] = c.A[r][0] * x + c.A[r][1] * y + c.A[r][2] * z + c.t[r];
-  float4 q;
-  if ((reinterpret_cast<uintptr_t>(a.rotation) & 15) == 0) {
-    q = *reinterpret_cast<const float4*>(a.rotation + 4 * (size_t)i);
-  } else {  // a view into a flat parameter slab (avatar_pose.optim) starts at float 3P: aligned only when P % 4 == 0
-    const float* qp = a.rotation + 4 * (size_t)i;
-    q = make_float4(qp[0], qp[1], qp[2], qp[3]);
-  }
+  const float4 q = raw.q;
   const float norm = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
   c.inv_norm = 1.0f / norm;
   const float qr = q.x * c.inv_norm, qx = q.y * c.inv_norm, qy = q.z * c.inv_norm, qz = q.w * c.inv_norm;
@@ -133,7 +156,7 @@ __device__ __forceinline__ void pose_core(const PoseArgs& a, int i, const float*
 #pragma unroll
     for (int k = 0; k < 3; k++) c.Rb[r][k] = c.A[r][0] * c.R[0][k] + c.A[r][1] * c.R[1][k] + c.A[r][2] * c.R[2][k];
 #pragma unroll
-  for (int k = 0; k < 3; k++) c.s[k] = a.scaling_modifier * expf(a.scaling[3 * (size_t)i + k]);
+  for (int k = 0; k < 3; k++) c.s[k] = a.scaling_modifier * expf(raw.sc[k]);
 }
 
 // view direction fed to eval_sh (texture.py:23-35): returns d (un-normalised), n = |d|
@@ -154,8 +177,8 @@ __device__ __forceinline__ void view_dir(const PoseArgs& a, const PoseCore& c, c
 }
 
 // SH coefficient k of channel ch: dc from global (12 B per thread), the rest from this lane's staged row
-__device__ __forceinline__ float sh_coef(const PoseArgs& a, int i, const float* __restrict__ rest_row, int k, int ch) {
-  return k == 0 ? a.features_dc[3 * (size_t)i + ch] : rest_row[(k - 1) * 3 + ch];
+__device__ __forceinline__ float sh_coef(const PoseRaw& raw, const float* __restrict__ rest_row, int k, int ch) {
+  return k == 0 ? raw.dc[ch] : rest_row[(k - 1) * 3 + ch];
 }
 
 __global__ void __launch_bounds__(128) pose_fwd_kernel(PoseArgs a) {
@@ -171,11 +194,16 @@ __global__ void __launch_bounds__(128) pose_fwd_kernel(PoseArgs a) {
   const int nrest = (a.M - 1) * 3;  // floats per Gaussian in features_rest (<= 45)
   for (int i0 = blockIdx.x * blockDim.x + threadIdx.x - lane; i0 < a.P; i0 += gridDim.x * blockDim.x) {  // warp-uniform
     const int i = i0 + lane;
-    if (nrest) warp_stage_in(s_rest, a.features_rest + (size_t)i0 * nrest, min(32, a.P - i0) * nrest, lane);
+    const int nstaged = min(32, a.P - i0) * nrest;
+    float v[POSE_MAXREST];
+    PoseRaw raw;
+    if (nrest) warp_stage_load(v, a.features_rest + (size_t)i0 * nrest, nstaged, lane);
+    if (i < a.P) pose_load(a, i, raw);
+    if (nrest) warp_stage_commit(s_rest, v, nstaged, lane);
     const float* rest_row = s_rest + lane * nrest;
     if (i < a.P) {
     PoseCore c;
-    pose_core(a, i, s_bones, c);
+    pose_core(a, raw, s_bones, c);
     a.means3D[3 * (size_t)i] = c.xb[0]; a.means3D[3 * (size_t)i + 1] = c.xb[1]; a.means3D[3 * (size_t)i + 2] = c.xb[2];
     float L[3][3];
 #pragma unroll
@@ -189,17 +217,19 @@ __global__ void __launch_bounds__(128) pose_fwd_kernel(PoseArgs a) {
     cov[3] = L[1][0] * L[1][0] + L[1][1] * L[1][1] + L[1][2] * L[1][2];
     cov[4] = L[1][0] * L[2][0] + L[1][1] * L[2][1] + L[1][2] * L[2][2];
     cov[5] = L[2][0] * L[2][0] + L[2][1] * L[2][1] + L[2][2] * L[2][2];
-    a.opacity_out[i] = 1.0f / (1.0f + expf(-a.opacity[i]));
+    a.opacity_out[i] = 1.0f / (1.0f + expf(-raw.op));
     float d[3], n;
     view_dir(a, c, s_cam, d, n);
     const float inv = 1.0f / (n + 1e-12f);
     float b[16];
-    sh_basis(a.sh_degree, d[0] * inv, d[1] * inv, d[2] * inv, b);
+    sh_basis16(d[0] * inv, d[1] * inv, d[2] * inv, b);
     const int nb = (a.sh_degree + 1) * (a.sh_degree + 1);
 #pragma unroll
     for (int ch = 0; ch < 3; ch++) {
       float acc = 0.f;
-      for (int k = 0; k < nb; k++) acc += b[k] * sh_coef(a, i, rest_row, k, ch);
+#pragma unroll
+      for (int k = 0; k < 16; k++)
+        if (k < nb) acc += b[k] * sh_coef(raw, rest_row, k, ch);
       a.colors[3 * (size_t)i + ch] = fmaxf(acc + 0.5f, 0.0f);
     }
     if (a.T_fwd) {
@@ -225,7 +255,7 @@ __global__ void __launch_bounds__(128) pose_fwd_kernel(PoseArgs a) {
   }
 }
 
-__global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
+__global__ void __launch_bounds__(128, 3) pose_bwd_kernel(PoseBackwardArgs ba) {
   GS_PDL_PROLOGUE();
   const PoseArgs& a = ba.fwd;
   __shared__ float s_bones[24 * 16];
@@ -242,15 +272,26 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
   for (int i0 = blockIdx.x * blockDim.x + threadIdx.x - lane; i0 < a.P; i0 += gridDim.x * blockDim.x) {  // warp-uniform
     const int i = i0 + lane;
     const int nstaged = min(32, a.P - i0) * nrest;
-    if (nrest) warp_stage_in(s_rest, a.features_rest + (size_t)i0 * nrest, nstaged, lane);
+    float v[POSE_MAXREST];
+    PoseRaw raw;
+    float gxb[3] = {0.f, 0.f, 0.f}, gcol[3] = {0.f, 0.f, 0.f}, g6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, gop = 0.f;
+    if (nrest) warp_stage_load(v, a.features_rest + (size_t)i0 * nrest, nstaged, lane);
+    if (i < a.P) {  // every global load of the Gaussian, upstream gradients included, in the same round trip
+      pose_load(a, i, raw);
+#pragma unroll
+      for (int k = 0; k < 3; k++) { gxb[k] = ba.dL_dmeans3D[3 * (size_t)i + k]; gcol[k] = ba.dL_dcolors[3 * (size_t)i + k]; }
+#pragma unroll
+      for (int k = 0; k < 6; k++) g6[k] = ba.dL_dcov3D[6 * (size_t)i + k];
+      gop = ba.dL_dopacity[i];
+    }
+    if (nrest) warp_stage_commit(s_rest, v, nstaged, lane);
     float* rest_row = s_rest + lane * nrest;
     float gT[12];  // dL/dT_fwd[:3, :4] of this Gaussian (zero for the lanes past P)
 #pragma unroll
     for (int k = 0; k < 12; k++) gT[k] = 0.f;
     if (i < a.P) {
     PoseCore c;
-    pose_core(a, i, s_bones, c);
-    float gxb[3] = {ba.dL_dmeans3D[3 * (size_t)i], ba.dL_dmeans3D[3 * (size_t)i + 1], ba.dL_dmeans3D[3 * (size_t)i + 2]};
+    pose_core(a, raw, s_bones, c);
     // ---- colour -> SH coefficients and view direction ----
     {
       float d[3], n;
@@ -258,20 +299,25 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
       const float inv = 1.0f / (n + 1e-12f);
       const float ux = d[0] * inv, uy = d[1] * inv, uz = d[2] * inv;
       float b[16], bx[16], by[16], bz[16];
-      sh_basis(a.sh_degree, ux, uy, uz, b);
-      sh_basis_grad(a.sh_degree, ux, uy, uz, bx, by, bz);
+      sh_basis16(ux, uy, uz, b);
+      sh_basis_grad16(ux, uy, uz, bx, by, bz);
       const int nb = (a.sh_degree + 1) * (a.sh_degree + 1);
       float gu[3] = {0.f, 0.f, 0.f};
 #pragma unroll
       for (int ch = 0; ch < 3; ch++) {
         float acc = 0.f;
-        for (int k = 0; k < nb; k++) acc += b[k] * sh_coef(a, i, rest_row, k, ch);
-        const float gc = (acc + 0.5f < 0.0f) ? 0.f : ba.dL_dcolors[3 * (size_t)i + ch];
+#pragma unroll
+        for (int k = 0; k < 16; k++)
+          if (k < nb) acc += b[k] * sh_coef(raw, rest_row, k, ch);
+        const float gc = (acc + 0.5f < 0.0f) ? 0.f : gcol[ch];
         ba.dL_dfeatures_dc[3 * (size_t)i + ch] = b[0] * gc;
-        for (int k = 1; k < a.M; k++) {
-          const float coef = k < nb ? rest_row[(k - 1) * 3 + ch] : 0.f;
-          rest_row[(k - 1) * 3 + ch] = k < nb ? b[k] * gc : 0.f;  // the staged coefficient is consumed: its slot takes the gradient
-          if (k < nb) { gu[0] += bx[k] * coef * gc; gu[1] += by[k] * coef * gc; gu[2] += bz[k] * coef * gc; }
+#pragma unroll
+        for (int k = 1; k < 16; k++) {
+          if (k < a.M) {
+            const float coef = k < nb ? rest_row[(k - 1) * 3 + ch] : 0.f;
+            rest_row[(k - 1) * 3 + ch] = k < nb ? b[k] * gc : 0.f;  // the staged coefficient is consumed: its slot takes the gradient
+            if (k < nb) { gu[0] += bx[k] * coef * gc; gu[1] += by[k] * coef * gc; gu[2] += bz[k] * coef * gc; }
+          }
         }
       }
       // u = d / (n + eps):  dL/dd = g/(n+eps) - d (d.g) / (n (n+eps)^2)
@@ -293,7 +339,6 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
       }
     }
     // ---- covariance -> R_bar, scaling ----
-    const float* g6 = ba.dL_dcov3D + 6 * (size_t)i;
     const float G[3][3] = {{g6[0], 0.5f * g6[1], 0.5f * g6[2]}, {0.5f * g6[1], g6[3], 0.5f * g6[4]}, {0.5f * g6[2], 0.5f * g6[4], g6[5]}};
     float L[3][3], dLm[3][3], gRb[3][3];
 #pragma unroll
@@ -340,11 +385,11 @@ __global__ void __launch_bounds__(128) pose_bwd_kernel(PoseBackwardArgs ba) {
       }
     }
     // mean: x_bar = A x + t
-    const float x = a.xyz[3 * (size_t)i], y = a.xyz[3 * (size_t)i + 1], z = a.xyz[3 * (size_t)i + 2];
+    const float x = raw.x, y = raw.y, z = raw.z;
 #pragma unroll
     for (int k = 0; k < 3; k++) ba.dL_dxyz[3 * (size_t)i + k] = c.A[0][k] * gxb[0] + c.A[1][k] * gxb[1] + c.A[2][k] * gxb[2];
-    const float so = 1.0f / (1.0f + expf(-a.opacity[i]));
-    ba.dL_dopacity_logit[i] = ba.dL_dopacity[i] * so * (1.0f - so);
+    const float so = 1.0f / (1.0f + expf(-raw.op));
+    ba.dL_dopacity_logit[i] = gop * so * (1.0f - so);
     if (ba.dL_dweights || ba.dL_dbone_transforms) {
 #pragma unroll
       for (int r = 0; r < 3; r++) {
