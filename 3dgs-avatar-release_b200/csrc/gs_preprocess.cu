@@ -122,6 +122,29 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsForwardArgs a, GsGeom
   __shared__ float s_view[16], s_proj[16], s_cam[3];
   if (threadIdx.x < 16) { s_view[threadIdx.x] = a.viewmatrix[threadIdx.x]; s_proj[threadIdx.x] = a.projmatrix[threadIdx.x]; }
   if (threadIdx.x < 3 && a.campos) s_cam[threadIdx.x] = a.campos[threadIdx.x];
+  // The Gaussian's own inputs (all in bounds for a culled Gaussian too) are requested BEFORE the barrier behind the camera
+  // loads and before the visibility / empty-rectangle branches: one memory round trip per thread instead of four.
+  const int idx0 = blockIdx.x * blockDim.x + threadIdx.x;
+  float mx = 0.f, my = 0.f, mz = 0.f, c6in[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, sc[3] = {0.f, 0.f, 0.f}, rq[4] = {0.f, 0.f, 0.f, 0.f};
+  float colin[3] = {0.f, 0.f, 0.f}, oin = 0.f;
+  auto load_inputs = [&](int idx) {
+    mx = a.means3D[3 * idx]; my = a.means3D[3 * idx + 1]; mz = a.means3D[3 * idx + 2];
+    if (a.cov3D_precomp) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) c6in[k] = a.cov3D_precomp[6 * (size_t)idx + k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < 3; k++) sc[k] = a.scales[3 * (size_t)idx + k];
+#pragma unroll
+      for (int k = 0; k < 4; k++) rq[k] = a.rotations[4 * (size_t)idx + k];
+    }
+    if (a.colors_precomp) {
+#pragma unroll
+      for (int k = 0; k < 3; k++) colin[k] = a.colors_precomp[3 * (size_t)idx + k];
+    }
+    oin = a.opacities[idx];
+  };
+  if (idx0 < a.P) load_inputs(idx0);
   __syncthreads();
   const float* v = s_view;
   const float* pm = s_proj;
@@ -130,15 +153,15 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsForwardArgs a, GsGeom
   const float focal_y = H / (2.0f * a.tan_fovy), focal_x = W / (2.0f * a.tan_fovx);  // rasterizer_impl.cu:222-223
   const float limx = __fmul_rn(a.tan_fovx, 1.3f), limy = __fmul_rn(a.tan_fovy, 1.3f);
 
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < a.P; idx += gridDim.x * blockDim.x) {
+  for (int idx = idx0; idx < a.P; idx += gridDim.x * blockDim.x) {
     uint32_t key = 0xFFFFFFFFu;
     int radius = 0;
     uint32_t touched = 0;
+    if (idx != idx0) load_inputs(idx);
     {  // accumulators of the backward blend start at zero (no separate fill launch)
       float4* const ac = reinterpret_cast<float4*>(g.acc + (size_t)GS_ACC * idx);
       ac[0] = ac[1] = ac[2] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    const float mx = a.means3D[3 * idx], my = a.means3D[3 * idx + 1], mz = a.means3D[3 * idx + 2];
     const float pvz = gs_dot3p(mx, v[2], my, v[6], mz, v[10], v[14]);
     if (pvz > 0.2f) {  // auxiliary.h:154
       float hx = gs_dot3p(mx, pm[0], my, pm[4], mz, pm[8], pm[12]);
@@ -149,9 +172,9 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsForwardArgs a, GsGeom
       float c6[6];
       if (a.cov3D_precomp) {
 #pragma unroll
-        for (int k = 0; k < 6; k++) c6[k] = a.cov3D_precomp[6 * (size_t)idx + k];
+        for (int k = 0; k < 6; k++) c6[k] = c6in[k];
       } else {
-        cov3d_from_scale_rot(a.scales + 3 * (size_t)idx, a.scale_modifier, a.rotations + 4 * (size_t)idx, c6);
+        cov3d_from_scale_rot(sc, a.scale_modifier, rq, c6);
 #pragma unroll
         for (int k = 0; k < 6; k++) g.cov3D[6 * (size_t)idx + k] = c6[k];
       }
@@ -200,9 +223,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsForwardArgs a, GsGeom
         if (area != 0) {
           GsRec rec;
           if (a.colors_precomp) {
-            rec.r = a.colors_precomp[3 * (size_t)idx];
-            rec.g = a.colors_precomp[3 * (size_t)idx + 1];
-            rec.b = a.colors_precomp[3 * (size_t)idx + 2];
+            rec.r = colin[0]; rec.g = colin[1]; rec.b = colin[2];
           } else {
             float rgb[3];
             uint8_t cl[3];
@@ -210,7 +231,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsForwardArgs a, GsGeom
             rec.r = rgb[0]; rec.g = rgb[1]; rec.b = rgb[2];
             g.clamped[3 * (size_t)idx] = cl[0]; g.clamped[3 * (size_t)idx + 1] = cl[1]; g.clamped[3 * (size_t)idx + 2] = cl[2];
           }
-          float o = a.opacities[idx];
+          float o = oin;
           rec.x = px; rec.y = py; rec.depth = pvz;
           rec.tau = __logf(255.0f * o);  // cull helper only (never decides a blend; see gs_blend.cu)
           rec.ca = con_a; rec.cb = con_b; rec.cc = con_c; rec.o = o;
