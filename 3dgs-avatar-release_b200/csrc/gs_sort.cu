@@ -241,7 +241,7 @@ __device__ __forceinline__ BinWarp bin_load(int P, int i, const uint32_t* __rest
   if (i < P) {
     gid = __ldcg(sorted_gid + i);  // NOT an invariant load: it must stay behind the caller's griddepcontrol.wait
     cnt = tiles_touched[gid];
-    if (cnt) r = *reinterpret_cast<const uint2*>(rect + 2 * (size_t)gid);
+    r = *reinterpret_cast<const uint2*>(rect + 2 * (size_t)gid);  // unconditional (in bounds; unused when cnt == 0): both loads in one round trip
   }
   uint32_t incl = cnt;
 #pragma unroll
