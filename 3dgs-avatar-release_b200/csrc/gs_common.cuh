@@ -158,6 +158,7 @@ static inline __host__ size_t gs_carve_list(char* base, int64_t cap, int W, int 
 #endif
 #define GS_SORT_SMALL_MAX (1 << 19)                        // inputs up to this size use the small tile
 #define GS_SORT_THREADS 256
+#define GS_SORT_FUSED_MAX_BLOCKS 148                       // depth chain in one launch up to this many CTAs (co-resident: one per SM)
 #define GS_SORT_TILE (GS_SORT_ITEMS * GS_SORT_THREADS)   // 4096 keys per CTA
 #define GS_EMIT_THREADS 256
 #define GS_L1_MAX_BLOCKS 592                               // fused L1 loss: 4 CTAs per SM

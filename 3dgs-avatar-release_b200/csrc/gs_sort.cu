@@ -211,6 +211,149 @@ onesweep_pass_kernel(const uint32_t* keys_in, uint32_t* keys_out, const uint32_t
   }
 }
 
+// The whole depth chain in ONE launch (small inputs: every CTA of the grid is resident at once).  The passes over non-constant
+// digits run back to back inside the kernel, separated by a grid-wide barrier (one atomic arrive + spin per CTA, ~1.5 us)
+// instead of a kernel boundary (~3 us of drain + dependent wake-up each, and a whole launch for a skipped digit).  Tile = block
+// index: all predecessors of the look-back are running.  Keys and payloads written by another SM one pass ago are read with
+// ld.global.cg -- the ping-pong returns to a buffer this SM may still hold in L1 from two passes ago.  Same ranking, same
+// look-back, same scatter as onesweep_pass_kernel: identical permutation; the result sits where depth_result_buffer() says.
+template <int ITEMS>
+__global__ void __launch_bounds__(GS_SORT_THREADS)
+depth_sort_fused_kernel(uint32_t* key0, uint32_t* key1, uint32_t* val0, uint32_t* val1, unsigned long long n,
+                        const uint32_t* __restrict__ hist_chain, uint32_t* __restrict__ status, size_t status_stride,
+                        uint32_t* grid_bar, unsigned int* __restrict__ error_flag) {
+  GS_PDL_PROLOGUE();
+  constexpr int LB = 32;
+  constexpr int WARPS = GS_SORT_THREADS / 32;
+  __shared__ uint32_t s_warp_hist[WARPS][256];
+  __shared__ uint32_t s_digit_base[256];
+  __shared__ uint32_t s_scan[WARPS];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const uint32_t tile = blockIdx.x;
+  const unsigned long long base = (unsigned long long)tile * (ITEMS * GS_SORT_THREADS);
+  const unsigned long long wbase = base + (unsigned long long)w * (32 * ITEMS);
+  uint32_t hd[4];
+#pragma unroll
+  for (int p = 0; p < 4; p++) hd[p] = hist_chain[p * 256 + tid];
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  int cur = 0;
+  uint32_t phase = 0;
+#pragma unroll 1
+  for (int p = 0; p < 4; p++) {
+    const uint32_t h_own = p == 0 ? hd[0] : p == 1 ? hd[1] : p == 2 ? hd[2] : hd[3];
+    if (__syncthreads_or((unsigned long long)h_own == n)) continue;  // constant digit: identity, skipped without a copy
+    if (phase > 0) {  // grid-wide barrier: the previous effective pass has been scattered by every CTA
+      __syncthreads();
+      if (tid == 0) {
+        __threadfence();
+        atomicAdd(grid_bar, 1u);
+        uint32_t spins = 0;
+        while (ld_volatile(grid_bar) < gridDim.x * phase)
+          if (++spins > SPIN_LIMIT) { atomicExch(error_flag, 1u); break; }
+        __threadfence();
+      }
+      __syncthreads();
+    }
+    phase++;
+    const uint32_t* keys_in = cur ? key1 : key0;
+    const uint32_t* vals_in = cur ? val1 : val0;
+    uint32_t* keys_out = cur ? key0 : key1;
+    uint32_t* vals_out = cur ? val0 : val1;
+    cur ^= 1;
+    if (base >= n) continue;  // (block-uniform) a spare CTA only keeps the barriers company
+    const int shift = 8 * p;
+#pragma unroll
+    for (int i = 0; i < WARPS; i++) s_warp_hist[i][tid] = 0;
+    uint32_t key[ITEMS], val[ITEMS], rank[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      const unsigned long long idx = wbase + i * 32 + lane;
+      key[i] = idx < n ? __ldcg(keys_in + idx) : 0xFFFFFFFFu;
+      val[i] = idx < n ? __ldcg(vals_in + idx) : 0u;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      const unsigned long long idx = wbase + i * 32 + lane;
+      const bool valid = idx < n;
+      const uint32_t digit = (key[i] >> shift) & 255u;
+      const uint32_t m = __match_any_sync(0xFFFFFFFFu, valid ? digit : 256u);
+      const int leader = __ffs(m) - 1;
+      uint32_t prev = 0;
+      if (valid && lane == leader) {
+        prev = s_warp_hist[w][digit];
+        s_warp_hist[w][digit] = prev + __popc(m);
+      }
+      prev = __shfl_sync(0xFFFFFFFFu, prev, leader);
+      rank[i] = prev + __popc(m & lt_mask);
+      __syncwarp();
+    }
+    __syncthreads();
+    const int d = tid;
+    uint32_t run = 0;
+#pragma unroll
+    for (int i = 0; i < WARPS; i++) {
+      const uint32_t c = s_warp_hist[i][d];
+      s_warp_hist[i][d] = run;
+      run += c;
+    }
+    uint32_t* const st = status + (size_t)p * status_stride;
+    uint32_t* const my_status = st + (size_t)tile * 256 + d;
+    st_volatile(my_status, (tile == 0 ? FLAG_INCL : FLAG_LOCAL) | run);
+    uint32_t excl = 0;
+    if (tile > 0) {
+      long long t = (long long)tile - 1;
+      uint32_t spins = 0;
+      bool finished = false;
+      while (!finished && t >= 0) {
+        uint32_t sv[LB];
+#pragma unroll
+        for (int k = 0; k < LB; k++) sv[k] = (t - k >= 0) ? ld_volatile(st + (size_t)(t - k) * 256 + d) : FLAG_INCL;
+        int used = LB;
+#pragma unroll
+        for (int k = 0; k < LB; k++) {
+          if (k < used) {
+            if (sv[k] == 0) { used = k; }
+            else {
+              excl += sv[k] & VALUE_MASK;
+              if (sv[k] & FLAG_INCL) { finished = true; used = k; }
+            }
+          }
+        }
+        if (!finished) {
+          t -= used;
+          if (used == 0 && ++spins > SPIN_LIMIT) { atomicExch(error_flag, 1u); break; }
+        }
+      }
+      st_volatile(my_status, FLAG_INCL | (excl + run));
+    }
+    uint32_t incl = h_own;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t2 = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += t2;
+    }
+    if (lane == 31) s_scan[w] = incl;
+    __syncthreads();
+    uint32_t wpre = 0;
+#pragma unroll
+    for (int i = 0; i < WARPS; i++) wpre += (i < w) ? s_scan[i] : 0u;
+    s_digit_base[d] = wpre + incl - h_own + excl;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+      const unsigned long long idx = wbase + i * 32 + lane;
+      if (idx < n) {
+        const uint32_t digit = (key[i] >> shift) & 255u;
+        const uint32_t pos = s_digit_base[digit] + s_warp_hist[w][digit] + rank[i];
+        keys_out[pos] = key[i];
+        vals_out[pos] = val[i];
+      }
+    }
+    __syncthreads();  // s_warp_hist / s_digit_base are rewritten by the next pass
+  }
+}
+
 // Index (0/1) of the depth ping-pong buffer that holds the sorted result: the number of effective (non-constant) passes,
 // mod 2.  Block-wide call (>= 256 threads, all threads).
 __device__ __forceinline__ int depth_result_buffer(const uint32_t* __restrict__ hist_chain, unsigned long long n, int tid) {
@@ -740,6 +883,13 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   const int blocks_d = (int)gs_sort_blocks((unsigned long long)P);
   const bool small_d = gs_sort_items((unsigned long long)P) == GS_SORT_ITEMS_SMALL;
   const int prewait = gs_prewait_mask();
+  // one launch when every CTA of the chain can be resident at once (GS_SORT_FUSED=0: the four-launch chain)
+  static const bool sort_fused = [] { const char* e = getenv("GS_SORT_FUSED"); return e ? atoi(e) != 0 : true; }();
+  if (sort_fused && small_d && blocks_d <= GS_SORT_FUSED_MAX_BLOCKS) {
+    gs_launch(depth_sort_fused_kernel<GS_SORT_ITEMS_SMALL>, dim3(blocks_d), dim3(GS_SORT_THREADS), 0, st, s.dkey[0], s.dkey[1], s.dval[0],
+              s.dval[1], (unsigned long long)P, (const uint32_t*)s.hist, s.status_d, (size_t)s.blocks_d * 256, s.counters + 12,
+              &g.hdr->error);
+  } else
   for (int p = 0; p < 4; p++) {
     const bool early = (prewait & 1) && p >= 1;  // link 0 follows preprocess, the producer of everything it reads
     auto kern = small_d ? (early ? onesweep_pass_kernel<GS_SORT_ITEMS_SMALL, true> : onesweep_pass_kernel<GS_SORT_ITEMS_SMALL, false>)

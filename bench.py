@@ -991,11 +991,13 @@ def ours_main(args):
             ref_cuda = {"unavailable": str(ex)[:200]}
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     blocks_c = (P + 1023) // 1024
+    # depth sort (gs_sort.cu): ONE launch while its CTAs (1024 keys each) are co-resident, else one launch per 8-bit digit
+    depth = 1 if (P <= (1 << 19) and blocks_c <= 148 and os.environ.get("GS_SORT_FUSED", "1") != "0") else 4
     if tiles <= 2048:  # direct placement (gs_sort.cu): count+place fused into one grid up to 120 blocks, else two kernels
-        binning = 4 + (1 if blocks_c <= 120 else 3)                # depth passes, placement (its last block plans) | count, place, plan
+        binning = depth + (1 if blocks_c <= 120 else 3)            # depth sort, placement (its last block plans) | count, place, plan
     else:
         tile_passes = (max(tiles.bit_length(), 1) + 7) // 8
-        binning = 4 + 1 + tile_passes + 1 + 1                       # depth passes, emit, tile passes, ranges, plan
+        binning = depth + 1 + tile_passes + 1 + 1                   # depth sort, emit, tile passes, ranges, plan
     # pose_fwd | preprocess, binning, blend_fwd | l1 loss fwd + bwd | blend_bwd, preprocess_bwd | pose_bwd
     launches = args.steps * (1 + (1 + binning + 1) + 2 + 2 + 1 + (1 if symm_slab is not None else 0))  # + slab_allreduce
     h2d = int(f_pin["small"].numel() * 4 + f_pin["target"].numel() * 4)

@@ -359,11 +359,14 @@ def test_mark_visible(built_lib):
         assert np.array_equal(got, rmask), f"{int((got != rmask).sum())} visibility decisions differ from the reference build"
 
 
-@pytest.mark.parametrize("env", [{"GS_FWD_ORDER": "0"}, {"GS_FWD_ORDER": "1"}, {"GS_FWD_KERNEL": "block"}], ids=["order0", "order1", "block_kernel"])
+@pytest.mark.parametrize("env", [{"GS_FWD_ORDER": "0"}, {"GS_FWD_ORDER": "1"}, {"GS_FWD_KERNEL": "block"}, {"GS_SORT_FUSED": "0", "GS_PREWAIT": "0"}],
+                         ids=["order0", "order1", "block_kernel", "sort_chain_of_four_launches"])
 def test_alternative_forward_variants(built_lib, env):
     """The forward blend has two kernels (chunked, the default for tile grids <= 2048 tiles; per-block with producer / consumer
     warps, the default above: GS_FWD_KERNEL=chunk|block forces one) and the chunked kernel three orders of its work items
-    (GS_FWD_ORDER: 2 = mixed, the default; 0 = longest remaining chain first; 1 = level by level).  All of them only SCHEDULE the
+    (GS_FWD_ORDER: 2 = mixed, the default; 0 = longest remaining chain first; 1 = level by level); the depth sort runs as one
+    launch (default for small inputs) or as a chain of four (GS_SORT_FUSED=0, here with the prologues behind the wait,
+    GS_PREWAIT=0).  All of them only SCHEDULE the
     same per-pixel operation sequence: images, n_contrib and gradients must not depend on the choice.  The variables are read once
     per process, so the bit-exact tests of the deep-list, bench-size, trained-like and A/B-against-the-reference scenes run in
     a child process."""
