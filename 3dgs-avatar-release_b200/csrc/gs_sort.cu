@@ -885,7 +885,12 @@ int gs_launch_binning(const GsForwardArgs& a, const GsGeom& g, const GsImage& im
   const int prewait = gs_prewait_mask();
   // one launch when every CTA of the chain can be resident at once (GS_SORT_FUSED=0: the four-launch chain)
   static const bool sort_fused = [] { const char* e = getenv("GS_SORT_FUSED"); return e ? atoi(e) != 0 : true; }();
-  if (sort_fused && small_d && blocks_d <= GS_SORT_FUSED_MAX_BLOCKS) {
+  const int blocks_f = (P + GS_SORT_FUSED_ITEMS * GS_SORT_THREADS - 1) / (GS_SORT_FUSED_ITEMS * GS_SORT_THREADS);
+  if (sort_fused && small_d && blocks_f <= GS_SORT_FUSED_MAX_BLOCKS) {  // shorter tiles while the grid stays co-resident
+    gs_launch(depth_sort_fused_kernel<GS_SORT_FUSED_ITEMS>, dim3(blocks_f), dim3(GS_SORT_THREADS), 0, st, s.dkey[0], s.dkey[1], s.dval[0],
+              s.dval[1], (unsigned long long)P, (const uint32_t*)s.hist, s.status_d, (size_t)s.blocks_d * 256, s.counters + 12,
+              &g.hdr->error);
+  } else if (sort_fused && small_d && blocks_d <= GS_SORT_FUSED_MAX_BLOCKS) {
     gs_launch(depth_sort_fused_kernel<GS_SORT_ITEMS_SMALL>, dim3(blocks_d), dim3(GS_SORT_THREADS), 0, st, s.dkey[0], s.dkey[1], s.dval[0],
               s.dval[1], (unsigned long long)P, (const uint32_t*)s.hist, s.status_d, (size_t)s.blocks_d * 256, s.counters + 12,
               &g.hdr->error);
