@@ -223,7 +223,7 @@ depth_sort_fused_kernel(uint32_t* key0, uint32_t* key1, uint32_t* val0, uint32_t
                         const uint32_t* __restrict__ hist_chain, uint32_t* __restrict__ status, size_t status_stride,
                         uint32_t* grid_bar, unsigned int* __restrict__ error_flag) {
   GS_PDL_PROLOGUE();
-  constexpr int LB = 32;
+  constexpr int LB = 32;  // predecessors per look-back round trip (measured: 64 -> binning 52 us; 16 or 8 -> the stage alone 42 us but the whole step +11 us; 32 -> 45 us)
   constexpr int WARPS = GS_SORT_THREADS / 32;
   __shared__ uint32_t s_warp_hist[WARPS][256];
   __shared__ uint32_t s_digit_base[256];
